@@ -1,0 +1,103 @@
+"""Parity oracle loaders (TEST INFRASTRUCTURE ONLY -- never imported by mv3d_b200).
+
+Two CPU implementations of the view encoder, both behind ctypes:
+
+* `restated`  -- oracle/view_oracle.c, our flat-array restatement (oracle/_build/libview_oracle.so);
+* `reference` -- the reference's own ver3 C sources compiled unmodified (oracle/_ref/*.so), when present.
+
+Both are called the way `ver3/createTopMaps.py:15-23` / `ver3/createTopAndFrontMaps.py:20-33` call the
+reference. Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs use this.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+RESTATED_SO = os.path.join(_HERE, "_build", "libview_oracle.so")
+REF_TOP_SO = os.path.join(_HERE, "_ref", "LidarTopPreprocess.so")
+REF_TOPFRONT_SO = os.path.join(_HERE, "_ref", "LidarTopAndFrontPreprocess.so")
+
+_cf, _ci, _vp = ctypes.c_float, ctypes.c_int, ctypes.c_void_p
+_TOP_ARGTYPES = [_vp, _ci, _vp] + [_cf] * 9 + [_ci] * 3
+_TOPFRONT_ARGTYPES = [_vp, _ci, _vp, _vp] + [_cf] * 9 + [_ci] * 3 + [_cf] * 9
+
+
+def build(force: bool = False) -> None:
+    """Compile the restatement (always) and oracle/_ref (only where /root/reference exists)."""
+    if force or not os.path.exists(RESTATED_SO) or \
+            os.path.getmtime(RESTATED_SO) < os.path.getmtime(os.path.join(_HERE, "view_oracle.c")):
+        subprocess.run(["make", "-C", _HERE, "_build/libview_oracle.so"], check=True, capture_output=True)
+    if force or not reference_available():
+        subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
+
+
+def reference_available() -> bool:
+    return os.path.exists(REF_TOP_SO) and os.path.exists(REF_TOPFRONT_SO)
+
+
+_libs = {}
+
+
+def _lib(path):
+    if path not in _libs:
+        _libs[path] = ctypes.CDLL(path)
+    return _libs[path]
+
+
+def _points(raw):
+    raw = np.ascontiguousarray(raw, dtype=np.float32)
+    assert raw.ndim == 2 and raw.shape[1] == 4, "points must be (N, 4) float32"
+    return raw
+
+
+def _front_alloc(front):
+    # The reference stores one row + one pixel past the end when r_coord == R_SIZE:
+    # give it room, return only the in-bounds image.
+    n = front.rn * front.cn * front.fn
+    buf = np.ones(n + front.cn * front.fn + 2 * front.fn + 16, dtype=np.float32)
+    return buf, n
+
+
+def top_maps(raw, top, impl: str = "restated") -> np.ndarray:
+    """`createTopMaps` semantics -> float32 `[Xn][Yn][Zn+2]` (un-flipped, as the ABI leaves it)."""
+    raw = _points(raw)
+    out = np.ones(top.shape, dtype=np.float32)  # callee overwrites everything
+    if impl == "restated":
+        fn = _lib(RESTATED_SO).oracle_createTopMaps
+    elif impl == "reference":
+        fn = _lib(REF_TOP_SO).createTopMaps
+    else:
+        raise ValueError(impl)
+    fn.argtypes = _TOP_ARGTYPES
+    fn(raw.ctypes.data, raw.shape[0], out.ctypes.data, *top.floats, top.xn, top.yn, top.zn)
+    return out
+
+
+def top_and_front_maps(raw, top, front, impl: str = "restated"):
+    """`createTopAndFrontMaps` semantics -> (top `[Xn][Yn][Zn+2]`, front `[R][C][F]`), float32."""
+    raw = _points(raw)
+    out = np.ones(top.shape, dtype=np.float32)
+    fbuf, n = _front_alloc(front)
+    if impl == "restated":
+        fn = _lib(RESTATED_SO).oracle_createTopAndFrontMaps
+    elif impl == "reference":
+        fn = _lib(REF_TOPFRONT_SO).createTopAndFrontMaps
+    else:
+        raise ValueError(impl)
+    fn.argtypes = _TOPFRONT_ARGTYPES
+    fn(raw.ctypes.data, raw.shape[0], out.ctypes.data, fbuf.ctypes.data, *top.floats,
+       top.xn, top.yn, top.zn, front.phi_min, front.phi_max, front.theta_min, front.theta_max,
+       front.phi_div, front.theta_div, float(front.cn), float(front.rn), float(front.fn))
+    return out, fbuf[:n].reshape(front.shape).copy()
+
+
+def density_table() -> np.ndarray:
+    out = np.zeros(32, dtype=np.float32)
+    fn = _lib(RESTATED_SO).oracle_density_table
+    fn.argtypes = [_vp]
+    fn(out.ctypes.data)
+    return out
