@@ -1,0 +1,125 @@
+/*
+ * mv3d_encode.h -- C ABI of libmv3d_encode.so, the B200 (sm_100a) LiDAR view encoder.
+ *
+ * Part 1 is the drop-in boundary: the two symbols MV3D loads with ctypes.cdll.LoadLibrary, with
+ * byte-identical signatures, host pointers, synchronous, same output layout.
+ * Part 2 is additive: a device-resident, batched entry point for callers that keep sweeps in HBM.
+ *
+ * All citations are relative to the reference tree (jeasinema/MV3D).
+ * No function here throws or aborts; failures are reported through mv3d_last_error().
+ * There is no CPU fallback: without a CUDA device every entry point fails loudly.
+ */
+#ifndef MV3D_ENCODE_H
+#define MV3D_ENCODE_H
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------------
+ * Part 1 -- reference symbols (drop-in)
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Replaces src/lidar_data_preprocess/Python_to_C_Interface/ver3/LidarTopPreprocess.c:30.
+ * Bound by src/data.py:280-289 and ver3/createTopMaps.py:15-23.
+ *   raw_data : host, num x 4 float32 (x, y, z, intensity), C-contiguous, read-only
+ *   top_data : host, X_SIZE*Y_SIZE*(Z_SIZE+2) float32, fully overwritten (despite the const)
+ * Cell index by (int) truncation. On failure top_data is zero-filled and mv3d_last_error() is set. */
+void createTopMaps(const void *raw_data, int num, const void *top_data,
+                   float x_MIN, float x_MAX, float y_MIN, float y_MAX, float z_MIN, float z_MAX,
+                   float x_DIVISION, float y_DIVISION, float z_DIVISION,
+                   int X_SIZE, int Y_SIZE, int Z_SIZE);
+
+/* Replaces .../ver3/LidarTopAndFrontPreprocess.c:30. Bound by ver3/createTopAndFrontMaps.py:20-33.
+ *   front_data : host, R_SIZE*C_SIZE*F_SIZE float32, fully overwritten
+ * Cell index by (int)floor(). The reference stores one row past the end of front_data when
+ * r_coord == R_SIZE; this implementation applies the same linear index and drops those stores.
+ * C_SIZE/R_SIZE/F_SIZE must hold integral values with F_SIZE >= 3 (what the reference's wrapper passes). */
+void createTopAndFrontMaps(const void *raw_data, int num, const void *top_data, const void *front_data,
+                           float x_MIN, float x_MAX, float y_MIN, float y_MAX, float z_MIN, float z_MAX,
+                           float x_DIVISION, float y_DIVISION, float z_DIVISION,
+                           int X_SIZE, int Y_SIZE, int Z_SIZE,
+                           float phi_MIN, float phi_MAX, float theta_MIN, float theta_MAX,
+                           float phi_DIVISION, float theta_DIVISION,
+                           float C_SIZE, float R_SIZE, float F_SIZE);
+
+/* ------------------------------------------------------------------------------------------------
+ * Part 2 -- additive API (the reference has no equivalent; its ABI returns void and keeps no state)
+ * ---------------------------------------------------------------------------------------------- */
+
+/* Error text of the last failing call on this thread ("" if none). Never NULL. */
+const char *mv3d_last_error(void);
+
+/* The 9 floats + 3 ints of createTopMaps, in the reference's argument order. */
+typedef struct mv3d_top_params {
+    float x_min, x_max, y_min, y_max, z_min, z_max;
+    float x_div, y_div, z_div;
+    int xn, yn, zn;
+} mv3d_top_params;
+
+/* The 9 trailing floats of createTopAndFrontMaps, in the reference's argument order. */
+typedef struct mv3d_front_params {
+    float phi_min, phi_max, theta_min, theta_max; /* dead parameters in the reference, kept for symmetry */
+    float phi_div, theta_div;
+    float c_size, r_size, f_size;
+} mv3d_front_params;
+
+/* Which reference routine's arithmetic to reproduce. They differ in the density channel
+ * (truncation keeps points with z in (z_MIN - z_DIV, z_MIN); floor rejects them). */
+enum {
+    MV3D_SEM_TOP = 0,      /* createTopMaps:          (int)((p - MIN) / DIV)        LidarTopPreprocess.c:107-109 */
+    MV3D_SEM_TOPFRONT = 1  /* createTopAndFrontMaps:  (int)floor((p - MIN) / DIV)   LidarTopAndFrontPreprocess.c:124-126 */
+};
+
+/* Per-cell reduction strategy for the bird's-eye view. */
+enum {
+    MV3D_STRATEGY_AUTO = 0,
+    MV3D_STRATEGY_ATOMIC = 1, /* zero-fill, then order-preserving integer atomics straight into the output in HBM/L2 */
+    MV3D_STRATEGY_TILE = 2    /* bin points by output tile, reduce in shared memory, one bulk (TMA) store per tile */
+};
+
+typedef struct mv3d_ctx mv3d_ctx;
+
+/* Creates a per-GPU context (workspace grows on demand, density table, stream pool). 0 on success. */
+int mv3d_ctx_create(int device, mv3d_ctx **out);
+void mv3d_ctx_destroy(mv3d_ctx *ctx);
+
+/* Encodes `batch` sweeps that are already resident in device memory.
+ *   points_dev   : device, total x 4 float32, 16-byte aligned; sweep i is rows [offsets[i], offsets[i+1])
+ *   offsets_host : host, batch+1 ints, non-decreasing, offsets[0] >= 0
+ *   top_dev      : device, batch x [xn][yn][zn+2] float32, or NULL to skip the bird's-eye view
+ *   front_dev    : device, batch x [R][C][F] float32, or NULL to skip the front view (fp may then be NULL)
+ *   stream       : a cudaStream_t (NULL = legacy default stream). The call only enqueues work.
+ * Returns 0 on success. */
+int mv3d_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *offsets_host, int batch,
+                          float *top_dev, float *front_dev,
+                          const mv3d_top_params *tp, const mv3d_front_params *fp,
+                          int semantics, int strategy, void *stream);
+
+/* Same, with host buffers: host->device copy, encode, device->host copy, pipelined frame by frame over
+ * internal streams; returns after the outputs are complete in host memory. Pinned (page-locked) host
+ * buffers (mv3d_host_alloc) are DMA'd directly; pageable ones go through the driver's staging path. */
+int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, const int *offsets_host, int batch,
+                           float *top_host, float *front_host,
+                           const mv3d_top_params *tp, const mv3d_front_params *fp,
+                           int semantics, int strategy);
+
+/* Page-locked host memory for the buffers above (NULL on failure). */
+void *mv3d_host_alloc(size_t bytes);
+void mv3d_host_free(void *p);
+
+/* Kernels launched by this context so far (bench.py's gpu_launches). */
+long long mv3d_ctx_launch_count(const mv3d_ctx *ctx);
+
+/* The strategy MV3D_STRATEGY_AUTO resolves to for a parameter set (MV3D_STRATEGY_ATOMIC or _TILE). */
+int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy);
+
+/* Library / build identification, e.g. "mv3d_encode 0.1 sm_100a". */
+const char *mv3d_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MV3D_ENCODE_H */

@@ -1,0 +1,111 @@
+"""Build and load libmv3d_encode.so (the C-ABI library declared in include/mv3d_encode.h).
+
+The library is compiled in-tree with nvcc for sm_100a only. There is no Python or CPU implementation
+behind it: if it cannot be built or loaded, importing callers get an exception, not a fallback.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import shutil
+import subprocess
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(_HERE, "csrc")
+LIB_PATH = os.path.join(_HERE, "libmv3d_encode.so")
+SOURCES = ["encode_kernels.cu", "mv3d_abi.cu"]
+HEADERS = ["encode_kernels.h", "view_math.cuh", os.path.join("..", "..", "include", "mv3d_encode.h")]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
+              "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), shutil.which("nvcc"), "/usr/local/cuda/bin/nvcc"):
+        if cand and os.path.exists(cand):
+            return cand
+    raise RuntimeError("nvcc not found: libmv3d_encode.so cannot be built (set NVCC=/path/to/nvcc)")
+
+
+def _stale() -> bool:
+    if not os.path.exists(LIB_PATH):
+        return True
+    built = os.path.getmtime(LIB_PATH)
+    deps = [os.path.join(CSRC, f) for f in SOURCES + HEADERS]
+    return any(os.path.exists(d) and os.path.getmtime(d) > built for d in deps)
+
+
+def build_library(force: bool = False, verbose: bool = False) -> str:
+    """Compile csrc/*.cu into mv3d_b200/libmv3d_encode.so for sm_100a (nvcc cross-compiles without a GPU)."""
+    if not force and not _stale():
+        return LIB_PATH
+    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH] + [os.path.join(CSRC, s) for s in SOURCES]
+    if verbose:
+        cmd.insert(1, "-Xptxas=-v")
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    if res.returncode != 0:
+        raise RuntimeError("nvcc failed:\n" + " ".join(cmd) + "\n" + res.stdout + res.stderr)
+    if verbose:
+        print(res.stderr)
+    return LIB_PATH
+
+
+class TopParamsC(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_float) for n in
+                ("x_min", "x_max", "y_min", "y_max", "z_min", "z_max", "x_div", "y_div", "z_div")] + \
+               [(n, ctypes.c_int) for n in ("xn", "yn", "zn")]
+
+
+class FrontParamsC(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_float) for n in
+                ("phi_min", "phi_max", "theta_min", "theta_max", "phi_div", "theta_div", "c_size", "r_size", "f_size")]
+
+
+SEM_TOP, SEM_TOPFRONT = 0, 1
+STRATEGY_AUTO, STRATEGY_ATOMIC, STRATEGY_TILE = 0, 1, 2
+STRATEGIES = {"auto": STRATEGY_AUTO, "atomic": STRATEGY_ATOMIC, "tile": STRATEGY_TILE}
+
+# Every symbol include/mv3d_encode.h declares (tests check the built library exports exactly these).
+EXPORTED_SYMBOLS = (
+    "createTopMaps", "createTopAndFrontMaps", "mv3d_last_error", "mv3d_ctx_create", "mv3d_ctx_destroy",
+    "mv3d_encode_batch_dev", "mv3d_encode_batch_host", "mv3d_host_alloc", "mv3d_host_free",
+    "mv3d_ctx_launch_count", "mv3d_resolve_strategy", "mv3d_version",
+)
+
+_lib = None
+
+
+def load_library() -> ctypes.CDLL:
+    """Load (building first if the sources are newer) and type the C ABI."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if _stale():
+        build_library()
+    lib = ctypes.CDLL(LIB_PATH)
+    cf, ci, vp = ctypes.c_float, ctypes.c_int, ctypes.c_void_p
+    lib.createTopMaps.argtypes = [vp, ci, vp] + [cf] * 9 + [ci] * 3
+    lib.createTopMaps.restype = None
+    lib.createTopAndFrontMaps.argtypes = [vp, ci, vp, vp] + [cf] * 9 + [ci] * 3 + [cf] * 9
+    lib.createTopAndFrontMaps.restype = None
+    lib.mv3d_last_error.restype = ctypes.c_char_p
+    lib.mv3d_version.restype = ctypes.c_char_p
+    lib.mv3d_ctx_create.argtypes = [ci, ctypes.POINTER(vp)]
+    lib.mv3d_ctx_destroy.argtypes = [vp]
+    lib.mv3d_ctx_destroy.restype = None
+    lib.mv3d_encode_batch_dev.argtypes = [vp, vp, ctypes.POINTER(ci), ci, vp, vp,
+                                          ctypes.POINTER(TopParamsC), ctypes.POINTER(FrontParamsC), ci, ci, vp]
+    lib.mv3d_encode_batch_host.argtypes = [vp, vp, ctypes.POINTER(ci), ci, vp, vp,
+                                           ctypes.POINTER(TopParamsC), ctypes.POINTER(FrontParamsC), ci, ci]
+    lib.mv3d_host_alloc.argtypes = [ctypes.c_size_t]
+    lib.mv3d_host_alloc.restype = vp
+    lib.mv3d_host_free.argtypes = [vp]
+    lib.mv3d_host_free.restype = None
+    lib.mv3d_ctx_launch_count.argtypes = [vp]
+    lib.mv3d_ctx_launch_count.restype = ctypes.c_longlong
+    lib.mv3d_resolve_strategy.argtypes = [vp, ctypes.POINTER(TopParamsC), ci]
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load_library().mv3d_last_error().decode("utf-8", "replace")

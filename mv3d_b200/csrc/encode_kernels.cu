@@ -1,0 +1,492 @@
+// encode_kernels.cu -- sm_100a kernels of the LiDAR view encoder and their launchers.
+//
+// Two strategies for the per-cell reduction of the bird's-eye view (BEV), chosen per parameter set:
+//
+//  TILE (default)  classify -> scan -> bin -> tile_build
+//      The output [X][Y][Z+2] is cell-major, so any run of consecutive cells is one contiguous chunk of
+//      memory. Points are binned by output tile (a counting sort keyed on tile id; the rank inside the bin
+//      comes from the same atomic that builds the histogram). One CTA then owns one tile at a time: it
+//      reduces the tile's points in shared memory with order-preserving integer atomics, finalises the
+//      touched cells in place, and writes the tile -- zeros included -- with ONE bulk async (TMA) store.
+//      Every output byte is written exactly once and never read; HBM traffic = the algorithmic bytes.
+//
+//  ATOMIC          fill_zero -> atomic_scatter -> atomic_finalize
+//      Zero-fill the output, reduce with global atomics straight into the output cells (tagged raw values),
+//      then a second pass over the points converts the touched slots. No binning; relies on L2 atomics.
+//
+// The front view (FV) is a per-pixel "last point in input order wins" image: classify/scatter records the
+// winning point index per pixel with atomicMax, front_finalize recomputes the three channel values from the
+// winner and writes the whole image (zeros included) once.
+#include "encode_kernels.h"
+#include "view_math.cuh"
+
+namespace mv3d {
+
+constexpr int kPointThreads = 256;
+constexpr int kTileThreads = 256;
+constexpr int kZeroChunkBytes = 8192;  // shared all-zero source for empty tiles (multiple of 16)
+
+// ------------------------------------------------------------------------------------------------
+// small PTX wrappers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_addr(const void *p)
+{
+    return (uint32_t)__cvta_generic_to_shared(p);
+}
+// Make generic-proxy writes to shared memory visible to the async proxy (TMA) before a bulk store reads them.
+__device__ __forceinline__ void fence_proxy_async_smem()
+{
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+// Bulk async copy shared -> global (TMA, non-tensor form). bytes % 16 == 0, both addresses 16-byte aligned.
+__device__ __forceinline__ void bulk_store(void *gdst, const void *ssrc, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
+                 :: "l"(gdst), "r"(smem_addr(ssrc)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit()
+{
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+// Wait until all committed bulk stores of this thread have finished READING shared memory.
+__device__ __forceinline__ void bulk_wait_read_all()
+{
+    asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void store_zero16(float4 *p)
+{
+    asm volatile("st.global.cs.v4.f32 [%0], {%1,%1,%1,%1};" :: "l"(p), "f"(0.0f) : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------
+// TILE strategy, pass 1: classify every point, histogram tiles, elect front-view winners.
+//   keys[g] = {output cell, rank inside its tile's bin}  ({kInvalidKey, 0} when the point is rejected)
+// grid = (blocks, batch); each CTA strides over one sweep's points with coalesced 16-byte loads.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kPointThreads)
+classify_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
+                uint2 *__restrict__ keys, unsigned *__restrict__ tile_count, unsigned *__restrict__ fv_winner)
+{
+    const int f = blockIdx.y;
+    const int base = offs.off[f];
+    const int n = offs.off[f + 1] - base;
+    const unsigned lane = threadIdx.x & 31u;
+    unsigned *counts = tile_count + (size_t)f * (p.tiles_per_frame + 1);
+    unsigned *winners = fv_winner + (size_t)f * p.front_pixels;
+
+    // warp-uniform trip count so the match/shuffle below is convergent
+    const int stride = gridDim.x * blockDim.x;
+    const int first = blockIdx.x * blockDim.x + threadIdx.x;
+    const int warp_first = first - (int)lane;
+    for (int i0 = warp_first; i0 < n; i0 += stride) {
+        const int i = i0 + (int)lane;
+        uint32_t cell = kInvalidKey;
+        uint32_t tile = kInvalidKey;
+        if (i < n) {
+            const float4 pt = load_point(pts + base + i);
+            const CellHit c = classify(pt, p);
+            if (c.keep) {
+                cell = c.cell;
+                if (p.want_front) {
+                    const int pix = front_pixel(pt, p);
+                    if (pix >= 0) atomicMax(winners + pix, (unsigned)i + 1u);
+                }
+            }
+        }
+        if (p.want_top) {
+            if (cell != kInvalidKey) tile = cell / (uint32_t)p.tile_cells;
+            // Warp-aggregated histogram: lanes that hit the same tile share one atomicAdd.
+            const unsigned peers = __match_any_sync(0xFFFFFFFFu, tile);
+            const int leader = __ffs(peers) - 1;
+            unsigned rank = 0;
+            if (tile != kInvalidKey && (int)lane == leader) rank = atomicAdd(counts + tile, (unsigned)__popc(peers));
+            rank = __shfl_sync(0xFFFFFFFFu, rank, leader);
+            rank += (unsigned)__popc(peers & ((1u << lane) - 1u));
+            if (i < n) keys[base + i] = make_uint2(cell, rank);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// TILE strategy, pass 2: exclusive scan of one sweep's tile histogram (one CTA per sweep).
+// Writes tiles_per_frame+1 offsets and clears the histogram for the next call (self-cleaning workspace).
+// ------------------------------------------------------------------------------------------------
+constexpr int kScanThreads = 1024;
+__global__ void __launch_bounds__(kScanThreads)
+tile_scan_kernel(unsigned *__restrict__ tile_count, unsigned *__restrict__ tile_off, int tiles_per_frame)
+{
+    __shared__ unsigned warp_sums[kScanThreads / 32];
+    __shared__ unsigned carry;
+    unsigned *cnt = tile_count + (size_t)blockIdx.x * (tiles_per_frame + 1);
+    unsigned *off = tile_off + (size_t)blockIdx.x * (tiles_per_frame + 1);
+    const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (int t0 = 0; t0 < tiles_per_frame; t0 += kScanThreads) {
+        const int t = t0 + threadIdx.x;
+        unsigned v = 0;
+        if (t < tiles_per_frame) { v = cnt[t]; cnt[t] = 0; }
+        unsigned incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const unsigned up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
+            if ((int)lane >= d) incl += up;
+        }
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            unsigned w = warp_sums[lane];
+            unsigned wincl = w;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const unsigned up = __shfl_up_sync(0xFFFFFFFFu, wincl, d);
+                if ((int)lane >= d) wincl += up;
+            }
+            warp_sums[lane] = wincl - w;  // exclusive prefix of the warp totals
+        }
+        __syncthreads();
+        const unsigned excl = carry + warp_sums[warp] + incl - v;
+        if (t < tiles_per_frame) off[t] = excl;
+        __syncthreads();
+        if (threadIdx.x == kScanThreads - 1) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) off[tiles_per_frame] = carry;
+}
+
+// ------------------------------------------------------------------------------------------------
+// TILE strategy, pass 3: move each kept point's record into its tile's bin.
+//   record = { cell-in-tile | slice << 16,  h bits,  point index,  intensity bits }   (16 bytes)
+// Order inside a bin is arbitrary; every order-dependent decision uses the point index carried along.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kPointThreads)
+bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
+           const uint2 *__restrict__ keys, const unsigned *__restrict__ tile_off, uint4 *__restrict__ binned)
+{
+    const int f = blockIdx.y;
+    const int base = offs.off[f];
+    const int n = offs.off[f + 1] - base;
+    const unsigned *off = tile_off + (size_t)f * (p.tiles_per_frame + 1);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint2 k = keys[base + i];
+        if (k.x == kInvalidKey) continue;
+        const float4 pt = load_point(pts + base + i);
+        const uint32_t tile = k.x / (uint32_t)p.tile_cells;
+        const uint32_t local = k.x - tile * (uint32_t)p.tile_cells;
+        const int Z = quantise(pt.z, p.z_min, p.z_div, p.quant_floor);
+        const float h = __fsub_rn(pt.z, p.z_min);
+        binned[(size_t)base + off[tile] + k.y] =
+            make_uint4(local | ((uint32_t)Z << 16), __float_as_uint(h), (uint32_t)i, __float_as_uint(pt.w));
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// TILE strategy, pass 4: build and store output tiles. Persistent CTAs, tile t -> CTA t mod grid.
+//
+// Shared memory per CTA: the tile image (tile_cells * planes words, kept all-zero between tiles), one
+// 64-bit (h, ~index) key per cell, and the list of cells touched by the current tile.
+//   accumulate : slot[k] = max h bits (h > 0 orders like an unsigned int); count++ in the density slot;
+//                key = max (h, ~index) -> highest point, earliest in input order on ties
+//   finalise   : touched cells only -- heights to h/z_DIV - k, count to the libm-built density table,
+//                intensity of the key's winner
+//   store      : one cp.async.bulk shared->global for the whole tile (plain stores if misaligned)
+//   clean      : re-zero only the touched cells, after the bulk store has finished reading
+// Empty tiles (the majority) skip everything but the store, straight from the all-zero image.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kTileThreads)
+tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
+                  ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int T = p.tile_cells;
+    const int planes = p.planes;
+    const int zn = p.zn;
+    unsigned *img = reinterpret_cast<unsigned *>(smem_raw);
+    const size_t img_bytes = ((size_t)T * planes * 4 + 15) & ~(size_t)15;
+    unsigned long long *key = reinterpret_cast<unsigned long long *>(smem_raw + img_bytes);
+    unsigned *dirty = reinterpret_cast<unsigned *>(key + T);
+    // Never-modified zeros: empty tiles are stored from here, so their in-flight bulk reads can never
+    // overlap a later tile's accumulation into the image.
+    __shared__ __align__(128) unsigned zeros[kZeroChunkBytes / 4];
+    __shared__ unsigned ndirty;
+
+    for (int w = threadIdx.x; w < T * planes; w += blockDim.x) img[w] = 0u;
+    for (int w = threadIdx.x; w < T; w += blockDim.x) key[w] = 0ull;
+    for (int w = threadIdx.x; w < kZeroChunkBytes / 4; w += blockDim.x) zeros[w] = 0u;
+    if (threadIdx.x == 0) ndirty = 0;
+    fence_proxy_async_smem();
+    __syncthreads();
+
+    const long long cells_total = (long long)p.xn * p.yn;
+    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+        const int f = t / p.tiles_per_frame;
+        const int tl = t - f * p.tiles_per_frame;
+        const long long cell0 = (long long)tl * T;
+        const int ncell = (int)min((long long)T, cells_total - cell0);
+        const uint32_t bytes = (uint32_t)ncell * (uint32_t)planes * 4u;
+        float *dst = top + (size_t)f * p.top_frame_floats + (size_t)cell0 * planes;
+        const bool bulk = ((reinterpret_cast<uintptr_t>(dst) | (uintptr_t)bytes) & 15u) == 0;
+        const unsigned *off = tile_off + (size_t)f * (p.tiles_per_frame + 1) + tl;
+        const unsigned beg = off[0];
+        const int n = (int)(off[1] - beg);
+
+        if (n == 0) {  // empty tile: stream zeros, no synchronisation needed (the image is not modified)
+            if (bulk) {
+                if (threadIdx.x == 0) {
+                    for (uint32_t b = 0; b < bytes; b += kZeroChunkBytes)
+                        bulk_store(reinterpret_cast<unsigned char *>(dst) + b, zeros, min(bytes - b, (uint32_t)kZeroChunkBytes));
+                    bulk_commit();
+                }
+            } else {
+                for (int w = threadIdx.x; w < ncell * planes; w += blockDim.x) dst[w] = 0.0f;
+            }
+            continue;
+        }
+
+        const uint4 *rec = binned + (size_t)offs.off[f] + beg;
+        for (int r = threadIdx.x; r < n; r += blockDim.x) {
+            const uint4 q = __ldg(rec + r);
+            const unsigned local = q.x & 0xFFFFu, Z = q.x >> 16;
+            unsigned *cellw = img + local * planes;
+            if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(&ndirty, 1u)] = local;
+            if ((int)q.y > 0) {  // h > 0: the reference's maps start at 0 and update on strict '>'
+                atomicMax(cellw + Z, q.y);
+                atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
+            }
+        }
+        __syncthreads();
+
+        const int nd = (int)ndirty;
+        for (int r = threadIdx.x; r < n; r += blockDim.x) {  // intensity of the cell's winner
+            const uint4 q = __ldg(rec + r);
+            const unsigned local = q.x & 0xFFFFu;
+            if ((int)q.y > 0 &&
+                key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z)))
+                img[local * planes + zn] = q.w;
+        }
+        for (int w = threadIdx.x; w < nd * planes; w += blockDim.x) {
+            const int d = w / planes, k = w - d * planes;
+            unsigned *slot = img + dirty[d] * planes + k;
+            if (k < zn) {
+                const unsigned raw = *slot;
+                if (raw) *slot = __float_as_uint(slice_value(__uint_as_float(raw), p.z_div, k));
+            } else if (k == zn + 1) {
+                const unsigned c = *slot;
+                *slot = __float_as_uint(__ldg(lut + (c < 31u ? c : 31u)));
+            }
+        }
+        fence_proxy_async_smem();
+        __syncthreads();
+
+        if (bulk) {
+            if (threadIdx.x == 0) { bulk_store(dst, img, bytes); bulk_commit(); bulk_wait_read_all(); }
+        } else {
+            for (int w = threadIdx.x; w < ncell * planes; w += blockDim.x) dst[w] = __uint_as_float(img[w]);
+        }
+        __syncthreads();
+
+        for (int w = threadIdx.x; w < nd * planes; w += blockDim.x) {
+            const int d = w / planes, k = w - d * planes;
+            img[dirty[d] * planes + k] = 0u;
+        }
+        for (int d = threadIdx.x; d < nd; d += blockDim.x) key[dirty[d]] = 0ull;
+        if (threadIdx.x == 0) ndirty = 0;
+        fence_proxy_async_smem();
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
+}
+
+// ------------------------------------------------------------------------------------------------
+// Front view: write the whole [R][C][F] image from the per-pixel winners, and clear the winners.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kPointThreads)
+front_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
+                      unsigned *__restrict__ fv_winner, float *__restrict__ front)
+{
+    const int f = blockIdx.y;
+    unsigned *winners = fv_winner + (size_t)f * p.front_pixels;
+    float *out = front + (size_t)f * p.front_frame_floats;
+    for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < p.front_pixels; pix += gridDim.x * blockDim.x) {
+        const unsigned w = winners[pix];
+        float v0 = 0.0f, v1 = 0.0f, v2 = 0.0f;
+        if (w) {
+            winners[pix] = 0u;
+            const float4 pt = pts[offs.off[f] + (int)(w - 1u)];
+            front_values(pt, p, v0, v1, v2);
+        }
+        float *o = out + (size_t)pix * p.fn;
+        o[0] = v0; o[1] = v1; o[2] = v2;
+        for (int c = 3; c < p.fn; c++) o[c] = 0.0f;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// ATOMIC strategy
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) fill_zero_kernel(float *__restrict__ dst, size_t count)
+{
+    // head (to 16-byte alignment), vector body, tail
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(dst);
+    size_t head = ((16 - (addr & 15)) & 15) / 4;
+    if (head > count) head = count;
+    const size_t body = (count - head) / 4;
+    float4 *v = reinterpret_cast<float4 *>(dst + head);
+    const size_t tid = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t nthreads = (size_t)gridDim.x * blockDim.x;
+    for (size_t i = tid; i < body; i += nthreads) store_zero16(v + i);
+    if (tid < head) dst[tid] = 0.0f;
+    const size_t tail0 = head + body * 4;
+    if (tid < count - tail0) dst[tail0 + tid] = 0.0f;
+}
+
+// Pass 1: reduce straight into the (zeroed) output. Height slots hold kRawTag | h bits until finalised,
+// the density slot holds the raw count, cellkey holds the (h, ~index) winner key.
+__global__ void __launch_bounds__(kPointThreads)
+atomic_scatter_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
+                      float *__restrict__ top, unsigned long long *__restrict__ cellkey,
+                      unsigned *__restrict__ fv_winner)
+{
+    const int f = blockIdx.y;
+    const int base = offs.off[f];
+    const int n = offs.off[f + 1] - base;
+    unsigned *out = reinterpret_cast<unsigned *>(top + (size_t)f * p.top_frame_floats);
+    unsigned long long *keys = cellkey + (size_t)f * ((size_t)p.xn * p.yn);
+    unsigned *winners = fv_winner + (size_t)f * p.front_pixels;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 pt = load_point(pts + base + i);
+        const CellHit c = classify(pt, p);
+        if (!c.keep) continue;
+        if (p.want_top) {
+            unsigned *cellw = out + (size_t)c.cell * p.planes;
+            atomicAdd(cellw + p.zn + 1, 1u);
+            if (c.h > 0.0f) {
+                atomicMax(cellw + c.slice, __float_as_uint(c.h) | kRawTag);
+                atomicMax(keys + c.cell, cell_key(c.h, (uint32_t)i));
+            }
+        }
+        if (p.want_front) {
+            const int pix = front_pixel(pt, p);
+            if (pix >= 0) atomicMax(winners + pix, (unsigned)i + 1u);
+        }
+    }
+}
+
+// Pass 2: every kept point revisits its cell. The slot winner (tagged value == its own) converts the height;
+// the key winner writes the intensity; anyone who still sees a raw count converts it.
+// Raw counts (< 2^30) and density floats (>= 0.2f = 0x3E4CCCCD) cannot be confused, and all writers of one
+// density slot write the same value, so the race between them is benign.
+__global__ void __launch_bounds__(kPointThreads)
+atomic_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p, const float *__restrict__ lut,
+                       float *__restrict__ top, unsigned long long *__restrict__ cellkey)
+{
+    const int f = blockIdx.y;
+    const int base = offs.off[f];
+    const int n = offs.off[f + 1] - base;
+    unsigned *out = reinterpret_cast<unsigned *>(top + (size_t)f * p.top_frame_floats);
+    unsigned long long *keys = cellkey + (size_t)f * ((size_t)p.xn * p.yn);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 pt = load_point(pts + base + i);
+        const CellHit c = classify(pt, p);
+        if (!c.keep) continue;
+        unsigned *cellw = out + (size_t)c.cell * p.planes;
+        const unsigned cnt = *reinterpret_cast<volatile unsigned *>(cellw + p.zn + 1);
+        if (cnt < 0x3E000000u) cellw[p.zn + 1] = __float_as_uint(__ldg(lut + (cnt < 31u ? cnt : 31u)));
+        if (c.h > 0.0f) {
+            const unsigned mine = __float_as_uint(c.h) | kRawTag;
+            if (*reinterpret_cast<volatile unsigned *>(cellw + c.slice) == mine)
+                cellw[c.slice] = __float_as_uint(slice_value(c.h, p.z_div, c.slice));
+            if (keys[c.cell] == cell_key(c.h, (uint32_t)i)) cellw[p.zn] = __float_as_uint(pt.w);
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// launchers
+// ------------------------------------------------------------------------------------------------
+static inline int point_blocks(int max_points)
+{
+    int b = (max_points + kPointThreads - 1) / kPointThreads;
+    return b < 1 ? 1 : (b > 4096 ? 4096 : b);
+}
+
+size_t tile_smem_bytes(const ViewParams &p)
+{
+    const size_t img = ((size_t)p.tile_cells * p.planes * 4 + 15) & ~(size_t)15;
+    return img + (size_t)p.tile_cells * 8 + (size_t)p.tile_cells * 4;
+}
+
+cudaError_t tile_build_configure(const ViewParams &p, int *blocks_per_sm)
+{
+    const size_t smem = tile_smem_bytes(p);
+    cudaError_t e = cudaFuncSetAttribute(tile_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, tile_build_kernel, kTileThreads, smem);
+}
+
+int launch_classify(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
+                    uint2 *keys, unsigned *tile_count, unsigned *fv_winner, cudaStream_t s)
+{
+    dim3 grid(point_blocks(max_points), batch);
+    classify_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_count, fv_winner);
+    return 1;
+}
+
+int launch_tile_scan(unsigned *tile_count, unsigned *tile_off, int tiles_per_frame, int batch, cudaStream_t s)
+{
+    tile_scan_kernel<<<batch, kScanThreads, 0, s>>>(tile_count, tile_off, tiles_per_frame);
+    return 1;
+}
+
+int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
+               const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s)
+{
+    dim3 grid(point_blocks(max_points), batch);
+    bin_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_off, binned);
+    return 1;
+}
+
+int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
+                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s)
+{
+    const int total = batch * p.tiles_per_frame;
+    const int grid = grid_blocks < total ? grid_blocks : total;
+    tile_build_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
+    return 1;
+}
+
+int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch,
+                          unsigned *fv_winner, float *front, cudaStream_t s)
+{
+    dim3 grid(point_blocks(p.front_pixels), batch);
+    front_finalize_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, fv_winner, front);
+    return 1;
+}
+
+int launch_fill_zero(float *dst, size_t count, int sm_count, cudaStream_t s)
+{
+    if (count == 0) return 0;
+    size_t want = (count / 4 + 255) / 256;
+    const size_t cap = (size_t)sm_count * 16;
+    int blocks = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+    fill_zero_kernel<<<blocks, 256, 0, s>>>(dst, count);
+    return 1;
+}
+
+int launch_atomic_scatter(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
+                          float *top, unsigned long long *cellkey, unsigned *fv_winner, cudaStream_t s)
+{
+    dim3 grid(point_blocks(max_points), batch);
+    atomic_scatter_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, top, cellkey, fv_winner);
+    return 1;
+}
+
+int launch_atomic_finalize(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const float *lut,
+                           int batch, int max_points, float *top, unsigned long long *cellkey, cudaStream_t s)
+{
+    dim3 grid(point_blocks(max_points), batch);
+    atomic_finalize_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, lut, top, cellkey);
+    return 1;
+}
+
+} // namespace mv3d

@@ -1,0 +1,31 @@
+// encode_kernels.h -- launchers of the view-encoder kernels (internal; the public ABI is include/mv3d_encode.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stddef.h>
+#include <stdint.h>
+
+namespace mv3d {
+
+struct ViewParams;
+struct FrameOffsets;
+
+// Each launcher enqueues on `s` and returns the number of kernels it launched.
+size_t tile_smem_bytes(const ViewParams &p);
+cudaError_t tile_build_configure(const ViewParams &p, int *blocks_per_sm);
+
+int launch_classify(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
+                    uint2 *keys, unsigned *tile_count, unsigned *fv_winner, cudaStream_t s);
+int launch_tile_scan(unsigned *tile_count, unsigned *tile_off, int tiles_per_frame, int batch, cudaStream_t s);
+int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
+               const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s);
+int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
+                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
+int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch,
+                          unsigned *fv_winner, float *front, cudaStream_t s);
+int launch_fill_zero(float *dst, size_t count, int sm_count, cudaStream_t s);
+int launch_atomic_scatter(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
+                          float *top, unsigned long long *cellkey, unsigned *fv_winner, cudaStream_t s);
+int launch_atomic_finalize(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const float *lut,
+                           int batch, int max_points, float *top, unsigned long long *cellkey, cudaStream_t s);
+
+} // namespace mv3d

@@ -1,0 +1,492 @@
+// mv3d_abi.cu -- the C ABI of libmv3d_encode.so (include/mv3d_encode.h): context, workspace, the batched
+// device entry point, the pipelined host entry point, and the two reference symbols
+// createTopMaps / createTopAndFrontMaps (ver3/LidarTopPreprocess.c:30, ver3/LidarTopAndFrontPreprocess.c:30).
+//
+// There is no CPU implementation in this library: every path ends in the sm_100a kernels of
+// encode_kernels.cu, and every failure is reported through mv3d_last_error().
+#include "../../include/mv3d_encode.h"
+#include "encode_kernels.h"
+#include "view_math.cuh"
+
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+
+using namespace mv3d;
+
+// ------------------------------------------------------------------------------------------------
+// error reporting
+// ------------------------------------------------------------------------------------------------
+static thread_local char g_error[512] = "";
+
+static int fail(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+    return -1;
+}
+
+#define CUDA_TRY(expr)                                                                              \
+    do {                                                                                            \
+        cudaError_t _e = (expr);                                                                    \
+        if (_e != cudaSuccess)                                                                      \
+            return fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
+    } while (0)
+
+extern "C" const char *mv3d_last_error(void) { return g_error; }
+extern "C" const char *mv3d_version(void) { return "mv3d_encode 0.1 sm_100a"; }
+
+// ------------------------------------------------------------------------------------------------
+// context
+// ------------------------------------------------------------------------------------------------
+namespace {
+
+struct DeviceBuffer {
+    void *ptr = nullptr;
+    size_t bytes = 0;
+};
+
+// Scratch for one in-flight encode call. Zero-initialised where the kernels rely on it (tile histogram,
+// front-view winners) and left zero by them, so no per-call memset is needed on the tile path.
+struct Workspace {
+    DeviceBuffer keys, binned, tile_count, tile_off, fv_winner, cellkey;
+};
+
+constexpr int kSlots = 3;  // host pipeline depth: copy-in / encode / copy-out of consecutive sweeps overlap
+
+struct HostSlot {
+    cudaStream_t stream = nullptr;
+    Workspace ws;
+    DeviceBuffer points, top, front;
+};
+
+} // namespace
+
+struct mv3d_ctx {
+    int device = 0;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+    float *lut = nullptr;
+    Workspace ws;            // used by mv3d_encode_batch_dev (one call in flight per context)
+    HostSlot slots[kSlots];  // used by mv3d_encode_batch_host
+    long long launches = 0;
+    size_t tile_bytes_target = 0;
+    std::mutex mu;
+};
+
+static int ensure(DeviceBuffer &b, size_t bytes, bool zero, cudaStream_t s)
+{
+    if (bytes <= b.bytes) return 0;
+    // Growing is rare (first call / larger batch); make sure nothing still uses the old allocation.
+    CUDA_TRY(cudaStreamSynchronize(s));
+    if (b.ptr) CUDA_TRY(cudaFree(b.ptr));
+    b.ptr = nullptr;
+    b.bytes = 0;
+    size_t want = bytes + bytes / 8;
+    want = (want + 255) & ~(size_t)255;
+    CUDA_TRY(cudaMalloc(&b.ptr, want));
+    b.bytes = want;
+    if (zero) {
+        CUDA_TRY(cudaMemsetAsync(b.ptr, 0, want, s));
+        CUDA_TRY(cudaStreamSynchronize(s));
+    }
+    return 0;
+}
+
+static void release(DeviceBuffer &b)
+{
+    if (b.ptr) cudaFree(b.ptr);
+    b.ptr = nullptr;
+    b.bytes = 0;
+}
+
+static void release(Workspace &w)
+{
+    release(w.keys); release(w.binned); release(w.tile_count); release(w.tile_off);
+    release(w.fv_winner); release(w.cellkey);
+}
+
+static void build_density_lut(float *v)
+{
+    // Same type mix as the reference (LidarTopPreprocess.c:167): logf on a float argument, double log(32),
+    // quotient in double, narrowed to float, clamped to 1 -- evaluated by this host's libm at run time.
+    for (int c = 0; c < kDensityLutSize; c++) {
+        volatile float arg = (float)c + 1.0f;
+        volatile double base = 32.0;
+        const float val = (float)((double)logf(arg) / log(base));
+        v[c] = (val < 1.0f) ? val : 1.0f;
+    }
+}
+
+extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
+{
+    if (!out) return fail("mv3d_ctx_create: out is NULL");
+    *out = nullptr;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0)
+        return fail("mv3d_ctx_create: no CUDA device (%s); this library has no CPU fallback",
+                    e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= count) return fail("mv3d_ctx_create: device %d out of range [0,%d)", device, count);
+    CUDA_TRY(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10)
+        return fail("mv3d_ctx_create: device %d is sm_%d%d; this library is built for sm_100a only", device,
+                    prop.major, prop.minor);
+    mv3d_ctx *ctx = new (std::nothrow) mv3d_ctx();
+    if (!ctx) return fail("mv3d_ctx_create: out of host memory");
+    ctx->device = device;
+    ctx->sm_count = prop.multiProcessorCount;
+    ctx->smem_optin = prop.sharedMemPerBlockOptin;
+    const char *tb = getenv("MV3D_TILE_BYTES");
+    ctx->tile_bytes_target = tb ? (size_t)strtoull(tb, nullptr, 10) : (size_t)(44 * 1024);
+    float lut[kDensityLutSize];
+    build_density_lut(lut);
+    if (cudaMalloc(&ctx->lut, sizeof(lut)) != cudaSuccess ||
+        cudaMemcpy(ctx->lut, lut, sizeof(lut), cudaMemcpyHostToDevice) != cudaSuccess) {
+        fail("mv3d_ctx_create: cannot allocate the density table: %s", cudaGetErrorString(cudaGetLastError()));
+        delete ctx;
+        return -1;
+    }
+    *out = ctx;
+    return 0;
+}
+
+extern "C" void mv3d_ctx_destroy(mv3d_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    release(ctx->ws);
+    for (auto &s : ctx->slots) {
+        release(s.ws);
+        release(s.points); release(s.top); release(s.front);
+        if (s.stream) cudaStreamDestroy(s.stream);
+    }
+    if (ctx->lut) cudaFree(ctx->lut);
+    delete ctx;
+}
+
+extern "C" long long mv3d_ctx_launch_count(const mv3d_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" void *mv3d_host_alloc(size_t bytes)
+{
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) {
+        fail("mv3d_host_alloc(%zu): %s", bytes, cudaGetErrorString(cudaGetLastError()));
+        return nullptr;
+    }
+    return p;
+}
+
+extern "C" void mv3d_host_free(void *p)
+{
+    if (p) cudaFreeHost(p);
+}
+
+// ------------------------------------------------------------------------------------------------
+// parameter validation and kernel parameter block
+// ------------------------------------------------------------------------------------------------
+static bool integral(float v) { return std::isfinite(v) && v == std::floor(v); }
+
+// Tile size for a parameter set: as many whole cells as fit the target, a multiple of 4 cells so every
+// tile is a multiple of 16 bytes (bulk-store granularity) whatever the plane count.
+static int pick_tile_cells(const mv3d_ctx *ctx, int planes, long long cells)
+{
+    long long t = (long long)(ctx->tile_bytes_target / ((size_t)planes * 4));
+    t &= ~3LL;
+    if (t < 4) t = 4;
+    if (t > 65532) t = 65532;
+    const long long cells4 = (cells + 3) & ~3LL;
+    if (t > cells4) t = cells4;
+    return (int)t;
+}
+
+static bool tile_feasible(const mv3d_ctx *ctx, const mv3d_top_params *tp)
+{
+    if (!tp || tp->zn > 65535) return false;
+    const int planes = tp->zn + 2;
+    const int t = pick_tile_cells(ctx, planes, (long long)tp->xn * tp->yn);
+    const size_t smem = (((size_t)t * planes * 4 + 15) & ~(size_t)15) + (size_t)t * 12 + 8192 + 64;
+    return smem <= ctx->smem_optin;
+}
+
+extern "C" int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy)
+{
+    if (strategy == MV3D_STRATEGY_ATOMIC) return MV3D_STRATEGY_ATOMIC;
+    if (!ctx || !tp) return MV3D_STRATEGY_ATOMIC;
+    if (strategy == MV3D_STRATEGY_TILE || strategy == MV3D_STRATEGY_AUTO)
+        return tile_feasible(ctx, tp) ? MV3D_STRATEGY_TILE : MV3D_STRATEGY_ATOMIC;
+    return MV3D_STRATEGY_ATOMIC;
+}
+
+static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3d_front_params *fp, bool want_top,
+                       bool want_front, int semantics, ViewParams *out)
+{
+    if (!tp) return fail("top parameters are required (the front view is gated by the bird's-eye-view box)");
+    if (semantics != MV3D_SEM_TOP && semantics != MV3D_SEM_TOPFRONT) return fail("unknown semantics %d", semantics);
+    ViewParams p;
+    memset(&p, 0, sizeof(p));
+    if (tp->xn < 0 || tp->yn < 0 || tp->zn < 0) return fail("negative grid size %d x %d x %d", tp->xn, tp->yn, tp->zn);
+    const long long cells = (long long)tp->xn * tp->yn;
+    if (cells >= (1LL << 31) - 8) return fail("grid %d x %d has too many cells", tp->xn, tp->yn);
+    p.x_min = tp->x_min; p.y_min = tp->y_min; p.z_min = tp->z_min;
+    p.x_div = tp->x_div; p.y_div = tp->y_div; p.z_div = tp->z_div;
+    p.xn = tp->xn; p.yn = tp->yn; p.zn = tp->zn; p.planes = tp->zn + 2;
+    p.quant_floor = (semantics == MV3D_SEM_TOPFRONT) ? 1 : 0;
+    p.want_top = want_top ? 1 : 0;
+    p.want_front = want_front ? 1 : 0;
+    p.top_frame_floats = cells * p.planes;
+    p.tile_cells = pick_tile_cells(ctx, p.planes, cells);
+    p.tiles_per_frame = (int)((cells + p.tile_cells - 1) / p.tile_cells);
+    p.z_span = tp->z_max - tp->z_min;  // float subtraction, LidarTopAndFrontPreprocess.c:185
+    if (want_front) {
+        if (!fp) return fail("front parameters are required when a front view is requested");
+        if (!integral(fp->c_size) || !integral(fp->r_size) || !integral(fp->f_size) || fp->c_size < 1 ||
+            fp->r_size < 1 || fp->f_size < 3)
+            return fail("front view sizes must be integral with C,R >= 1 and F >= 3 (got C=%g R=%g F=%g)",
+                        fp->c_size, fp->r_size, fp->f_size);
+        const double len = (double)fp->c_size * fp->r_size * fp->f_size;
+        if (len >= 16777216.0) return fail("front view of %g floats exceeds the reference's exact float index range", len);
+        p.rad_to_deg = (float)(180 / 3.141596);  // sic, LidarTopAndFrontPreprocess.c:36
+        p.phi_div = fp->phi_div; p.theta_div = fp->theta_div;
+        p.r_size_f = fp->r_size; p.c_size_f = fp->c_size;
+        p.rn = (int)fp->r_size; p.cn = (int)fp->c_size; p.fn = (int)fp->f_size;
+        p.center_c = (int)(fp->c_size / 2);  // :37
+        p.center_r = (int)(fp->r_size / 2);  // :38
+        p.front_pixels = p.rn * p.cn;
+        p.front_frame_floats = (long long)p.front_pixels * p.fn;
+    }
+    *out = p;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// enqueue one chunk (<= kMaxBatchPerLaunch sweeps) on a stream
+// ------------------------------------------------------------------------------------------------
+static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
+                         float *top_dev, float *front_dev, const ViewParams &p, int strategy, cudaStream_t s)
+{
+    FrameOffsets offs;
+    memset(&offs, 0, sizeof(offs));
+    const int origin = offsets[0];
+    int max_points = 0;
+    for (int i = 0; i <= batch; i++) offs.off[i] = offsets[i] - origin;
+    for (int i = 0; i < batch; i++) {
+        const int n = offs.off[i + 1] - offs.off[i];
+        if (n > max_points) max_points = n;
+    }
+    const size_t total = (size_t)offs.off[batch];
+    const float4 *pts = reinterpret_cast<const float4 *>(points_dev) + origin;
+    const size_t cells = (size_t)p.xn * p.yn;
+
+    if (p.want_front) {
+        if (ensure(ws.fv_winner, (size_t)batch * p.front_pixels * 4, true, s)) return -1;
+    }
+    unsigned *winners = static_cast<unsigned *>(ws.fv_winner.ptr);
+
+    if (p.want_top && cells > 0 && strategy == MV3D_STRATEGY_TILE) {
+        if (ensure(ws.keys, total * sizeof(uint2) + 16, false, s)) return -1;
+        if (ensure(ws.binned, total * sizeof(uint4) + 16, false, s)) return -1;
+        const size_t hist = (size_t)batch * (p.tiles_per_frame + 1) * 4;
+        if (ensure(ws.tile_count, hist, true, s)) return -1;
+        if (ensure(ws.tile_off, hist, false, s)) return -1;
+        int blocks_per_sm = 0;
+        CUDA_TRY(tile_build_configure(p, &blocks_per_sm));
+        if (blocks_per_sm < 1) return fail("tile kernel does not fit: %zu bytes of shared memory", tile_smem_bytes(p));
+        ctx->launches += launch_classify(pts, offs, p, batch, max_points, static_cast<uint2 *>(ws.keys.ptr),
+                                         static_cast<unsigned *>(ws.tile_count.ptr), winners, s);
+        ctx->launches += launch_tile_scan(static_cast<unsigned *>(ws.tile_count.ptr),
+                                          static_cast<unsigned *>(ws.tile_off.ptr), p.tiles_per_frame, batch, s);
+        ctx->launches += launch_bin(pts, offs, p, batch, max_points, static_cast<const uint2 *>(ws.keys.ptr),
+                                    static_cast<const unsigned *>(ws.tile_off.ptr), static_cast<uint4 *>(ws.binned.ptr), s);
+        ctx->launches += launch_tile_build(static_cast<const uint4 *>(ws.binned.ptr),
+                                           static_cast<const unsigned *>(ws.tile_off.ptr), offs, p, ctx->lut, top_dev,
+                                           batch, blocks_per_sm * ctx->sm_count, s);
+    } else if (p.want_top && cells > 0) {
+        if (ensure(ws.cellkey, (size_t)batch * cells * 8, false, s)) return -1;
+        ctx->launches += launch_fill_zero(top_dev, (size_t)batch * (size_t)p.top_frame_floats, ctx->sm_count, s);
+        ctx->launches += launch_fill_zero(static_cast<float *>(ws.cellkey.ptr), (size_t)batch * cells * 2, ctx->sm_count, s);
+        ctx->launches += launch_atomic_scatter(pts, offs, p, batch, max_points, top_dev,
+                                               static_cast<unsigned long long *>(ws.cellkey.ptr), winners, s);
+        ctx->launches += launch_atomic_finalize(pts, offs, p, ctx->lut, batch, max_points, top_dev,
+                                                static_cast<unsigned long long *>(ws.cellkey.ptr), s);
+    } else if (p.want_front) {
+        // front view only: the classify pass alone elects the winners (BEV gate still applies)
+        ViewParams q = p;
+        q.want_top = 0;
+        ctx->launches += launch_classify(pts, offs, q, batch, max_points, nullptr, nullptr, winners, s);
+    }
+    if (p.want_front && p.front_pixels > 0)
+        ctx->launches += launch_front_finalize(pts, offs, p, batch, winners, front_dev, s);
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+static int check_offsets(const int *offsets, int batch)
+{
+    if (batch < 0) return fail("negative batch %d", batch);
+    if (!offsets) return fail("offsets is NULL");
+    if (offsets[0] < 0) return fail("offsets[0] = %d is negative", offsets[0]);
+    for (int i = 0; i < batch; i++) {
+        if (offsets[i + 1] < offsets[i]) return fail("offsets decrease at sweep %d (%d -> %d)", i, offsets[i], offsets[i + 1]);
+        if (offsets[i + 1] - offsets[i] > 1000000000) return fail("sweep %d has more than 1e9 points", i);
+    }
+    return 0;
+}
+
+static int encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
+                             float *top_dev, float *front_dev, const ViewParams &p, int strategy, cudaStream_t s)
+{
+    if (offsets[batch] > offsets[0] && (reinterpret_cast<uintptr_t>(points_dev) & 15u))
+        return fail("points_dev must be 16-byte aligned");
+    for (int c0 = 0; c0 < batch; c0 += kMaxBatchPerLaunch) {
+        const int nb = (batch - c0 < kMaxBatchPerLaunch) ? batch - c0 : kMaxBatchPerLaunch;
+        float *top_c = top_dev ? top_dev + (size_t)c0 * (size_t)p.top_frame_floats : nullptr;
+        float *front_c = front_dev ? front_dev + (size_t)c0 * (size_t)p.front_frame_floats : nullptr;
+        if (enqueue_chunk(ctx, ws, points_dev, offsets + c0, nb, top_c, front_c, p, strategy, s)) return -1;
+    }
+    return 0;
+}
+
+extern "C" int mv3d_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *offsets_host, int batch,
+                                     float *top_dev, float *front_dev, const mv3d_top_params *tp,
+                                     const mv3d_front_params *fp, int semantics, int strategy, void *stream)
+{
+    if (!ctx) return fail("mv3d_encode_batch_dev: ctx is NULL");
+    if (check_offsets(offsets_host, batch)) return -1;
+    ViewParams p;
+    if (make_params(ctx, tp, fp, top_dev != nullptr, front_dev != nullptr, semantics, &p)) return -1;
+    if (batch == 0 || (!top_dev && !front_dev)) return 0;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    const int strat = mv3d_resolve_strategy(ctx, tp, strategy);
+    return encode_dev_locked(ctx, ctx->ws, points_dev, offsets_host, batch, top_dev, front_dev, p, strat,
+                             static_cast<cudaStream_t>(stream));
+}
+
+// ------------------------------------------------------------------------------------------------
+// host buffers: per-sweep pipeline over kSlots streams (copy-in, encode, copy-out overlap across sweeps)
+// ------------------------------------------------------------------------------------------------
+extern "C" int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, const int *offsets_host, int batch,
+                                      float *top_host, float *front_host, const mv3d_top_params *tp,
+                                      const mv3d_front_params *fp, int semantics, int strategy)
+{
+    if (!ctx) return fail("mv3d_encode_batch_host: ctx is NULL");
+    if (check_offsets(offsets_host, batch)) return -1;
+    ViewParams p;
+    if (make_params(ctx, tp, fp, top_host != nullptr, front_host != nullptr, semantics, &p)) return -1;
+    if (batch == 0 || (!top_host && !front_host)) return 0;
+    if (offsets_host[batch] > offsets_host[0] && !points_host) return fail("points_host is NULL");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    const int strat = mv3d_resolve_strategy(ctx, tp, strategy);
+    const size_t top_bytes = (size_t)p.top_frame_floats * 4, front_bytes = (size_t)p.front_frame_floats * 4;
+
+    int rc = 0;
+    for (int i = 0; i < batch && rc == 0; i++) {
+        HostSlot &slot = ctx->slots[i % kSlots];
+        if (!slot.stream) CUDA_TRY(cudaStreamCreateWithFlags(&slot.stream, cudaStreamNonBlocking));
+        cudaStream_t s = slot.stream;
+        const int n = offsets_host[i + 1] - offsets_host[i];
+        // Stream order makes the slot's previous copy-out finish before its buffers are reused.
+        if (ensure(slot.points, (size_t)n * 16 + 16, false, s)) { rc = -1; break; }
+        if (top_host && ensure(slot.top, top_bytes + 16, false, s)) { rc = -1; break; }
+        if (front_host && ensure(slot.front, front_bytes + 16, false, s)) { rc = -1; break; }
+        if (n > 0)
+            CUDA_TRY(cudaMemcpyAsync(slot.points.ptr, points_host + (size_t)offsets_host[i] * 4, (size_t)n * 16,
+                                     cudaMemcpyHostToDevice, s));
+        const int local_off[2] = {0, n};
+        float *top_d = top_host ? static_cast<float *>(slot.top.ptr) : nullptr;
+        float *front_d = front_host ? static_cast<float *>(slot.front.ptr) : nullptr;
+        if (encode_dev_locked(ctx, slot.ws, static_cast<const float *>(slot.points.ptr), local_off, 1, top_d, front_d,
+                              p, strat, s)) { rc = -1; break; }
+        if (top_host && top_bytes)
+            CUDA_TRY(cudaMemcpyAsync(top_host + (size_t)i * (size_t)p.top_frame_floats, top_d, top_bytes,
+                                     cudaMemcpyDeviceToHost, s));
+        if (front_host && front_bytes)
+            CUDA_TRY(cudaMemcpyAsync(front_host + (size_t)i * (size_t)p.front_frame_floats, front_d, front_bytes,
+                                     cudaMemcpyDeviceToHost, s));
+    }
+    for (auto &slot : ctx->slots)
+        if (slot.stream) {
+            cudaError_t e = cudaStreamSynchronize(slot.stream);
+            if (e != cudaSuccess && rc == 0) rc = fail("pipeline failed: %s", cudaGetErrorString(e));
+        }
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// the reference symbols
+// ------------------------------------------------------------------------------------------------
+static std::mutex g_default_mu;
+static mv3d_ctx *g_default_ctx = nullptr;
+
+// Created on first use, so a process that forks workers before encoding (multiprocessing.Pool in
+// src/data.py:495) gets one CUDA context per worker, like the reference's pycuda loaders do.
+static mv3d_ctx *default_ctx()
+{
+    std::lock_guard<std::mutex> lock(g_default_mu);
+    if (!g_default_ctx) {
+        const char *dev = getenv("MV3D_DEVICE");
+        if (mv3d_ctx_create(dev ? atoi(dev) : 0, &g_default_ctx)) g_default_ctx = nullptr;
+    }
+    return g_default_ctx;
+}
+
+static void zero_host(void *p, double floats)
+{
+    if (p && floats > 0 && floats < 1e12) memset(p, 0, (size_t)floats * 4);
+}
+
+extern "C" void createTopMaps(const void *raw_data, int num, const void *top_data, float x_MIN, float x_MAX,
+                              float y_MIN, float y_MAX, float z_MIN, float z_MAX, float x_DIVISION, float y_DIVISION,
+                              float z_DIVISION, int X_SIZE, int Y_SIZE, int Z_SIZE)
+{
+    g_error[0] = 0;
+    const mv3d_top_params tp = {x_MIN, x_MAX, y_MIN, y_MAX, z_MIN, z_MAX, x_DIVISION, y_DIVISION, z_DIVISION,
+                                X_SIZE, Y_SIZE, Z_SIZE};
+    const int offsets[2] = {0, num > 0 ? num : 0};
+    mv3d_ctx *ctx = default_ctx();
+    int rc = ctx ? mv3d_encode_batch_host(ctx, static_cast<const float *>(raw_data), offsets, 1,
+                                          static_cast<float *>(const_cast<void *>(top_data)), nullptr, &tp, nullptr,
+                                          MV3D_SEM_TOP, MV3D_STRATEGY_AUTO)
+                 : -1;
+    if (rc) {
+        fprintf(stderr, "libmv3d_encode: createTopMaps failed: %s\n", g_error);
+        if (X_SIZE > 0 && Y_SIZE > 0 && Z_SIZE >= 0)
+            zero_host(const_cast<void *>(top_data), (double)X_SIZE * Y_SIZE * (Z_SIZE + 2));
+    }
+}
+
+extern "C" void createTopAndFrontMaps(const void *raw_data, int num, const void *top_data, const void *front_data,
+                                      float x_MIN, float x_MAX, float y_MIN, float y_MAX, float z_MIN, float z_MAX,
+                                      float x_DIVISION, float y_DIVISION, float z_DIVISION, int X_SIZE, int Y_SIZE,
+                                      int Z_SIZE, float phi_MIN, float phi_MAX, float theta_MIN, float theta_MAX,
+                                      float phi_DIVISION, float theta_DIVISION, float C_SIZE, float R_SIZE, float F_SIZE)
+{
+    g_error[0] = 0;
+    const mv3d_top_params tp = {x_MIN, x_MAX, y_MIN, y_MAX, z_MIN, z_MAX, x_DIVISION, y_DIVISION, z_DIVISION,
+                                X_SIZE, Y_SIZE, Z_SIZE};
+    const mv3d_front_params fp = {phi_MIN, phi_MAX, theta_MIN, theta_MAX, phi_DIVISION, theta_DIVISION,
+                                  C_SIZE, R_SIZE, F_SIZE};
+    const int offsets[2] = {0, num > 0 ? num : 0};
+    mv3d_ctx *ctx = default_ctx();
+    int rc = ctx ? mv3d_encode_batch_host(ctx, static_cast<const float *>(raw_data), offsets, 1,
+                                          static_cast<float *>(const_cast<void *>(top_data)),
+                                          static_cast<float *>(const_cast<void *>(front_data)), &tp, &fp,
+                                          MV3D_SEM_TOPFRONT, MV3D_STRATEGY_AUTO)
+                 : -1;
+    if (rc) {
+        fprintf(stderr, "libmv3d_encode: createTopAndFrontMaps failed: %s\n", g_error);
+        if (X_SIZE > 0 && Y_SIZE > 0 && Z_SIZE >= 0)
+            zero_host(const_cast<void *>(top_data), (double)X_SIZE * Y_SIZE * (Z_SIZE + 2));
+        if (C_SIZE > 0 && R_SIZE > 0 && F_SIZE > 0) zero_host(const_cast<void *>(front_data), (double)C_SIZE * R_SIZE * F_SIZE);
+    }
+}

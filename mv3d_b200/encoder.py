@@ -1,0 +1,120 @@
+"""Device-resident, batched view encoder: thin Python over the additive C ABI (include/mv3d_encode.h).
+
+PyTorch is plumbing here (device memory, streams, torch.distributed); every computation happens in
+libmv3d_encode.so. Tensors are handed over by `data_ptr()`.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import _lib
+from .params import FrontParams, TopParams
+
+
+def _top_c(top: TopParams) -> _lib.TopParamsC:
+    return _lib.TopParamsC(*top.floats, top.xn, top.yn, top.zn)
+
+
+def _front_c(front: FrontParams) -> _lib.FrontParamsC:
+    return _lib.FrontParamsC(front.phi_min, front.phi_max, front.theta_min, front.theta_max,
+                             front.phi_div, front.theta_div, float(front.cn), float(front.rn), float(front.fn))
+
+
+class ViewEncoder:
+    """One per GPU. `semantics`: "top" = createTopMaps arithmetic (truncating cell index),
+    "topfront" = createTopAndFrontMaps arithmetic (floor). `strategy`: "auto" | "tile" | "atomic"."""
+
+    def __init__(self, device: int = 0, semantics: str = "topfront", strategy: str = "auto"):
+        self._lib = _lib.load_library()
+        self._ctx = ctypes.c_void_p()
+        if self._lib.mv3d_ctx_create(int(device), ctypes.byref(self._ctx)) != 0:
+            raise RuntimeError("mv3d_ctx_create: " + _lib.last_error())
+        self.device = int(device)
+        self.semantics = {"top": _lib.SEM_TOP, "topfront": _lib.SEM_TOPFRONT}[semantics]
+        self.strategy = _lib.STRATEGIES[strategy]
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._lib.mv3d_ctx_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.mv3d_ctx_launch_count(self._ctx))
+
+    def resolved_strategy(self, top: TopParams) -> str:
+        code = self._lib.mv3d_resolve_strategy(self._ctx, ctypes.byref(_top_c(top)), self.strategy)
+        return {v: k for k, v in _lib.STRATEGIES.items()}[code]
+
+    # -- device-resident path ---------------------------------------------------------------------
+    def encode_device(self, points, offsets, top: TopParams, front: FrontParams | None = None,
+                      top_out=None, front_out=None, want_top: bool = True, stream=None):
+        """Encode `batch = len(offsets)-1` sweeps held in one CUDA tensor `points` (total, 4) float32.
+
+        Returns `(top_out, front_out)`: float32 CUDA tensors `[batch, Xn, Yn, Zn+2]` / `[batch, R, C, F]`
+        (None for a view that was not requested). Only enqueues work on `stream` (default: torch's current).
+        """
+        import torch
+        assert points.is_cuda and points.dtype == torch.float32 and points.is_contiguous()
+        offs = np.ascontiguousarray(offsets, dtype=np.int32)
+        batch = len(offs) - 1
+        if want_top and top_out is None:
+            top_out = torch.empty((batch, *top.shape), dtype=torch.float32, device=points.device)
+        if front is not None and front_out is None:
+            front_out = torch.empty((batch, *front.shape), dtype=torch.float32, device=points.device)
+        if stream is None:
+            stream = torch.cuda.current_stream(points.device).cuda_stream
+        rc = self._lib.mv3d_encode_batch_dev(
+            self._ctx, points.data_ptr(), offs.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), batch,
+            top_out.data_ptr() if (want_top and top_out is not None) else None,
+            front_out.data_ptr() if front_out is not None else None,
+            ctypes.byref(_top_c(top)), ctypes.byref(_front_c(front)) if front is not None else None,
+            self.semantics, self.strategy, ctypes.c_void_p(stream))
+        if rc != 0:
+            raise RuntimeError("mv3d_encode_batch_dev: " + _lib.last_error())
+        return (top_out if want_top else None), front_out
+
+    # -- host buffers (H2D + encode + D2H, pipelined inside the library) -----------------------------
+    def encode_host(self, points: np.ndarray, offsets, top: TopParams, front: FrontParams | None = None,
+                    top_out: np.ndarray | None = None, front_out: np.ndarray | None = None, want_top: bool = True):
+        """Same, for numpy buffers. Pass arrays from `pinned_empty` to get direct DMA."""
+        offs = np.ascontiguousarray(offsets, dtype=np.int32)
+        batch = len(offs) - 1
+        assert points.dtype == np.float32 and points.flags["C_CONTIGUOUS"]
+        if want_top and top_out is None:
+            top_out = np.empty((batch, *top.shape), dtype=np.float32)
+        if front is not None and front_out is None:
+            front_out = np.empty((batch, *front.shape), dtype=np.float32)
+        rc = self._lib.mv3d_encode_batch_host(
+            self._ctx, points.ctypes.data, offs.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), batch,
+            top_out.ctypes.data if (want_top and top_out is not None) else None,
+            front_out.ctypes.data if front_out is not None else None,
+            ctypes.byref(_top_c(top)), ctypes.byref(_front_c(front)) if front is not None else None,
+            self.semantics, self.strategy)
+        if rc != 0:
+            raise RuntimeError("mv3d_encode_batch_host: " + _lib.last_error())
+        return (top_out if want_top else None), front_out
+
+
+def pinned_empty(shape, dtype=np.float32) -> np.ndarray:
+    """A numpy array on page-locked host memory (mv3d_host_alloc), so copies to/from the GPU are direct DMA.
+    The allocation is released when the last array viewing it is garbage-collected."""
+    import weakref
+    dtype = np.dtype(dtype)
+    count = int(np.prod(shape, dtype=np.int64))
+    nbytes = max(count * dtype.itemsize, 1)
+    lib = _lib.load_library()
+    ptr = lib.mv3d_host_alloc(nbytes)
+    if not ptr:
+        raise MemoryError("mv3d_host_alloc: " + _lib.last_error())
+    buf = (ctypes.c_char * nbytes).from_address(ptr)
+    weakref.finalize(buf, lib.mv3d_host_free, ptr)
+    return np.frombuffer(buf, dtype=dtype, count=count).reshape(shape)

@@ -1,0 +1,69 @@
+"""CPU tests of the boundary: libmv3d_encode.so builds for sm_100a, loads, and exports every symbol that
+include/mv3d_encode.h declares -- and nothing on the product path reaches for the oracle."""
+import ctypes
+import os
+import re
+import subprocess
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "mv3d_encode.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(createTopMaps|createTopAndFrontMaps|mv3d_[a-z_]+)\s*\(", text)))
+
+
+def test_header_symbols_are_exported(encoder_lib):
+    from mv3d_b200 import _lib
+    declared = _declared_symbols()
+    assert set(declared) == set(_lib.EXPORTED_SYMBOLS)
+    for name in declared:
+        assert hasattr(encoder_lib, name), name
+    out = subprocess.run(["nm", "-D", "--defined-only", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    for name in declared:
+        assert re.search(rf" T {name}$", out, flags=re.M), f"{name} not exported as a C symbol"
+
+
+def test_library_is_sm100a_only():
+    from mv3d_b200 import _lib
+    out = subprocess.run(["cuobjdump", "-lelf", _lib.LIB_PATH], capture_output=True, text=True).stdout
+    archs = set(re.findall(r"sm_(\d+a?)", out))
+    assert archs == {"100a"}, out
+
+
+def test_fails_loudly_without_gpu(encoder_lib):
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    ctx = ctypes.c_void_p()
+    assert encoder_lib.mv3d_ctx_create(0, ctypes.byref(ctx)) != 0
+    assert b"no CPU fallback" in encoder_lib.mv3d_last_error()
+    import numpy as np
+    from mv3d_b200.ver3 import createTopMaps
+    from mv3d_b200.params import TopParams
+    top = TopParams(0, 1, 0, 1, 0, 1, 0.5, 0.5, 0.5)
+    out = np.ones(top.shape, np.float32)
+    with pytest.raises(RuntimeError):
+        createTopMaps(np.zeros((1, 4), np.float32), 1, out, top.as_top_paras())
+    assert not out.any()  # failure leaves zeros, never stale data
+
+
+def test_product_never_imports_oracle():
+    for dirpath, _, files in os.walk(os.path.join(ROOT, "mv3d_b200")):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert not re.search(r"^\s*(import|from)\s+oracle\b", text, flags=re.M), f
+                assert "view_oracle" not in text and "oracle/_ref" not in text, f
+
+
+def test_param_grid_sizes():
+    from mv3d_b200.params import DENSE_TOP, KITTI_FRONT_64x512, KITTI_PAPER_TOP, REFERENCE_KITTI_TOP
+    assert KITTI_PAPER_TOP.shape == (704, 800, 27)
+    assert DENSE_TOP.shape == (1408, 1600, 10)
+    assert REFERENCE_KITTI_TOP.shape == (800, 600, 27)  # src/utils/batch_loading.py:620
+    assert KITTI_FRONT_64x512.shape == (64, 512, 3)
+    assert KITTI_FRONT_64x512.as_front_paras()[6:] == (64, 512, 3)

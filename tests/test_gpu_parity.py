@@ -1,0 +1,222 @@
+"""GPU parity tests (run with -m gpu on the B200 box): the CUDA path, called through the C ABI of
+libmv3d_encode.so, against the CPU oracle on the same inputs. Bit-exact (np.array_equal) on every channel."""
+import numpy as np
+import pytest
+
+import cases
+from mv3d_b200.params import DENSE_TOP, KITTI_FRONT_64x512, KITTI_PAPER_TOP
+from mv3d_b200.sweeps import dense_cloud, hdl64_sweep, pack_sweeps
+
+pytestmark = pytest.mark.gpu
+
+ALL_CASES = cases.quirk_cases() + cases.small_cases() + cases.sweep_cases()
+IDS = [c[0] for c in ALL_CASES]
+
+
+def _diff(a, b):
+    bad = ~((a == b) | (np.isnan(a) & np.isnan(b)))
+    return f"{np.count_nonzero(bad)} of {a.size} cells differ; first at {np.argwhere(bad)[:3].tolist()}"
+
+
+def assert_same(a, b, what):
+    assert a.shape == b.shape, what
+    assert np.array_equal(a, b, equal_nan=True), f"{what}: {_diff(a, b)}"
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "these tests need a CUDA device"
+    return torch
+
+
+# ---- the reference symbols, host pointers ------------------------------------------------------------
+@pytest.mark.parametrize("name,pts,top,front", ALL_CASES, ids=IDS)
+def test_createTopMaps_symbol(oracle_mod, name, pts, top, front):
+    from mv3d_b200.ver3 import createTopMaps
+    out = np.ones(top.shape, dtype=np.float32)  # garbage in: the callee must overwrite everything (Q7)
+    createTopMaps(pts, pts.shape[0], out, top.as_top_paras())
+    assert_same(out, oracle_mod.top_maps(pts, top), f"{name} createTopMaps")
+
+
+@pytest.mark.parametrize("name,pts,top,front", ALL_CASES, ids=IDS)
+def test_createTopAndFrontMaps_symbol(oracle_mod, name, pts, top, front):
+    from mv3d_b200.ver3 import createTopAndFrontMaps
+    out = np.full(top.shape, 7.0, dtype=np.float32)
+    fout = np.full(front.shape, 7.0, dtype=np.float32)
+    createTopAndFrontMaps(pts, pts.shape[0], out, fout, top.as_top_paras(), front.as_front_paras())
+    et, ef = oracle_mod.top_and_front_maps(pts, top, front)
+    assert_same(out, et, f"{name} top")
+    assert_same(fout, ef, f"{name} front")
+
+
+def test_clidar_to_top_flip(oracle_mod):
+    from mv3d_b200.params import REFERENCE_KITTI_TOP
+    from mv3d_b200.ver3 import clidar_to_top
+    s = hdl64_sweep(3)
+    got = clidar_to_top(s)
+    exp = oracle_mod.top_maps(s, REFERENCE_KITTI_TOP)
+    assert_same(np.ascontiguousarray(got), np.ascontiguousarray(exp[::-1, ::-1]), "clidar_to_top")
+
+
+# ---- the batched device entry point ----------------------------------------------------------------------
+@pytest.mark.parametrize("strategy", ["tile", "atomic"])
+@pytest.mark.parametrize("semantics", ["top", "topfront"])
+def test_batched_device_ragged(torch_cuda, oracle_mod, strategy, semantics):
+    """Ragged batch on the real grid: full sweeps, an empty sweep, a single point, a hot cell."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    qc = {c[0]: c[1] for c in cases.quirk_cases()}
+    sweeps = [hdl64_sweep(0), np.zeros((0, 4), np.float32), qc["q5_ties"], hdl64_sweep(1)[:50001], qc["hot_cell"],
+              qc["q10_nonfinite"], hdl64_sweep(2)]
+    pts, offs = pack_sweeps(sweeps)
+    enc = ViewEncoder(0, semantics=semantics, strategy=strategy)
+    assert enc.resolved_strategy(KITTI_PAPER_TOP) == strategy
+    d = torch.from_numpy(pts).cuda()
+    for rep in range(2):  # twice: the workspace must clean itself between calls
+        top, front = enc.encode_device(d, offs, KITTI_PAPER_TOP, KITTI_FRONT_64x512 if semantics == "topfront" else None)
+        torch.cuda.synchronize()
+        top = top.cpu().numpy()
+        for i, s in enumerate(sweeps):
+            if semantics == "top":
+                assert_same(top[i], oracle_mod.top_maps(s, KITTI_PAPER_TOP), f"{strategy}/{semantics} rep{rep} sweep {i}")
+            else:
+                et, ef = oracle_mod.top_and_front_maps(s, KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+                assert_same(top[i], et, f"{strategy}/{semantics} rep{rep} sweep {i} top")
+                assert_same(front[i].cpu().numpy(), ef, f"{strategy}/{semantics} rep{rep} sweep {i} front")
+    assert enc.launch_count > 0
+    enc.close()
+
+
+@pytest.mark.parametrize("strategy", ["tile", "atomic"])
+@pytest.mark.parametrize("name,pts,top,front", cases.small_cases(), ids=[c[0] for c in cases.small_cases()])
+def test_batched_device_small_grids(torch_cuda, oracle_mod, strategy, name, pts, top, front):
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    enc = ViewEncoder(0, strategy=strategy)
+    sweeps = [pts, pts[: len(pts) // 2], pts[::-1].copy()]
+    packed, offs = pack_sweeps(sweeps)
+    d = torch.from_numpy(packed).cuda() if len(packed) else torch.zeros((0, 4), device="cuda")
+    t, f = enc.encode_device(d, offs, top, front)
+    torch.cuda.synchronize()
+    for i, s in enumerate(sweeps):
+        et, ef = oracle_mod.top_and_front_maps(s, top, front)
+        assert_same(t[i].cpu().numpy(), et, f"{name}[{i}] top")
+        assert_same(f[i].cpu().numpy(), ef, f"{name}[{i}] front")
+    enc.close()
+
+
+def test_front_only_and_top_only(torch_cuda, oracle_mod):
+    """BASELINE config 3: front view only (the BEV gate still applies, the BEV tensor is not produced)."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    enc = ViewEncoder(0)
+    sweeps = [hdl64_sweep(f) for f in range(10, 14)]
+    pts, offs = pack_sweeps(sweeps)
+    d = torch.from_numpy(pts).cuda()
+    t, f = enc.encode_device(d, offs, KITTI_PAPER_TOP, KITTI_FRONT_64x512, want_top=False)
+    assert t is None
+    t2, f2 = enc.encode_device(d, offs, KITTI_PAPER_TOP, None)
+    assert f2 is None
+    torch.cuda.synchronize()
+    for i, s in enumerate(sweeps):
+        et, ef = oracle_mod.top_and_front_maps(s, KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+        assert_same(f[i].cpu().numpy(), ef, f"front-only sweep {i}")
+        assert_same(t2[i].cpu().numpy(), et, f"top-only sweep {i}")
+    enc.close()
+
+
+def test_config2_batch64_bit_exact(torch_cuda, oracle_mod):
+    """BASELINE config 2: 64 KITTI-shaped sweeps, BEV 704x800x27 + FV 64x512x3, every frame vs the oracle."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    sweeps = [hdl64_sweep(f) for f in range(64)]
+    pts, offs = pack_sweeps(sweeps)
+    d = torch.from_numpy(pts).cuda()
+    enc = ViewEncoder(0)
+    top, front = enc.encode_device(d, offs, KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+    torch.cuda.synchronize()
+    front = front.cpu().numpy()
+    cells = mism = 0
+    for i, s in enumerate(sweeps):
+        et, ef = oracle_mod.top_and_front_maps(s, KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+        got = top[i].cpu().numpy()
+        cells += got.size + ef.size
+        mism += np.count_nonzero(got != et) + np.count_nonzero(front[i] != ef)
+    assert mism == 0, f"{mism} of {cells} cells differ"
+    enc.close()
+
+
+@pytest.mark.parametrize("strategy", ["tile", "atomic"])
+def test_config5_dense_cloud(torch_cuda, oracle_mod, strategy):
+    """BASELINE config 5: 2 M points, 1408x1600x(8+2) at 0.05 m -- the high-contention case."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    pts = dense_cloud()
+    offs = np.array([0, pts.shape[0]], np.int32)
+    enc = ViewEncoder(0, semantics="top", strategy=strategy)
+    top, _ = enc.encode_device(torch.from_numpy(pts).cuda(), offs, DENSE_TOP)
+    torch.cuda.synchronize()
+    assert_same(top[0].cpu().numpy(), oracle_mod.top_maps(pts, DENSE_TOP), f"dense {strategy}")
+    enc.close()
+
+
+def test_host_batch_pinned(torch_cuda, oracle_mod):
+    """The pipelined host entry point with page-locked buffers (what bench.py's e2e leg times)."""
+    from mv3d_b200.encoder import ViewEncoder, pinned_empty
+    sweeps = [hdl64_sweep(f) for f in range(20, 27)]
+    pts, offs = pack_sweeps(sweeps)
+    hp = pinned_empty(pts.shape)
+    hp[...] = pts
+    ht = pinned_empty((len(sweeps), *KITTI_PAPER_TOP.shape))
+    hf = pinned_empty((len(sweeps), *KITTI_FRONT_64x512.shape))
+    ht[...] = 3.0
+    enc = ViewEncoder(0)
+    enc.encode_host(hp, offs, KITTI_PAPER_TOP, KITTI_FRONT_64x512, top_out=ht, front_out=hf)
+    for i, s in enumerate(sweeps):
+        et, ef = oracle_mod.top_and_front_maps(s, KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+        assert_same(ht[i], et, f"host sweep {i} top")
+        assert_same(hf[i], ef, f"host sweep {i} front")
+    enc.close()
+
+
+def test_golden_fixtures_on_gpu():
+    """The committed outputs of the reference build (tests/golden) against the CUDA path directly."""
+    import os
+    import golden.make_golden as mg
+    from mv3d_b200.ver3 import createTopAndFrontMaps, createTopMaps
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ver3_golden.npz"))
+    for name, pts, top, front in mg.golden_cases():
+        out = np.ones(top.shape, np.float32)
+        createTopMaps(pts, pts.shape[0], out, top.as_top_paras())
+        assert_same(out, mg.unpack(g, name, "top", top.shape), f"{name} golden top")
+        fout = np.ones(front.shape, np.float32)
+        createTopAndFrontMaps(pts, pts.shape[0], out, fout, top.as_top_paras(), front.as_front_paras())
+        assert_same(out, mg.unpack(g, name, "topfront_top", top.shape), f"{name} golden topfront/top")
+        assert_same(fout, mg.unpack(g, name, "topfront_front", front.shape), f"{name} golden topfront/front")
+
+
+def test_size_independent_properties(torch_cuda):
+    """At full size, properties that need no oracle: point order only matters through the documented
+    tie-breaks (heights and density are permutation invariant), counts recovered from density sum to the
+    number of gated points, and the last output row/column stay zero (Q3)."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    s = hdl64_sweep(5)
+    perm = np.random.default_rng(0).permutation(len(s))
+    pts, offs = pack_sweeps([s, np.ascontiguousarray(s[perm])])
+    enc = ViewEncoder(0, semantics="top")
+    top, _ = enc.encode_device(torch.from_numpy(pts).cuda(), offs, KITTI_PAPER_TOP)
+    top = top.cpu().numpy()
+    zn = KITTI_PAPER_TOP.zn
+    assert np.array_equal(top[0][..., :zn], top[1][..., :zn])
+    assert np.array_equal(top[0][..., zn + 1], top[1][..., zn + 1])
+    assert not top[0][-1].any() and not top[0][:, -1].any()
+    assert ((top[0][..., :zn] >= 0) & (top[0][..., :zn] < 1)).all()
+    # counts from the density channel (below saturation) vs a float32 numpy restatement of the gate
+    k = KITTI_PAPER_TOP
+    q = lambda v, lo, d: ((v - np.float32(lo)) / np.float32(d)).astype(np.int64)
+    X, Y, Z = q(s[:, 0], k.x_min, k.x_div), q(s[:, 1], k.y_min, k.y_div), q(s[:, 2], k.z_min, k.z_div)
+    keep = (X >= 1) & (Y >= 1) & (Z >= 0) & (X < k.xn) & (Y < k.yn) & (Z < k.zn)
+    assert np.count_nonzero(top[0][..., zn + 1]) == len(set(zip(X[keep].tolist(), Y[keep].tolist())))
+    enc.close()
