@@ -113,6 +113,15 @@ void mv3d_host_free(void *p);
 /* Kernels launched by this context so far (bench.py's gpu_launches). */
 long long mv3d_ctx_launch_count(const mv3d_ctx *ctx);
 
+/* Optional per-kernel timing for bench.py's roofline: when enabled, CUDA events are recorded on the launching
+ * stream around every kernel. mv3d_ctx_kernel_times() waits for the recorded events and reports, per kernel
+ * class k in [0, mv3d_kernel_count()), the accumulated device milliseconds and launch counts
+ * (launch counts accumulate whether or not profiling is on). */
+int mv3d_ctx_set_profiling(mv3d_ctx *ctx, int enable);
+int mv3d_kernel_count(void);
+const char *mv3d_kernel_name(int kernel);
+int mv3d_ctx_kernel_times(mv3d_ctx *ctx, double *ms_out, long long *launches_out, int reset);
+
 /* The strategy MV3D_STRATEGY_AUTO resolves to for a parameter set (MV3D_STRATEGY_ATOMIC or _TILE). */
 int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy);
 

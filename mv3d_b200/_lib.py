@@ -69,6 +69,7 @@ EXPORTED_SYMBOLS = (
     "createTopMaps", "createTopAndFrontMaps", "mv3d_last_error", "mv3d_ctx_create", "mv3d_ctx_destroy",
     "mv3d_encode_batch_dev", "mv3d_encode_batch_host", "mv3d_host_alloc", "mv3d_host_free",
     "mv3d_ctx_launch_count", "mv3d_resolve_strategy", "mv3d_version",
+    "mv3d_ctx_set_profiling", "mv3d_kernel_count", "mv3d_kernel_name", "mv3d_ctx_kernel_times",
 )
 
 _lib = None
@@ -103,6 +104,10 @@ def load_library() -> ctypes.CDLL:
     lib.mv3d_ctx_launch_count.argtypes = [vp]
     lib.mv3d_ctx_launch_count.restype = ctypes.c_longlong
     lib.mv3d_resolve_strategy.argtypes = [vp, ctypes.POINTER(TopParamsC), ci]
+    lib.mv3d_ctx_set_profiling.argtypes = [vp, ci]
+    lib.mv3d_kernel_name.argtypes = [ci]
+    lib.mv3d_kernel_name.restype = ctypes.c_char_p
+    lib.mv3d_ctx_kernel_times.argtypes = [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), ci]
     _lib = lib
     return lib
 

@@ -14,6 +14,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
+#include <vector>
 
 using namespace mv3d;
 
@@ -67,7 +68,24 @@ struct HostSlot {
 
 } // namespace
 
+// Kernel classes, in the order mv3d_kernel_name() reports them.
+enum KernelId { K_CLASSIFY = 0, K_TILE_SCAN, K_BIN, K_TILE_BUILD, K_FRONT_FINALIZE, K_FILL_ZERO, K_ATOMIC_SCATTER,
+                K_ATOMIC_FINALIZE, K_COUNT };
+static const char *const kKernelNames[K_COUNT] = {"classify_kernel", "tile_scan_kernel", "bin_kernel",
+                                                  "tile_build_kernel", "front_finalize_kernel", "fill_zero_kernel",
+                                                  "atomic_scatter_kernel", "atomic_finalize_kernel"};
+
+struct TimedLaunch {
+    cudaEvent_t start, stop;
+    int kernel;
+};
+
 struct mv3d_ctx {
+    bool profiling = false;
+    std::vector<TimedLaunch> timed;        // pending (not yet accumulated) event pairs
+    std::vector<cudaEvent_t> event_pool;   // recycled events
+    double kernel_ms[K_COUNT] = {0};
+    long long kernel_launches[K_COUNT] = {0};
     int device = 0;
     int sm_count = 0;
     size_t smem_optin = 0;
@@ -170,10 +188,45 @@ extern "C" void mv3d_ctx_destroy(mv3d_ctx *ctx)
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     if (ctx->lut) cudaFree(ctx->lut);
+    for (auto &t : ctx->timed) { cudaEventDestroy(t.start); cudaEventDestroy(t.stop); }
+    for (auto e : ctx->event_pool) cudaEventDestroy(e);
     delete ctx;
 }
 
 extern "C" long long mv3d_ctx_launch_count(const mv3d_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int mv3d_ctx_set_profiling(mv3d_ctx *ctx, int enable)
+{
+    if (!ctx) return fail("mv3d_ctx_set_profiling: ctx is NULL");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    ctx->profiling = enable != 0;
+    return 0;
+}
+
+extern "C" int mv3d_kernel_count(void) { return K_COUNT; }
+extern "C" const char *mv3d_kernel_name(int kernel) { return (kernel >= 0 && kernel < K_COUNT) ? kKernelNames[kernel] : ""; }
+
+extern "C" int mv3d_ctx_kernel_times(mv3d_ctx *ctx, double *ms_out, long long *launches_out, int reset)
+{
+    if (!ctx) return fail("mv3d_ctx_kernel_times: ctx is NULL");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    for (auto &t : ctx->timed) {
+        CUDA_TRY(cudaEventSynchronize(t.stop));
+        float ms = 0.0f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, t.start, t.stop));
+        ctx->kernel_ms[t.kernel] += ms;
+        ctx->event_pool.push_back(t.start);
+        ctx->event_pool.push_back(t.stop);
+    }
+    ctx->timed.clear();
+    for (int k = 0; k < K_COUNT; k++) {
+        if (ms_out) ms_out[k] = ctx->kernel_ms[k];
+        if (launches_out) launches_out[k] = ctx->kernel_launches[k];
+        if (reset) { ctx->kernel_ms[k] = 0; ctx->kernel_launches[k] = 0; }
+    }
+    return 0;
+}
 
 extern "C" void *mv3d_host_alloc(size_t bytes)
 {
@@ -267,6 +320,37 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
     return 0;
 }
 
+// Optional per-kernel timing: CUDA events recorded on the launching stream around each kernel.
+static cudaEvent_t take_event(mv3d_ctx *ctx)
+{
+    cudaEvent_t e = nullptr;
+    if (!ctx->event_pool.empty()) {
+        e = ctx->event_pool.back();
+        ctx->event_pool.pop_back();
+    } else if (cudaEventCreate(&e) != cudaSuccess) {
+        e = nullptr;
+    }
+    return e;
+}
+
+template <typename F>
+static void timed_launch(mv3d_ctx *ctx, int kernel, cudaStream_t s, F &&launch)
+{
+    TimedLaunch t{nullptr, nullptr, kernel};
+    if (ctx->profiling) {
+        t.start = take_event(ctx);
+        t.stop = take_event(ctx);
+        if (t.start && t.stop) cudaEventRecord(t.start, s);
+    }
+    const int n = launch();
+    ctx->launches += n;
+    ctx->kernel_launches[kernel] += n;
+    if (ctx->profiling && t.start && t.stop) {
+        cudaEventRecord(t.stop, s);
+        ctx->timed.push_back(t);
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // enqueue one chunk (<= kMaxBatchPerLaunch sweeps) on a stream
 // ------------------------------------------------------------------------------------------------
@@ -300,31 +384,37 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
         int blocks_per_sm = 0;
         CUDA_TRY(tile_build_configure(p, &blocks_per_sm));
         if (blocks_per_sm < 1) return fail("tile kernel does not fit: %zu bytes of shared memory", tile_smem_bytes(p));
-        ctx->launches += launch_classify(pts, offs, p, batch, max_points, static_cast<uint2 *>(ws.keys.ptr),
-                                         static_cast<unsigned *>(ws.tile_count.ptr), winners, s);
-        ctx->launches += launch_tile_scan(static_cast<unsigned *>(ws.tile_count.ptr),
-                                          static_cast<unsigned *>(ws.tile_off.ptr), p.tiles_per_frame, batch, s);
-        ctx->launches += launch_bin(pts, offs, p, batch, max_points, static_cast<const uint2 *>(ws.keys.ptr),
-                                    static_cast<const unsigned *>(ws.tile_off.ptr), static_cast<uint4 *>(ws.binned.ptr), s);
-        ctx->launches += launch_tile_build(static_cast<const uint4 *>(ws.binned.ptr),
-                                           static_cast<const unsigned *>(ws.tile_off.ptr), offs, p, ctx->lut, top_dev,
-                                           batch, blocks_per_sm * ctx->sm_count, s);
+        uint2 *keys = static_cast<uint2 *>(ws.keys.ptr);
+        uint4 *binned = static_cast<uint4 *>(ws.binned.ptr);
+        unsigned *tcount = static_cast<unsigned *>(ws.tile_count.ptr), *toff = static_cast<unsigned *>(ws.tile_off.ptr);
+        const int grid_blocks = blocks_per_sm * ctx->sm_count;
+        timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, winners, s); });
+        timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
+        timed_launch(ctx, K_BIN, s, [&] { return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s); });
+        timed_launch(ctx, K_TILE_BUILD, s, [&] {
+            return launch_tile_build(binned, toff, offs, p, ctx->lut, top_dev, batch, grid_blocks, s);
+        });
     } else if (p.want_top && cells > 0) {
         if (ensure(ws.cellkey, (size_t)batch * cells * 8, false, s)) return -1;
-        ctx->launches += launch_fill_zero(top_dev, (size_t)batch * (size_t)p.top_frame_floats, ctx->sm_count, s);
-        ctx->launches += launch_fill_zero(static_cast<float *>(ws.cellkey.ptr), (size_t)batch * cells * 2, ctx->sm_count, s);
-        ctx->launches += launch_atomic_scatter(pts, offs, p, batch, max_points, top_dev,
-                                               static_cast<unsigned long long *>(ws.cellkey.ptr), winners, s);
-        ctx->launches += launch_atomic_finalize(pts, offs, p, ctx->lut, batch, max_points, top_dev,
-                                                static_cast<unsigned long long *>(ws.cellkey.ptr), s);
+        unsigned long long *cellkey = static_cast<unsigned long long *>(ws.cellkey.ptr);
+        timed_launch(ctx, K_FILL_ZERO, s, [&] {
+            return launch_fill_zero(top_dev, (size_t)batch * (size_t)p.top_frame_floats, ctx->sm_count, s) +
+                   launch_fill_zero(reinterpret_cast<float *>(cellkey), (size_t)batch * cells * 2, ctx->sm_count, s);
+        });
+        timed_launch(ctx, K_ATOMIC_SCATTER, s, [&] {
+            return launch_atomic_scatter(pts, offs, p, batch, max_points, top_dev, cellkey, winners, s);
+        });
+        timed_launch(ctx, K_ATOMIC_FINALIZE, s, [&] {
+            return launch_atomic_finalize(pts, offs, p, ctx->lut, batch, max_points, top_dev, cellkey, s);
+        });
     } else if (p.want_front) {
         // front view only: the classify pass alone elects the winners (BEV gate still applies)
         ViewParams q = p;
         q.want_top = 0;
-        ctx->launches += launch_classify(pts, offs, q, batch, max_points, nullptr, nullptr, winners, s);
+        timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, q, batch, max_points, nullptr, nullptr, winners, s); });
     }
     if (p.want_front && p.front_pixels > 0)
-        ctx->launches += launch_front_finalize(pts, offs, p, batch, winners, front_dev, s);
+        timed_launch(ctx, K_FRONT_FINALIZE, s, [&] { return launch_front_finalize(pts, offs, p, batch, winners, front_dev, s); });
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

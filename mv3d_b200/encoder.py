@@ -50,6 +50,19 @@ class ViewEncoder:
     def launch_count(self) -> int:
         return int(self._lib.mv3d_ctx_launch_count(self._ctx))
 
+    def set_profiling(self, enable: bool) -> None:
+        """Record CUDA events around every kernel (read back with `kernel_times`)."""
+        self._lib.mv3d_ctx_set_profiling(self._ctx, int(bool(enable)))
+
+    def kernel_times(self, reset: bool = False) -> dict:
+        """{kernel name: (accumulated device ms, launches)}; waits for the recorded events."""
+        n = self._lib.mv3d_kernel_count()
+        ms = (ctypes.c_double * n)()
+        cnt = (ctypes.c_longlong * n)()
+        if self._lib.mv3d_ctx_kernel_times(self._ctx, ms, cnt, int(reset)) != 0:
+            raise RuntimeError("mv3d_ctx_kernel_times: " + _lib.last_error())
+        return {self._lib.mv3d_kernel_name(k).decode(): (float(ms[k]), int(cnt[k])) for k in range(n)}
+
     def resolved_strategy(self, top: TopParams) -> str:
         code = self._lib.mv3d_resolve_strategy(self._ctx, ctypes.byref(_top_c(top)), self.strategy)
         return {v: k for k, v in _lib.STRATEGIES.items()}[code]
