@@ -289,8 +289,9 @@ def run_ours(args):
     dom_ms, dom_launches = ktimes[dominant]
     step_kernel_ms = sum(v[0] for v in ktimes.values())
     # bytes the dominant kernel is responsible for, per launch
-    per_launch = {"tile_build_kernel": ab["bev"] * BATCH, "fill_zero_kernel": ab["bev"] * BATCH}.get(
-        dominant, ab["total"] * BATCH)
+    # (a step may launch it several times: one launch per pipelined sub-batch)
+    per_step = {"tile_build_kernel": ab["bev"] * BATCH}.get(dominant, ab["total"] * BATCH)
+    per_launch = per_step * args.steps / max(dom_launches, 1)
     achieved = per_launch / (dom_ms / max(dom_launches, 1) * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     step_achieved = ab["total"] * BATCH * args.steps / (elapsed_ms * 1e-3) / 1e9
     traffic = ncu_traffic(dominant)
@@ -298,6 +299,7 @@ def run_ours(args):
                 "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": per_launch,
                 "kernel_ms_per_launch": dom_ms / max(dom_launches, 1),
+                "kernel_launches_per_step": dom_launches / args.steps,
                 "kernel_share_of_step": dom_ms / step_kernel_ms if step_kernel_ms else None,
                 "step_achieved": step_achieved, "step_frac": step_achieved / peak,
                 "algorithmic_bytes_per_sweep": ab["total"],

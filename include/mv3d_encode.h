@@ -122,6 +122,14 @@ int mv3d_kernel_count(void);
 const char *mv3d_kernel_name(int kernel);
 int mv3d_ctx_kernel_times(mv3d_ctx *ctx, double *ms_out, long long *launches_out, int reset);
 
+/* Test hook: the per-point decisions of the encoder, for one sweep resident in device memory.
+ *   cell_dev[i]      output cell (X-1)*yn + (Y-1) of point i, or -1 when the gate rejects it
+ *   pix_dev[i]       front-view pixel r*C + c through the production arithmetic, or -1 (fp may be NULL: skipped)
+ *   pix_exact_dev[i] the same pixel through the all-double evaluation (the two must always agree) */
+int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int num, const mv3d_top_params *tp,
+                          const mv3d_front_params *fp, int semantics, int *cell_dev, int *pix_dev,
+                          int *pix_exact_dev, void *stream);
+
 /* The strategy MV3D_STRATEGY_AUTO resolves to for a parameter set (MV3D_STRATEGY_ATOMIC or _TILE). */
 int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy);
 

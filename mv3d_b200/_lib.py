@@ -70,6 +70,7 @@ EXPORTED_SYMBOLS = (
     "mv3d_encode_batch_dev", "mv3d_encode_batch_host", "mv3d_host_alloc", "mv3d_host_free",
     "mv3d_ctx_launch_count", "mv3d_resolve_strategy", "mv3d_version",
     "mv3d_ctx_set_profiling", "mv3d_kernel_count", "mv3d_kernel_name", "mv3d_ctx_kernel_times",
+    "mv3d_debug_point_keys",
 )
 
 _lib = None
@@ -108,6 +109,8 @@ def load_library() -> ctypes.CDLL:
     lib.mv3d_kernel_name.argtypes = [ci]
     lib.mv3d_kernel_name.restype = ctypes.c_char_p
     lib.mv3d_ctx_kernel_times.argtypes = [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), ci]
+    lib.mv3d_debug_point_keys.argtypes = [vp, vp, ci, ctypes.POINTER(TopParamsC), ctypes.POINTER(FrontParamsC), ci,
+                                          vp, vp, vp, vp]
     _lib = lib
     return lib
 

@@ -24,7 +24,6 @@ namespace mv3d {
 
 constexpr int kPointThreads = 256;
 constexpr int kTileThreads = 256;
-constexpr int kZeroChunkBytes = 8192;  // shared all-zero source for empty tiles (multiple of 16)
 
 // ------------------------------------------------------------------------------------------------
 // small PTX wrappers
@@ -135,14 +134,14 @@ tile_scan_kernel(unsigned *__restrict__ tile_count, unsigned *__restrict__ tile_
         if (lane == 31) warp_sums[warp] = incl;
         __syncthreads();
         if (warp == 0) {
-            unsigned w = warp_sums[lane];
+            unsigned w = (lane < kScanThreads / 32) ? warp_sums[lane] : 0u;
             unsigned wincl = w;
 #pragma unroll
             for (int d = 1; d < 32; d <<= 1) {
                 const unsigned up = __shfl_up_sync(0xFFFFFFFFu, wincl, d);
                 if ((int)lane >= d) wincl += up;
             }
-            warp_sums[lane] = wincl - w;  // exclusive prefix of the warp totals
+            if (lane < kScanThreads / 32) warp_sums[lane] = wincl - w;  // exclusive prefix of the warp totals
         }
         __syncthreads();
         const unsigned excl = carry + warp_sums[warp] + incl - v;
@@ -191,7 +190,8 @@ bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
 //                intensity of the key's winner
 //   store      : one cp.async.bulk shared->global for the whole tile (plain stores if misaligned)
 //   clean      : re-zero only the touched cells, after the bulk store has finished reading
-// Empty tiles (the majority) skip everything but the store, straight from the all-zero image.
+// Empty tiles (the majority) skip everything but the store, straight from the all-zero image; a non-empty
+// tile first waits for those in-flight reads of the image before accumulating into it.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kTileThreads)
 tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
@@ -205,96 +205,119 @@ tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
     const size_t img_bytes = ((size_t)T * planes * 4 + 15) & ~(size_t)15;
     unsigned long long *key = reinterpret_cast<unsigned long long *>(smem_raw + img_bytes);
     unsigned *dirty = reinterpret_cast<unsigned *>(key + T);
-    // Never-modified zeros: empty tiles are stored from here, so their in-flight bulk reads can never
-    // overlap a later tile's accumulation into the image.
-    __shared__ __align__(128) unsigned zeros[kZeroChunkBytes / 4];
     __shared__ unsigned ndirty;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int kWarps = kTileThreads / 32;
 
-    for (int w = threadIdx.x; w < T * planes; w += blockDim.x) img[w] = 0u;
-    for (int w = threadIdx.x; w < T; w += blockDim.x) key[w] = 0ull;
-    for (int w = threadIdx.x; w < kZeroChunkBytes / 4; w += blockDim.x) zeros[w] = 0u;
-    if (threadIdx.x == 0) ndirty = 0;
+    for (int w = tid; w < T * planes; w += kTileThreads) img[w] = 0u;
+    for (int w = tid; w < T; w += kTileThreads) key[w] = 0ull;
+    if (tid == 0) ndirty = 0;
     fence_proxy_async_smem();
     __syncthreads();
 
+    // Software pipeline over this CTA's tiles: the bin offsets of tile t+2 and the first record of tile t+1
+    // are requested while tile t is being built, so their L2 latency is off the per-tile critical path.
+    const int step = gridDim.x;
+    const int tpf = p.tiles_per_frame;
+    auto bin_range = [&](int t, const uint4 *&rec, int &n) {
+        n = 0;
+        rec = binned;
+        if (t < total_tiles) {
+            const int f = t / tpf, tl = t - f * tpf;
+            const unsigned *off = tile_off + (size_t)f * (tpf + 1) + tl;
+            const unsigned beg = __ldg(off);
+            n = (int)(__ldg(off + 1) - beg);
+            rec = binned + (size_t)offs.off[f] + beg;
+        }
+    };
+    const uint4 *rec0, *rec1, *rec2;
+    int n0, n1, n2;
+    bin_range(blockIdx.x, rec0, n0);
+    bin_range(blockIdx.x + step, rec1, n1);
+    uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+    if (tid < n0) q0 = __ldg(rec0 + tid);
+
     const long long cells_total = (long long)p.xn * p.yn;
-    for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-        const int f = t / p.tiles_per_frame;
-        const int tl = t - f * p.tiles_per_frame;
+    for (int t = blockIdx.x; t < total_tiles; t += step) {
+        bin_range(t + 2 * step, rec2, n2);
+        if (tid < n1) q1 = __ldg(rec1 + tid);
+
+        const int f = t / tpf, tl = t - f * tpf;
         const long long cell0 = (long long)tl * T;
         const int ncell = (int)min((long long)T, cells_total - cell0);
         const uint32_t bytes = (uint32_t)ncell * (uint32_t)planes * 4u;
         float *dst = top + (size_t)f * p.top_frame_floats + (size_t)cell0 * planes;
         const bool bulk = ((reinterpret_cast<uintptr_t>(dst) | (uintptr_t)bytes) & 15u) == 0;
-        const unsigned *off = tile_off + (size_t)f * (p.tiles_per_frame + 1) + tl;
-        const unsigned beg = off[0];
-        const int n = (int)(off[1] - beg);
 
-        if (n == 0) {  // empty tile: stream zeros, no synchronisation needed (the image is not modified)
+        if (n0 == 0) {
+            // Empty tile (the majority): stream the all-zero image; nothing is modified, so no barrier.
             if (bulk) {
-                if (threadIdx.x == 0) {
-                    for (uint32_t b = 0; b < bytes; b += kZeroChunkBytes)
-                        bulk_store(reinterpret_cast<unsigned char *>(dst) + b, zeros, min(bytes - b, (uint32_t)kZeroChunkBytes));
-                    bulk_commit();
-                }
+                if (tid == 0) { bulk_store(dst, img, bytes); bulk_commit(); }
             } else {
-                for (int w = threadIdx.x; w < ncell * planes; w += blockDim.x) dst[w] = 0.0f;
+                for (int w = tid; w < ncell * planes; w += kTileThreads) dst[w] = 0.0f;
             }
-            continue;
-        }
-
-        const uint4 *rec = binned + (size_t)offs.off[f] + beg;
-        for (int r = threadIdx.x; r < n; r += blockDim.x) {
-            const uint4 q = __ldg(rec + r);
-            const unsigned local = q.x & 0xFFFFu, Z = q.x >> 16;
-            unsigned *cellw = img + local * planes;
-            if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(&ndirty, 1u)] = local;
-            if ((int)q.y > 0) {  // h > 0: the reference's maps start at 0 and update on strict '>'
-                atomicMax(cellw + Z, q.y);
-                atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
-            }
-        }
-        __syncthreads();
-
-        const int nd = (int)ndirty;
-        for (int r = threadIdx.x; r < n; r += blockDim.x) {  // intensity of the cell's winner
-            const uint4 q = __ldg(rec + r);
-            const unsigned local = q.x & 0xFFFFu;
-            if ((int)q.y > 0 &&
-                key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z)))
-                img[local * planes + zn] = q.w;
-        }
-        for (int w = threadIdx.x; w < nd * planes; w += blockDim.x) {
-            const int d = w / planes, k = w - d * planes;
-            unsigned *slot = img + dirty[d] * planes + k;
-            if (k < zn) {
-                const unsigned raw = *slot;
-                if (raw) *slot = __float_as_uint(slice_value(__uint_as_float(raw), p.z_div, k));
-            } else if (k == zn + 1) {
-                const unsigned c = *slot;
-                *slot = __float_as_uint(__ldg(lut + (c < 31u ? c : 31u)));
-            }
-        }
-        fence_proxy_async_smem();
-        __syncthreads();
-
-        if (bulk) {
-            if (threadIdx.x == 0) { bulk_store(dst, img, bytes); bulk_commit(); bulk_wait_read_all(); }
         } else {
-            for (int w = threadIdx.x; w < ncell * planes; w += blockDim.x) dst[w] = __uint_as_float(img[w]);
-        }
-        __syncthreads();
+            // Earlier (empty-tile) bulk stores may still be reading the image: wait before touching it.
+            if (tid == 0) bulk_wait_read_all();
+            __syncthreads();
 
-        for (int w = threadIdx.x; w < nd * planes; w += blockDim.x) {
-            const int d = w / planes, k = w - d * planes;
-            img[dirty[d] * planes + k] = 0u;
+            // accumulate
+            for (int r = tid; r < n0; r += kTileThreads) {
+                const uint4 q = (r == tid) ? q0 : __ldg(rec0 + r);
+                const unsigned local = q.x & 0xFFFFu, Z = q.x >> 16;
+                unsigned *cellw = img + local * planes;
+                if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(&ndirty, 1u)] = local;
+                if ((int)q.y > 0) {  // h > 0: the reference's maps start at 0 and update on strict '>'
+                    atomicMax(cellw + Z, q.y);
+                    atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
+                }
+            }
+            __syncthreads();
+
+            // finalise the touched cells in place
+            const int nd = (int)ndirty;
+            for (int r = tid; r < n0; r += kTileThreads) {  // intensity of each cell's winner
+                const uint4 q = (r == tid) ? q0 : __ldg(rec0 + r);
+                const unsigned local = q.x & 0xFFFFu;
+                if ((int)q.y > 0 &&
+                    key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z)))
+                    img[local * planes + zn] = q.w;
+            }
+            for (int d = warp; d < nd; d += kWarps) {  // one warp per touched cell, lanes over planes
+                unsigned *cellw = img + dirty[d] * planes;
+                for (int k = lane; k < planes; k += 32) {
+                    if (k < zn) {
+                        const unsigned raw = cellw[k];
+                        if (raw) cellw[k] = __float_as_uint(slice_value(__uint_as_float(raw), p.z_div, k));
+                    } else if (k == zn + 1) {
+                        const unsigned c = cellw[k];
+                        cellw[k] = __float_as_uint(__ldg(lut + (c < 31u ? c : 31u)));
+                    }
+                }
+            }
+            fence_proxy_async_smem();
+            __syncthreads();
+
+            // store, then re-zero only what was touched once the bulk read of the image is done
+            if (bulk) {
+                if (tid == 0) { bulk_store(dst, img, bytes); bulk_commit(); bulk_wait_read_all(); }
+            } else {
+                for (int w = tid; w < ncell * planes; w += kTileThreads) dst[w] = __uint_as_float(img[w]);
+            }
+            __syncthreads();
+            for (int d = warp; d < nd; d += kWarps) {
+                const unsigned local = dirty[d];
+                for (int k = lane; k < planes; k += 32) img[local * planes + k] = 0u;
+                if (lane == 0) key[local] = 0ull;
+            }
+            if (tid == 0) ndirty = 0;
+            fence_proxy_async_smem();
+            __syncthreads();
         }
-        for (int d = threadIdx.x; d < nd; d += blockDim.x) key[dirty[d]] = 0ull;
-        if (threadIdx.x == 0) ndirty = 0;
-        fence_proxy_async_smem();
-        __syncthreads();
+        rec0 = rec1; n0 = n1; q0 = q1;
+        rec1 = rec2; n1 = n2;
     }
-    if (threadIdx.x == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
+    if (tid == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -402,6 +425,27 @@ atomic_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPa
 }
 
 // ------------------------------------------------------------------------------------------------
+// Debug / test hook: the per-point decisions, so tests can compare them one by one with the oracle.
+//   cell[i]      output cell of point i, or -1 if the gate rejects it
+//   pix[i]       front-view pixel through the production path (float fast path + exact fallback), or -1
+//   pix_exact[i] the same through the all-double evaluation
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kPointThreads)
+point_keys_kernel(const float4 *__restrict__ pts, int n, ViewParams p, int *__restrict__ cell,
+                  int *__restrict__ pix, int *__restrict__ pix_exact)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 pt = load_point(pts + i);
+        const CellHit c = classify(pt, p);
+        cell[i] = c.keep ? (int)c.cell : -1;
+        if (p.want_front) {
+            pix[i] = c.keep ? front_pixel(pt, p) : -1;
+            pix_exact[i] = c.keep ? front_pixel_exact(pt, p) : -1;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
 static inline int point_blocks(int max_points)
@@ -460,6 +504,13 @@ int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const Vie
 {
     dim3 grid(point_blocks(p.front_pixels), batch);
     front_finalize_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, fv_winner, front);
+    return 1;
+}
+
+int launch_point_keys(const float4 *pts, int n, const ViewParams &p, int *cell, int *pix, int *pix_exact, cudaStream_t s)
+{
+    if (n <= 0) return 0;
+    point_keys_kernel<<<point_blocks(n), kPointThreads, 0, s>>>(pts, n, p, cell, pix, pix_exact);
     return 1;
 }
 

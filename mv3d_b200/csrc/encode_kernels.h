@@ -22,6 +22,7 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
 int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch,
                           unsigned *fv_winner, float *front, cudaStream_t s);
+int launch_point_keys(const float4 *pts, int n, const ViewParams &p, int *cell, int *pix, int *pix_exact, cudaStream_t s);
 int launch_fill_zero(float *dst, size_t count, int sm_count, cudaStream_t s);
 int launch_atomic_scatter(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
                           float *top, unsigned long long *cellkey, unsigned *fv_winner, cudaStream_t s);

@@ -94,6 +94,9 @@ struct mv3d_ctx {
     HostSlot slots[kSlots];  // used by mv3d_encode_batch_host
     long long launches = 0;
     size_t tile_bytes_target = 0;
+    int sub_batch = 0;                    // sweeps per pipeline stage of the tile strategy (0 = no pipelining)
+    cudaStream_t side_stream = nullptr;   // runs the point passes ahead of the tile kernel
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_ready[kMaxBatchPerLaunch] = {nullptr};
     std::mutex mu;
 };
 
@@ -163,7 +166,19 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     ctx->sm_count = prop.multiProcessorCount;
     ctx->smem_optin = prop.sharedMemPerBlockOptin;
     const char *tb = getenv("MV3D_TILE_BYTES");
-    ctx->tile_bytes_target = tb ? (size_t)strtoull(tb, nullptr, 10) : (size_t)(44 * 1024);
+    ctx->tile_bytes_target = tb ? (size_t)strtoull(tb, nullptr, 10) : (size_t)(36 * 1024);
+    const char *sb = getenv("MV3D_SUB_BATCH");
+    ctx->sub_batch = sb ? atoi(sb) : 0;  // measured on B200: two-stream pipelining loses to one stream (profiles/)
+    bool ok = cudaStreamCreateWithFlags(&ctx->side_stream, cudaStreamNonBlocking) == cudaSuccess &&
+              cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) == cudaSuccess &&
+              cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; ok && i < kMaxBatchPerLaunch; i++)
+        ok = cudaEventCreateWithFlags(&ctx->ev_ready[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok) {
+        fail("mv3d_ctx_create: cannot create the pipeline stream/events: %s", cudaGetErrorString(cudaGetLastError()));
+        delete ctx;
+        return -1;
+    }
     float lut[kDensityLutSize];
     build_density_lut(lut);
     if (cudaMalloc(&ctx->lut, sizeof(lut)) != cudaSuccess ||
@@ -188,6 +203,10 @@ extern "C" void mv3d_ctx_destroy(mv3d_ctx *ctx)
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     if (ctx->lut) cudaFree(ctx->lut);
+    if (ctx->side_stream) cudaStreamDestroy(ctx->side_stream);
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    for (auto e : ctx->ev_ready) if (e) cudaEventDestroy(e);
     for (auto &t : ctx->timed) { cudaEventDestroy(t.start); cudaEventDestroy(t.stop); }
     for (auto e : ctx->event_pool) cudaEventDestroy(e);
     delete ctx;
@@ -266,7 +285,7 @@ static bool tile_feasible(const mv3d_ctx *ctx, const mv3d_top_params *tp)
     if (!tp || tp->zn > 65535) return false;
     const int planes = tp->zn + 2;
     const int t = pick_tile_cells(ctx, planes, (long long)tp->xn * tp->yn);
-    const size_t smem = (((size_t)t * planes * 4 + 15) & ~(size_t)15) + (size_t)t * 12 + 8192 + 64;
+    const size_t smem = (((size_t)t * planes * 4 + 15) & ~(size_t)15) + (size_t)t * 12 + 64;
     return smem <= ctx->smem_optin;
 }
 
@@ -309,6 +328,7 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
         if (len >= 16777216.0) return fail("front view of %g floats exceeds the reference's exact float index range", len);
         p.rad_to_deg = (float)(180 / 3.141596);  // sic, LidarTopAndFrontPreprocess.c:36
         p.phi_div = fp->phi_div; p.theta_div = fp->theta_div;
+        p.phi_scale = p.rad_to_deg / fp->phi_div; p.theta_scale = p.rad_to_deg / fp->theta_div;
         p.r_size_f = fp->r_size; p.c_size_f = fp->c_size;
         p.rn = (int)fp->r_size; p.cn = (int)fp->c_size; p.fn = (int)fp->f_size;
         p.center_c = (int)(fp->c_size / 2);  // :37
@@ -388,12 +408,44 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
         uint4 *binned = static_cast<uint4 *>(ws.binned.ptr);
         unsigned *tcount = static_cast<unsigned *>(ws.tile_count.ptr), *toff = static_cast<unsigned *>(ws.tile_off.ptr);
         const int grid_blocks = blocks_per_sm * ctx->sm_count;
-        timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, winners, s); });
-        timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
-        timed_launch(ctx, K_BIN, s, [&] { return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s); });
-        timed_launch(ctx, K_TILE_BUILD, s, [&] {
-            return launch_tile_build(binned, toff, offs, p, ctx->lut, top_dev, batch, grid_blocks, s);
-        });
+        // Sub-batch pipeline: the point passes (classify -> scan -> bin) of sub-batch j+1 run on a side stream
+        // while the memory-bound tile kernel of sub-batch j streams its output on the caller's stream.
+        const int sub = (ctx->sub_batch > 0 && ctx->sub_batch < batch && ctx->side_stream) ? ctx->sub_batch : batch;
+        const bool piped = sub < batch;
+        cudaStream_t sp = piped ? ctx->side_stream : s;
+        if (piped) {
+            CUDA_TRY(cudaEventRecord(ctx->ev_fork, s));
+            CUDA_TRY(cudaStreamWaitEvent(sp, ctx->ev_fork, 0));
+        }
+        for (int j0 = 0, j = 0; j0 < batch; j0 += sub, j++) {
+            const int nb = (batch - j0 < sub) ? batch - j0 : sub;
+            FrameOffsets so;
+            memset(&so, 0, sizeof(so));
+            int sub_max = 0;
+            for (int i = 0; i <= nb; i++) so.off[i] = offs.off[j0 + i];
+            for (int i = 0; i < nb; i++) sub_max = (so.off[i + 1] - so.off[i] > sub_max) ? so.off[i + 1] - so.off[i] : sub_max;
+            unsigned *tc = tcount + (size_t)j0 * (p.tiles_per_frame + 1), *to = toff + (size_t)j0 * (p.tiles_per_frame + 1);
+            unsigned *win = winners ? winners + (size_t)j0 * p.front_pixels : nullptr;
+            timed_launch(ctx, K_CLASSIFY, sp, [&] { return launch_classify(pts, so, p, nb, sub_max, keys, tc, win, sp); });
+            timed_launch(ctx, K_TILE_SCAN, sp, [&] { return launch_tile_scan(tc, to, p.tiles_per_frame, nb, sp); });
+            timed_launch(ctx, K_BIN, sp, [&] { return launch_bin(pts, so, p, nb, sub_max, keys, to, binned, sp); });
+            if (piped) {
+                CUDA_TRY(cudaEventRecord(ctx->ev_ready[j], sp));
+                CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_ready[j], 0));
+            }
+            float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
+            timed_launch(ctx, K_TILE_BUILD, s, [&] {
+                return launch_tile_build(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
+            });
+        }
+        if (piped) {
+            if (p.want_front && p.front_pixels > 0)
+                timed_launch(ctx, K_FRONT_FINALIZE, sp, [&] { return launch_front_finalize(pts, offs, p, batch, winners, front_dev, sp); });
+            CUDA_TRY(cudaEventRecord(ctx->ev_join, sp));
+            CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_join, 0));
+            CUDA_TRY(cudaGetLastError());
+            return 0;
+        }
     } else if (p.want_top && cells > 0) {
         if (ensure(ws.cellkey, (size_t)batch * cells * 8, false, s)) return -1;
         unsigned long long *cellkey = static_cast<unsigned long long *>(ws.cellkey.ptr);
@@ -459,6 +511,22 @@ extern "C" int mv3d_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, con
     const int strat = mv3d_resolve_strategy(ctx, tp, strategy);
     return encode_dev_locked(ctx, ctx->ws, points_dev, offsets_host, batch, top_dev, front_dev, p, strat,
                              static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int num, const mv3d_top_params *tp,
+                                     const mv3d_front_params *fp, int semantics, int *cell_dev, int *pix_dev,
+                                     int *pix_exact_dev, void *stream)
+{
+    if (!ctx) return fail("mv3d_debug_point_keys: ctx is NULL");
+    ViewParams p;
+    if (make_params(ctx, tp, fp, true, fp != nullptr, semantics, &p)) return -1;
+    if (!cell_dev || (fp && (!pix_dev || !pix_exact_dev))) return fail("mv3d_debug_point_keys: output pointer is NULL");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    ctx->launches += launch_point_keys(reinterpret_cast<const float4 *>(points_dev), num, p, cell_dev, pix_dev,
+                                       pix_exact_dev, static_cast<cudaStream_t>(stream));
+    CUDA_TRY(cudaGetLastError());
+    return 0;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -26,6 +26,7 @@ struct ViewParams {
     float z_span;                 // z_MAX - z_MIN, rounded to float [TF:185]
     float rad_to_deg;             // (float)(180/3.141596) [TF:36]
     float phi_div, theta_div;
+    float phi_scale, theta_scale; // rad_to_deg / div in float: only for the approximate fast path below
     float r_size_f, c_size_f;     // the float bounds of TF:176
     int rn, cn, fn, center_r, center_c;
     int front_pixels;             // rn*cn
@@ -97,16 +98,54 @@ __device__ __forceinline__ uint32_t cell_key_index(unsigned long long key)
     return 0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull);
 }
 
+// Angular bin (int)(atan2(num, den) * RAD_TO_DEG / DIV), the reference's double expression [TF:173-174].
+__device__ __forceinline__ int angle_bin_exact(double num, double den, float rad_to_deg, float div)
+{
+    return cvtt_f64(__ddiv_rn(__dmul_rn(atan2(num, den), (double)rad_to_deg), (double)div));
+}
+
+// Same bin from single-precision arithmetic, when that is provably enough. The float quotient qf differs from
+// the reference's double value by at most |q|*4e-7 + |scale|*0.6e-7 (2-ulp atan2f, <=1.25-ulp sqrt/arguments,
+// two roundings for the scale); the bin is accepted only if qf is at least eps = |qf|*4e-6 + |scale|*1e-6
+// (about 10x that bound) away from every integer, where truncation cannot differ. Otherwise the caller takes
+// the exact double path. About 0.1 % of points do; the result is bit-identical either way.
+__device__ __forceinline__ bool angle_bin_fast(float num, float den, float scale, int &bin)
+{
+    const float qf = __fmul_rn(atan2f(num, den), scale);
+    const float eps = fabsf(qf) * 4e-6f + fabsf(scale) * 1e-6f;
+    if (!(fabsf(qf) < 1.0e6f) || fabsf(qf - rintf(qf)) <= eps) return false;
+    bin = __float2int_rz(qf);
+    return true;
+}
+
 // Front-view pixel (linear index r_coord*C + c_coord) of a point that passed the BEV gate, or -1 when the
-// reference would not store it in bounds. Double arithmetic on promoted floats [TF:173-179]; the reference's
-// inclusive upper bounds are kept, so c_coord == C aliases pixel (r_coord+1, 0) exactly as its linear index
-// does, and anything at or beyond R*C (the reference's out-of-bounds store) is dropped.
+// reference would not store it in bounds. The reference's inclusive upper bounds are kept, so c_coord == C
+// aliases pixel (r_coord+1, 0) exactly as its linear index does, and anything at or beyond R*C (the
+// reference's out-of-bounds store) is dropped.
 __device__ __forceinline__ int front_pixel(const float4 &pt, const ViewParams &p)
 {
-    const double dx = (double)pt.x, dy = (double)pt.y, dz = (double)pt.z;
+    int R, C;
+    const float planar_f = sqrtf(__fadd_rn(__fmul_rn(pt.x, pt.x), __fmul_rn(pt.y, pt.y)));
+    if (!angle_bin_fast(pt.z, planar_f, p.phi_scale, R)) {
+        const double dx = (double)pt.x, dy = (double)pt.y;
+        const double planar = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+        R = angle_bin_exact((double)pt.z, planar, p.rad_to_deg, p.phi_div);
+    }
+    if (!angle_bin_fast(pt.y, pt.x, p.theta_scale, C))
+        C = angle_bin_exact((double)pt.y, (double)pt.x, p.rad_to_deg, p.theta_div);
+    const long long r = (long long)R + p.center_r, c = (long long)C + p.center_c;
+    if (!((float)r <= p.r_size_f && (float)c <= p.c_size_f && r >= 0 && c >= 0)) return -1;
+    const long long pix = r * p.cn + c;
+    return (pix < (long long)p.front_pixels) ? (int)pix : -1;
+}
+
+// The all-double evaluation of the same pixel (no fast path); used by the debug entry point to cross-check.
+__device__ __forceinline__ int front_pixel_exact(const float4 &pt, const ViewParams &p)
+{
+    const double dx = (double)pt.x, dy = (double)pt.y;
     const double planar = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
-    const int R = cvtt_f64(__ddiv_rn(__dmul_rn(atan2(dz, planar), (double)p.rad_to_deg), (double)p.phi_div));
-    const int C = cvtt_f64(__ddiv_rn(__dmul_rn(atan2(dy, dx), (double)p.rad_to_deg), (double)p.theta_div));
+    const int R = angle_bin_exact((double)pt.z, planar, p.rad_to_deg, p.phi_div);
+    const int C = angle_bin_exact(dy, dx, p.rad_to_deg, p.theta_div);
     const long long r = (long long)R + p.center_r, c = (long long)C + p.center_c;
     if (!((float)r <= p.r_size_f && (float)c <= p.c_size_f && r >= 0 && c >= 0)) return -1;
     const long long pix = r * p.cn + c;

@@ -95,6 +95,22 @@ class ViewEncoder:
             raise RuntimeError("mv3d_encode_batch_dev: " + _lib.last_error())
         return (top_out if want_top else None), front_out
 
+    def debug_point_keys(self, points, top: TopParams, front: FrontParams | None = None):
+        """Test hook: per-point (cell, front pixel, front pixel by the all-double path) as int32 CUDA tensors."""
+        import torch
+        n = points.shape[0]
+        cell = torch.empty(n, dtype=torch.int32, device=points.device)
+        pix = torch.empty(n, dtype=torch.int32, device=points.device) if front is not None else None
+        pix_exact = torch.empty(n, dtype=torch.int32, device=points.device) if front is not None else None
+        rc = self._lib.mv3d_debug_point_keys(
+            self._ctx, points.data_ptr(), n, ctypes.byref(_top_c(top)),
+            ctypes.byref(_front_c(front)) if front is not None else None, self.semantics, cell.data_ptr(),
+            pix.data_ptr() if pix is not None else None, pix_exact.data_ptr() if pix_exact is not None else None,
+            ctypes.c_void_p(torch.cuda.current_stream(points.device).cuda_stream))
+        if rc != 0:
+            raise RuntimeError("mv3d_debug_point_keys: " + _lib.last_error())
+        return cell, pix, pix_exact
+
     # -- host buffers (H2D + encode + D2H, pipelined inside the library) -----------------------------
     def encode_host(self, points: np.ndarray, offsets, top: TopParams, front: FrontParams | None = None,
                     top_out: np.ndarray | None = None, front_out: np.ndarray | None = None, want_top: bool = True):

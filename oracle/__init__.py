@@ -95,6 +95,22 @@ def top_and_front_maps(raw, top, front, impl: str = "restated"):
     return out, fbuf[:n].reshape(front.shape).copy()
 
 
+def point_keys(raw, top, front=None, semantics: str = "topfront"):
+    """Per-point (cell, front pixel) decisions of the restatement; -1 = rejected / not stored."""
+    raw = _points(raw)
+    n = raw.shape[0]
+    cell = np.empty(n, dtype=np.int32)
+    pix = np.empty(n, dtype=np.int32) if front is not None else None
+    fn = _lib(RESTATED_SO).oracle_point_keys
+    fn.argtypes = [_vp, _ci, _ci] + [_cf] * 6 + [_ci] * 3 + [_cf] * 4 + [_vp, _vp]
+    fn(raw.ctypes.data, n, {"top": 0, "topfront": 1}[semantics], top.x_min, top.y_min, top.z_min,
+       top.x_div, top.y_div, top.z_div, top.xn, top.yn, top.zn,
+       front.phi_div if front else 1.0, front.theta_div if front else 1.0,
+       float(front.cn) if front else 1.0, float(front.rn) if front else 1.0,
+       cell.ctypes.data, pix.ctypes.data if pix is not None else None)
+    return cell, pix
+
+
 def density_table() -> np.ndarray:
     out = np.zeros(32, dtype=np.float32)
     fn = _lib(RESTATED_SO).oracle_density_table

@@ -206,6 +206,39 @@ int oracle_createTopAndFrontMaps(const void *raw_data, int num, void *top_data, 
     return encode((const float *)raw_data, num, (float *)top_data, (float *)front_data, &tp, &fp, QUANT_FLOOR);
 }
 
+/* Per-point decisions (test hook): cell[i] = (X-1)*yn + (Y-1) or -1 when the gate rejects point i;
+ * pix[i] = r_coord*C + c_coord of the front-view store, or -1 when the reference would not store in bounds.
+ * mode: 0 = createTopMaps quantisation (truncate), 1 = createTopAndFrontMaps (floor). pix may be NULL. */
+void oracle_point_keys(const void *raw_data, int num, int mode,
+                       float x_MIN, float y_MIN, float z_MIN, float x_DIVISION, float y_DIVISION, float z_DIVISION,
+                       int X_SIZE, int Y_SIZE, int Z_SIZE, float phi_DIVISION, float theta_DIVISION,
+                       float C_SIZE, float R_SIZE, int *cell, int *pix)
+{
+    const float *pts = (const float *)raw_data;
+    const float rad_to_deg = (float)(180 / 3.141596);
+    const int center_c = cvtt_f32(C_SIZE / 2), center_r = cvtt_f32(R_SIZE / 2);
+    const long npix = (long)cvtt_f32(C_SIZE) * (long)cvtt_f32(R_SIZE);
+    for (int i = 0; i < num; i++) {
+        const float x = pts[4 * (size_t)i], y = pts[4 * (size_t)i + 1], z = pts[4 * (size_t)i + 2];
+        const int X = quantise(x, x_MIN, x_DIVISION, mode);
+        const int Y = quantise(y, y_MIN, y_DIVISION, mode);
+        const int Z = quantise(z, z_MIN, z_DIVISION, mode);
+        const int keep = (X >= 1 && Y >= 1 && Z >= 0 && X < X_SIZE && Y < Y_SIZE && Z < Z_SIZE);
+        cell[i] = keep ? (X - 1) * Y_SIZE + (Y - 1) : -1;
+        if (!pix) continue;
+        pix[i] = -1;
+        if (!keep) continue;
+        const double dx = x, dy = y, dz = z;
+        const int R = cvtt_f64(atan2(dz, sqrt(dx * dx + dy * dy)) * (double)rad_to_deg / (double)phi_DIVISION);
+        const int C = cvtt_f64(atan2(dy, dx) * (double)rad_to_deg / (double)theta_DIVISION);
+        const long r = (long)R + center_r, c = (long)C + center_c;
+        if ((float)r <= R_SIZE && (float)c <= C_SIZE && r >= 0 && c >= 0) {
+            const long q = r * (long)cvtt_f32(C_SIZE) + c;
+            if (q < npix) pix[i] = (int)q;
+        }
+    }
+}
+
 /* The 32 distinct density values (count 0..31; anything above is 1.0f), for host-side tests. */
 void oracle_density_table(float *out32)
 {

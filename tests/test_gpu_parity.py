@@ -161,6 +161,31 @@ def test_config5_dense_cloud(torch_cuda, oracle_mod, strategy):
     enc.close()
 
 
+@pytest.mark.parametrize("semantics", ["top", "topfront"])
+def test_per_point_decisions_20M(torch_cuda, oracle_mod, semantics):
+    """Every point's gate/cell and front-view pixel, one by one, on 20 M random points: the production
+    arithmetic (float fast path + exact fallback) == the all-double GPU path == the CPU oracle."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.params import FrontParams
+    from mv3d_b200.sweeps import uniform_in_box
+    enc = ViewEncoder(0, semantics=semantics)
+    fronts = [KITTI_FRONT_64x512, FrontParams(-20.0, 20.0, -45.0, 45.0, 0.1, 0.2)]
+    total = mism = 0
+    for seed in range(10):
+        pts = uniform_in_box(2_000_000, KITTI_PAPER_TOP, seed=100 + seed, margin=1.0)
+        if seed % 2:
+            pts[:, :3] = np.round(pts[:, :3], 1)  # coordinates sitting on cell and bin boundaries
+        front = fronts[seed % 2]
+        cell, pix, pix_exact = enc.debug_point_keys(torch.from_numpy(pts).cuda(), KITTI_PAPER_TOP, front)
+        ecell, epix = oracle_mod.point_keys(pts, KITTI_PAPER_TOP, front, semantics)
+        cell, pix, pix_exact = cell.cpu().numpy(), pix.cpu().numpy(), pix_exact.cpu().numpy()
+        total += len(pts)
+        mism += np.count_nonzero(cell != ecell) + np.count_nonzero(pix != epix) + np.count_nonzero(pix_exact != epix)
+    assert mism == 0, f"{mism} per-point mismatches in {total} points"
+    enc.close()
+
+
 def test_host_batch_pinned(torch_cuda, oracle_mod):
     """The pipelined host entry point with page-locked buffers (what bench.py's e2e leg times)."""
     from mv3d_b200.encoder import ViewEncoder, pinned_empty
