@@ -77,7 +77,9 @@ enum {
 enum {
     MV3D_STRATEGY_AUTO = 0,
     MV3D_STRATEGY_ATOMIC = 1, /* zero-fill, then order-preserving integer atomics straight into the output in HBM/L2 */
-    MV3D_STRATEGY_TILE = 2    /* bin points by output tile, reduce in shared memory, one bulk (TMA) store per tile */
+    MV3D_STRATEGY_TILE = 2,   /* bin points by output tile, reduce in shared memory, one bulk (TMA) store per tile */
+    MV3D_STRATEGY_PATCH = 3   /* zero-fill by TMA on a side stream while points are binned; then reduce per tile in
+                                 shared memory and overwrite only the sectors that hold touched cells */
 };
 
 typedef struct mv3d_ctx mv3d_ctx;
@@ -130,7 +132,8 @@ int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int num, const
                           const mv3d_front_params *fp, int semantics, int *cell_dev, int *pix_dev,
                           int *pix_exact_dev, void *stream);
 
-/* The strategy MV3D_STRATEGY_AUTO resolves to for a parameter set (MV3D_STRATEGY_ATOMIC or _TILE). */
+/* The strategy a request resolves to for a parameter set (tile strategies fall back to _ATOMIC when a tile
+ * cannot fit shared memory). AUTO additionally switches _TILE to _PATCH per call for large batches. */
 int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy);
 
 /* Library / build identification, e.g. "mv3d_encode 0.1 sm_100a". */

@@ -61,8 +61,8 @@ class FrontParamsC(ctypes.Structure):
 
 
 SEM_TOP, SEM_TOPFRONT = 0, 1
-STRATEGY_AUTO, STRATEGY_ATOMIC, STRATEGY_TILE = 0, 1, 2
-STRATEGIES = {"auto": STRATEGY_AUTO, "atomic": STRATEGY_ATOMIC, "tile": STRATEGY_TILE}
+STRATEGY_AUTO, STRATEGY_ATOMIC, STRATEGY_TILE, STRATEGY_PATCH = 0, 1, 2, 3
+STRATEGIES = {"auto": STRATEGY_AUTO, "atomic": STRATEGY_ATOMIC, "tile": STRATEGY_TILE, "patch": STRATEGY_PATCH}
 
 # Every symbol include/mv3d_encode.h declares (tests check the built library exports exactly these).
 EXPORTED_SYMBOLS = (

@@ -10,6 +10,13 @@
 //      touched cells in place, and writes the tile -- zeros included -- with ONE bulk async (TMA) store.
 //      Every output byte is written exactly once and never read; HBM traffic = the algorithmic bytes.
 //
+//  PATCH           fill_tma (side stream)  ||  classify -> scan -> bin ; then warp_patch per chunk of sweeps
+//      The zero-fill of the output needs no point data and almost no SM resources when it is done by bulk
+//      async (TMA) stores from one all-zero shared-memory buffer, so it runs beside the compute/latency-bound
+//      point passes instead of after them. Points are binned by small tiles; one WARP then owns a tile:
+//      it reduces the tile's records in a private shared-memory image and overwrites only the 32-byte
+//      sectors of the (already zero) output that hold a touched cell.
+//
 //  ATOMIC          fill_zero -> atomic_scatter -> atomic_finalize
 //      Zero-fill the output, reduce with global atomics straight into the output cells (tagged raw values),
 //      then a second pass over the points converts the touched slots. No binning; relies on L2 atomics.
@@ -42,6 +49,30 @@ __device__ __forceinline__ void bulk_store(void *gdst, const void *ssrc, uint32_
 {
     asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;"
                  :: "l"(gdst), "r"(smem_addr(ssrc)), "r"(bytes) : "memory");
+}
+// Same, with an L2 eviction policy: the zero-fill stream is written once and never read by this library, so it
+// should leave L2 first and not push the point/bin scratch out.
+__device__ __forceinline__ uint64_t l2_policy_evict_first()
+{
+    uint64_t pol;
+    asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ void bulk_store_hint(void *gdst, const void *ssrc, uint32_t bytes, uint64_t policy)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group.L2::cache_hint [%0], [%1], %2, %3;"
+                 :: "l"(gdst), "r"(smem_addr(ssrc)), "r"(bytes), "l"(policy) : "memory");
+}
+// Wait until all committed bulk stores of this thread are complete (writes performed, not only the smem read).
+__device__ __forceinline__ void bulk_wait_all()
+{
+    asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+}
+// Wait until at most N committed bulk stores of this thread are still pending (full completion).
+template <int N>
+__device__ __forceinline__ void bulk_wait_pending()
+{
+    asm volatile("cp.async.bulk.wait_group %0;" :: "n"(N) : "memory");
 }
 __device__ __forceinline__ void bulk_commit()
 {
@@ -320,6 +351,168 @@ tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
     if (tid == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
 }
 
+
+// ------------------------------------------------------------------------------------------------
+// PATCH strategy, zero-fill: bulk async (TMA) stores from one all-zero shared-memory buffer. One elected thread
+// per CTA issues the stores, so the kernel holds one warp and 16 KB of shared memory per CTA and leaves the SMs
+// to the point passes running beside it on another stream.
+// ------------------------------------------------------------------------------------------------
+constexpr int kFillThreads = 32;
+constexpr uint32_t kFillChunk = 16384;  // bytes per bulk store
+__global__ void __launch_bounds__(kFillThreads) fill_tma_kernel(float *__restrict__ dst, size_t count, int max_pending)
+{
+    __shared__ __align__(128) float4 zeros[kFillChunk / 16];
+    for (int w = threadIdx.x; w < (int)(kFillChunk / 16); w += kFillThreads) zeros[w] = make_float4(0.f, 0.f, 0.f, 0.f);
+    fence_proxy_async_smem();
+    __syncthreads();
+    // head (to 16-byte alignment) and tail by plain stores, body by bulk stores
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(dst);
+    size_t head = ((16 - (addr & 15)) & 15) / 4;
+    if (head > count) head = count;
+    const size_t body_bytes = ((count - head) * 4) & ~(size_t)15;
+    char *body = reinterpret_cast<char *>(dst + head);
+    if (blockIdx.x == 0) {
+        const size_t tail0 = head + body_bytes / 4;
+        if (threadIdx.x < head) dst[threadIdx.x] = 0.0f;
+        if (threadIdx.x < count - tail0) dst[tail0 + threadIdx.x] = 0.0f;
+    }
+    if (threadIdx.x == 0) {
+        const uint64_t pol = l2_policy_evict_first();
+        const size_t nchunk = (body_bytes + kFillChunk - 1) / kFillChunk;
+        for (size_t c = blockIdx.x; c < nchunk; c += gridDim.x) {
+            const size_t off = c * kFillChunk;
+            const uint32_t bytes = (uint32_t)((body_bytes - off < kFillChunk) ? body_bytes - off : kFillChunk);
+            bulk_store_hint(body + off, zeros, bytes, pol);
+            bulk_commit();
+            // Bound the bytes this SM has in flight: an unbounded queue of bulk stores delays every other
+            // memory request of the kernels running beside the fill.
+            if (max_pending <= 2) bulk_wait_pending<2>();
+            else if (max_pending <= 4) bulk_wait_pending<4>();
+            else if (max_pending <= 8) bulk_wait_pending<8>();
+            else if (max_pending <= 16) bulk_wait_pending<16>();
+        }
+        bulk_wait_all();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// PATCH strategy, reduction: one WARP per tile, persistent warps, tiles taken 32 at a time (lane l reads the bin
+// range of tile 32g+l, empty tiles cost nothing more). Per non-empty tile, warp-synchronous:
+//   accumulate : as in tile_build_kernel, into the warp's private image (shared-memory atomics)
+//   finalise   : touched cells only
+//   write      : for each touched cell, the whole 32-byte sectors of the output that overlap it (clipped to the
+//                tile), taken from the image -- full sectors, so L2 never fetches a partially written one;
+//                everything else in the tile is already zero in memory (fill_tma_kernel)
+//   clean      : re-zero the touched cells
+// ------------------------------------------------------------------------------------------------
+constexpr int kPatchWarps = 8;
+__host__ __device__ inline size_t patch_warp_bytes(int tile_cells, int planes)
+{
+    const size_t img = ((size_t)tile_cells * planes * 4 + 15) & ~(size_t)15;
+    return img + (size_t)tile_cells * 8 + ((((size_t)tile_cells + 1) * 4 + 15) & ~(size_t)15);
+}
+
+__global__ void __launch_bounds__(kPatchWarps * 32)
+warp_patch_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
+                  ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int batch)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    constexpr unsigned kFull = 0xFFFFFFFFu;
+    const int T = p.tile_cells, planes = p.planes, zn = p.zn;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char *mine = smem_raw + (size_t)warp * patch_warp_bytes(T, planes);
+    unsigned *img = reinterpret_cast<unsigned *>(mine);
+    unsigned long long *key = reinterpret_cast<unsigned long long *>(mine + (((size_t)T * planes * 4 + 15) & ~(size_t)15));
+    unsigned *dirty = reinterpret_cast<unsigned *>(key + T);  // dirty[0..T) cells, dirty[T] their number
+    for (int w = lane; w < T * planes; w += 32) img[w] = 0u;
+    for (int w = lane; w < T; w += 32) key[w] = 0ull;
+    if (lane == 0) dirty[T] = 0u;
+    __syncwarp();
+
+    const int tpf = p.tiles_per_frame;
+    const int groups_per_frame = (tpf + 31) >> 5;
+    const int total_groups = batch * groups_per_frame;
+    const long long cells_total = (long long)p.xn * p.yn;
+    const int nwarps = gridDim.x * kPatchWarps;
+    for (int g = blockIdx.x * kPatchWarps + warp; g < total_groups; g += nwarps) {
+        const int f = g / groups_per_frame;
+        const int t0 = (g - f * groups_per_frame) << 5;
+        const unsigned *off = tile_off + (size_t)f * (tpf + 1);
+        unsigned beg = 0, end = 0;
+        if (t0 + lane < tpf) { beg = __ldg(off + t0 + lane); end = __ldg(off + t0 + lane + 1); }
+        unsigned todo = __ballot_sync(kFull, end > beg);
+        const uint4 *frame_rec = binned + offs.off[f];
+        float *frame_top = top + (size_t)f * p.top_frame_floats;
+        while (todo) {
+            const int src = __ffs(todo) - 1;
+            todo &= todo - 1;
+            const unsigned b = __shfl_sync(kFull, beg, src);
+            const int n = (int)(__shfl_sync(kFull, end, src) - b);
+            const uint4 *rec = frame_rec + b;
+            const long long cell0 = (long long)(t0 + src) * T;
+            const int nfl = (int)min((long long)T, cells_total - cell0) * planes;
+            float *dst = frame_top + (size_t)cell0 * planes;
+
+            // accumulate
+            uint4 q0 = make_uint4(0, 0, 0, 0);
+            for (int r = lane; r < n; r += 32) {
+                const uint4 q = __ldg(rec + r);
+                if (r == lane) q0 = q;
+                const unsigned local = q.x & 0xFFFFu, Z = q.x >> 16;
+                unsigned *cellw = img + local * planes;
+                if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(dirty + T, 1u)] = local;
+                if ((int)q.y > 0) {  // h > 0: the reference's maps start at 0 and update on strict '>'
+                    atomicMax(cellw + Z, q.y);
+                    atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
+                }
+            }
+            __syncwarp();
+            const int nd = (int)dirty[T];
+            // intensity of each cell's winner
+            for (int r = lane; r < n; r += 32) {
+                const uint4 q = (r == lane) ? q0 : __ldg(rec + r);
+                const unsigned local = q.x & 0xFFFFu;
+                if ((int)q.y > 0 &&
+                    key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z)))
+                    img[local * planes + zn] = q.w;
+            }
+            // heights and density of the touched cells (lanes over planes; the intensity slot is not touched here)
+            for (int d = 0; d < nd; d++) {
+                unsigned *cellw = img + dirty[d] * planes;
+                for (int k = lane; k < planes; k += 32) {
+                    if (k < zn) {
+                        const unsigned raw = cellw[k];
+                        if (raw) cellw[k] = __float_as_uint(slice_value(__uint_as_float(raw), p.z_div, k));
+                    } else if (k == zn + 1) {
+                        const unsigned c = cellw[k];
+                        cellw[k] = __float_as_uint(__ldg(lut + (c < 31u ? c : 31u)));
+                    }
+                }
+            }
+            __syncwarp();
+            // write the sectors that hold touched cells
+            const long long abs0 = (long long)(reinterpret_cast<uintptr_t>(dst) >> 2);  // tile start, in floats
+            for (int d = 0; d < nd; d++) {
+                const long long a = abs0 + (long long)dirty[d] * planes;
+                int lo = (int)((a & ~7LL) - abs0), hi = (int)(((a + planes - 1) | 7LL) + 1 - abs0);
+                lo = lo < 0 ? 0 : lo;
+                hi = hi > nfl ? nfl : hi;
+                for (int w = lo + lane; w < hi; w += 32) dst[w] = __uint_as_float(img[w]);
+            }
+            __syncwarp();
+            // clean
+            for (int d = 0; d < nd; d++) {
+                const unsigned local = dirty[d];
+                for (int k = lane; k < planes; k += 32) img[local * planes + k] = 0u;
+                if (lane == 0) key[local] = 0ull;
+            }
+            __syncwarp();
+            if (lane == 0) dirty[T] = 0u;
+            __syncwarp();
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Front view: write the whole [R][C][F] image from the per-pixel winners, and clear the winners.
 // ------------------------------------------------------------------------------------------------
@@ -496,6 +689,37 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
     const int total = batch * p.tiles_per_frame;
     const int grid = grid_blocks < total ? grid_blocks : total;
     tile_build_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
+    return 1;
+}
+
+size_t patch_smem_bytes(const ViewParams &p) { return kPatchWarps * patch_warp_bytes(p.tile_cells, p.planes); }
+
+cudaError_t warp_patch_configure(const ViewParams &p, int *blocks_per_sm)
+{
+    const size_t smem = patch_smem_bytes(p);
+    cudaError_t e = cudaFuncSetAttribute(warp_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, warp_patch_kernel, kPatchWarps * 32, smem);
+}
+
+size_t fill_tma_smem_bytes() { return kFillChunk; }
+
+int launch_fill_tma(float *dst, size_t count, int blocks, int max_pending, cudaStream_t s)
+{
+    if (count == 0) return 0;
+    const size_t want = (count * 4 + kFillChunk - 1) / kFillChunk;
+    if ((size_t)blocks > want) blocks = (int)want;
+    fill_tma_kernel<<<blocks < 1 ? 1 : blocks, kFillThreads, 0, s>>>(dst, count, max_pending);
+    return 1;
+}
+
+int launch_warp_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
+                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s)
+{
+    const int groups = batch * ((p.tiles_per_frame + 31) / 32);
+    const int want = (groups + kPatchWarps - 1) / kPatchWarps;
+    const int grid = grid_blocks < want ? grid_blocks : want;
+    warp_patch_kernel<<<grid < 1 ? 1 : grid, kPatchWarps * 32, patch_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, batch);
     return 1;
 }
 

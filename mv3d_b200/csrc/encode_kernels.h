@@ -20,6 +20,12 @@ int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p,
                const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s);
 int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
+size_t patch_smem_bytes(const ViewParams &p);
+cudaError_t warp_patch_configure(const ViewParams &p, int *blocks_per_sm);
+size_t fill_tma_smem_bytes();
+int launch_fill_tma(float *dst, size_t count, int blocks, int max_pending, cudaStream_t s);
+int launch_warp_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
+                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
 int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch,
                           unsigned *fv_winner, float *front, cudaStream_t s);
 int launch_point_keys(const float4 *pts, int n, const ViewParams &p, int *cell, int *pix, int *pix_exact, cudaStream_t s);

@@ -70,10 +70,11 @@ struct HostSlot {
 
 // Kernel classes, in the order mv3d_kernel_name() reports them.
 enum KernelId { K_CLASSIFY = 0, K_TILE_SCAN, K_BIN, K_TILE_BUILD, K_FRONT_FINALIZE, K_FILL_ZERO, K_ATOMIC_SCATTER,
-                K_ATOMIC_FINALIZE, K_COUNT };
+                K_ATOMIC_FINALIZE, K_FILL_TMA, K_WARP_PATCH, K_COUNT };
 static const char *const kKernelNames[K_COUNT] = {"classify_kernel", "tile_scan_kernel", "bin_kernel",
                                                   "tile_build_kernel", "front_finalize_kernel", "fill_zero_kernel",
-                                                  "atomic_scatter_kernel", "atomic_finalize_kernel"};
+                                                  "atomic_scatter_kernel", "atomic_finalize_kernel",
+                                                  "fill_tma_kernel", "warp_patch_kernel"};
 
 struct TimedLaunch {
     cudaEvent_t start, stop;
@@ -94,6 +95,12 @@ struct mv3d_ctx {
     HostSlot slots[kSlots];  // used by mv3d_encode_batch_host
     long long launches = 0;
     size_t tile_bytes_target = 0;
+    size_t patch_tile_bytes = 0;          // tile size of the PATCH strategy (no tile store: smaller tiles, more CTAs)
+    int fill_chunk = 0;                   // sweeps per zero-fill launch of the PATCH strategy
+    int fill_ctas = 0;                    // fill CTAs per SM (one issuing thread each)
+    int fill_pending = 0;                 // bulk stores each fill CTA keeps in flight (> 16: unbounded)
+    size_t smem_per_sm = 0;
+    int patch_min_batch = 0;              // AUTO picks PATCH from this batch size on
     int sub_batch = 0;                    // sweeps per pipeline stage of the tile strategy (0 = no pipelining)
     cudaStream_t side_stream = nullptr;   // runs the point passes ahead of the tile kernel
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_ready[kMaxBatchPerLaunch] = {nullptr};
@@ -167,9 +174,24 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     ctx->smem_optin = prop.sharedMemPerBlockOptin;
     const char *tb = getenv("MV3D_TILE_BYTES");
     ctx->tile_bytes_target = tb ? (size_t)strtoull(tb, nullptr, 10) : (size_t)(36 * 1024);
+    const char *pb = getenv("MV3D_PATCH_TILE_BYTES");
+    ctx->patch_tile_bytes = pb ? (size_t)strtoull(pb, nullptr, 10) : (size_t)6912;
+    const char *fa = getenv("MV3D_FILL_CTAS");
+    ctx->fill_ctas = fa ? atoi(fa) : 2;
+    if (ctx->fill_ctas < 1) ctx->fill_ctas = 1;
+    const char *fpn = getenv("MV3D_FILL_PENDING");
+    ctx->fill_pending = fpn ? atoi(fpn) : 4;
+    ctx->smem_per_sm = prop.sharedMemPerMultiprocessor;
+    const char *fc = getenv("MV3D_FILL_CHUNK");
+    ctx->fill_chunk = fc ? atoi(fc) : 8;
+    if (ctx->fill_chunk < 1) ctx->fill_chunk = 1;
+    const char *pm = getenv("MV3D_PATCH_MIN_BATCH");
+    ctx->patch_min_batch = pm ? atoi(pm) : 1 << 30;
     const char *sb = getenv("MV3D_SUB_BATCH");
     ctx->sub_batch = sb ? atoi(sb) : 0;  // measured on B200: two-stream pipelining loses to one stream (profiles/)
-    bool ok = cudaStreamCreateWithFlags(&ctx->side_stream, cudaStreamNonBlocking) == cudaSuccess &&
+    int prio_lo = 0, prio_hi = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);  // the zero-fill is the long pole of PATCH: never starve it
+    bool ok = cudaStreamCreateWithPriority(&ctx->side_stream, cudaStreamNonBlocking, prio_hi) == cudaSuccess &&
               cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming) == cudaSuccess &&
               cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming) == cudaSuccess;
     for (int i = 0; ok && i < kMaxBatchPerLaunch; i++)
@@ -269,9 +291,9 @@ static bool integral(float v) { return std::isfinite(v) && v == std::floor(v); }
 
 // Tile size for a parameter set: as many whole cells as fit the target, a multiple of 4 cells so every
 // tile is a multiple of 16 bytes (bulk-store granularity) whatever the plane count.
-static int pick_tile_cells(const mv3d_ctx *ctx, int planes, long long cells)
+static int pick_tile_cells(size_t bytes_target, int planes, long long cells)
 {
-    long long t = (long long)(ctx->tile_bytes_target / ((size_t)planes * 4));
+    long long t = (long long)(bytes_target / ((size_t)planes * 4));
     t &= ~3LL;
     if (t < 4) t = 4;
     if (t > 65532) t = 65532;
@@ -280,26 +302,37 @@ static int pick_tile_cells(const mv3d_ctx *ctx, int planes, long long cells)
     return (int)t;
 }
 
-static bool tile_feasible(const mv3d_ctx *ctx, const mv3d_top_params *tp)
+static bool tile_feasible(const mv3d_ctx *ctx, const mv3d_top_params *tp, bool patch)
 {
     if (!tp || tp->zn > 65535) return false;
     const int planes = tp->zn + 2;
-    const int t = pick_tile_cells(ctx, planes, (long long)tp->xn * tp->yn);
-    const size_t smem = (((size_t)t * planes * 4 + 15) & ~(size_t)15) + (size_t)t * 12 + 64;
-    return smem <= ctx->smem_optin;
+    const int t = pick_tile_cells(patch ? ctx->patch_tile_bytes : ctx->tile_bytes_target, planes, (long long)tp->xn * tp->yn);
+    const size_t per = (((size_t)t * planes * 4 + 15) & ~(size_t)15) + (size_t)t * 12 + 64;
+    return (patch ? per * 8 : per) <= ctx->smem_optin;  // PATCH: one image per warp, 8 warps per CTA
 }
 
 extern "C" int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy)
 {
     if (strategy == MV3D_STRATEGY_ATOMIC) return MV3D_STRATEGY_ATOMIC;
     if (!ctx || !tp) return MV3D_STRATEGY_ATOMIC;
-    if (strategy == MV3D_STRATEGY_TILE || strategy == MV3D_STRATEGY_AUTO)
-        return tile_feasible(ctx, tp) ? MV3D_STRATEGY_TILE : MV3D_STRATEGY_ATOMIC;
-    return MV3D_STRATEGY_ATOMIC;
+    if (strategy == MV3D_STRATEGY_PATCH && tile_feasible(ctx, tp, true)) return MV3D_STRATEGY_PATCH;
+    if (!tile_feasible(ctx, tp, false)) return MV3D_STRATEGY_ATOMIC;
+    return MV3D_STRATEGY_TILE;  // AUTO is refined per call by the batch size (see resolve_for_batch)
+}
+
+// AUTO: PATCH (zero-fill on a side stream overlapped with the point passes) pays off once a call carries enough
+// sweeps to pipeline; single sweeps keep the one-pass TILE kernel.
+static int resolve_for_batch(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy, int batch)
+{
+    const int r = mv3d_resolve_strategy(ctx, tp, strategy);
+    if (strategy == MV3D_STRATEGY_AUTO && r == MV3D_STRATEGY_TILE && batch >= ctx->patch_min_batch &&
+        tile_feasible(ctx, tp, true))
+        return MV3D_STRATEGY_PATCH;
+    return r;
 }
 
 static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3d_front_params *fp, bool want_top,
-                       bool want_front, int semantics, ViewParams *out)
+                       bool want_front, int semantics, int strategy, ViewParams *out)
 {
     if (!tp) return fail("top parameters are required (the front view is gated by the bird's-eye-view box)");
     if (semantics != MV3D_SEM_TOP && semantics != MV3D_SEM_TOPFRONT) return fail("unknown semantics %d", semantics);
@@ -315,7 +348,8 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
     p.want_top = want_top ? 1 : 0;
     p.want_front = want_front ? 1 : 0;
     p.top_frame_floats = cells * p.planes;
-    p.tile_cells = pick_tile_cells(ctx, p.planes, cells);
+    p.tile_cells = pick_tile_cells(strategy == MV3D_STRATEGY_PATCH ? ctx->patch_tile_bytes : ctx->tile_bytes_target,
+                                   p.planes, cells);
     p.tiles_per_frame = (int)((cells + p.tile_cells - 1) / p.tile_cells);
     p.z_span = tp->z_max - tp->z_min;  // float subtraction, LidarTopAndFrontPreprocess.c:185
     if (want_front) {
@@ -395,19 +429,66 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
     }
     unsigned *winners = static_cast<unsigned *>(ws.fv_winner.ptr);
 
-    if (p.want_top && cells > 0 && strategy == MV3D_STRATEGY_TILE) {
+    if (p.want_top && cells > 0 && (strategy == MV3D_STRATEGY_TILE || strategy == MV3D_STRATEGY_PATCH)) {
+        const bool patch = strategy == MV3D_STRATEGY_PATCH;
         if (ensure(ws.keys, total * sizeof(uint2) + 16, false, s)) return -1;
         if (ensure(ws.binned, total * sizeof(uint4) + 16, false, s)) return -1;
         const size_t hist = (size_t)batch * (p.tiles_per_frame + 1) * 4;
         if (ensure(ws.tile_count, hist, true, s)) return -1;
         if (ensure(ws.tile_off, hist, false, s)) return -1;
         int blocks_per_sm = 0;
-        CUDA_TRY(tile_build_configure(p, &blocks_per_sm));
-        if (blocks_per_sm < 1) return fail("tile kernel does not fit: %zu bytes of shared memory", tile_smem_bytes(p));
+        if (patch) {
+            CUDA_TRY(warp_patch_configure(p, &blocks_per_sm));
+            // leave shared memory for the fill CTAs that must stay resident beside the patch warps
+            const size_t fill_need = (size_t)ctx->fill_ctas * (fill_tma_smem_bytes() + 1024);
+            const size_t per_cta = patch_smem_bytes(p) + 1024;
+            const int room = ctx->smem_per_sm > fill_need ? (int)((ctx->smem_per_sm - fill_need) / per_cta) : 0;
+            if (blocks_per_sm > room) blocks_per_sm = room;
+        } else {
+            CUDA_TRY(tile_build_configure(p, &blocks_per_sm));
+        }
+        if (blocks_per_sm < 1) return fail("tile kernel does not fit: %zu bytes of shared memory",
+                                           patch ? patch_smem_bytes(p) : tile_smem_bytes(p));
         uint2 *keys = static_cast<uint2 *>(ws.keys.ptr);
         uint4 *binned = static_cast<uint4 *>(ws.binned.ptr);
         unsigned *tcount = static_cast<unsigned *>(ws.tile_count.ptr), *toff = static_cast<unsigned *>(ws.tile_off.ptr);
         const int grid_blocks = blocks_per_sm * ctx->sm_count;
+        if (patch) {
+            // PATCH: the zero-fill of the whole output runs on the side stream as a handful of one-warp-per-SM TMA
+            // kernels (HBM-bound, almost no SM resources) while the point passes (compute/latency-bound) run on the
+            // caller's stream; each chunk of sweeps is then patched as soon as its fill has finished.
+            const int chunk = ctx->fill_chunk;
+            cudaStream_t sf = ctx->side_stream;
+            CUDA_TRY(cudaEventRecord(ctx->ev_fork, s));
+            CUDA_TRY(cudaStreamWaitEvent(sf, ctx->ev_fork, 0));
+            for (int j0 = 0, j = 0; j0 < batch; j0 += chunk, j++) {
+                const int nb = (batch - j0 < chunk) ? batch - j0 : chunk;
+                float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
+                timed_launch(ctx, K_FILL_TMA, sf, [&] {
+                    return launch_fill_tma(top_j, (size_t)nb * (size_t)p.top_frame_floats, ctx->sm_count * ctx->fill_ctas, ctx->fill_pending, sf);
+                });
+                CUDA_TRY(cudaEventRecord(ctx->ev_ready[j], sf));
+            }
+            timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, winners, s); });
+            timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
+            timed_launch(ctx, K_BIN, s, [&] { return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s); });
+            if (p.want_front && p.front_pixels > 0)
+                timed_launch(ctx, K_FRONT_FINALIZE, s, [&] { return launch_front_finalize(pts, offs, p, batch, winners, front_dev, s); });
+            for (int j0 = 0, j = 0; j0 < batch; j0 += chunk, j++) {
+                const int nb = (batch - j0 < chunk) ? batch - j0 : chunk;
+                FrameOffsets so;
+                memset(&so, 0, sizeof(so));
+                for (int i = 0; i <= nb; i++) so.off[i] = offs.off[j0 + i];
+                unsigned *to = toff + (size_t)j0 * (p.tiles_per_frame + 1);
+                float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
+                CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_ready[j], 0));
+                timed_launch(ctx, K_WARP_PATCH, s, [&] {
+                    return launch_warp_patch(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
+                });
+            }
+            CUDA_TRY(cudaGetLastError());
+            return 0;
+        }
         // Sub-batch pipeline: the point passes (classify -> scan -> bin) of sub-batch j+1 run on a side stream
         // while the memory-bound tile kernel of sub-batch j streams its output on the caller's stream.
         const int sub = (ctx->sub_batch > 0 && ctx->sub_batch < batch && ctx->side_stream) ? ctx->sub_batch : batch;
@@ -504,11 +585,11 @@ extern "C" int mv3d_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, con
     if (!ctx) return fail("mv3d_encode_batch_dev: ctx is NULL");
     if (check_offsets(offsets_host, batch)) return -1;
     ViewParams p;
-    if (make_params(ctx, tp, fp, top_dev != nullptr, front_dev != nullptr, semantics, &p)) return -1;
+    const int strat = resolve_for_batch(ctx, tp, strategy, batch);
+    if (make_params(ctx, tp, fp, top_dev != nullptr, front_dev != nullptr, semantics, strat, &p)) return -1;
     if (batch == 0 || (!top_dev && !front_dev)) return 0;
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
-    const int strat = mv3d_resolve_strategy(ctx, tp, strategy);
     return encode_dev_locked(ctx, ctx->ws, points_dev, offsets_host, batch, top_dev, front_dev, p, strat,
                              static_cast<cudaStream_t>(stream));
 }
@@ -519,7 +600,7 @@ extern "C" int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int
 {
     if (!ctx) return fail("mv3d_debug_point_keys: ctx is NULL");
     ViewParams p;
-    if (make_params(ctx, tp, fp, true, fp != nullptr, semantics, &p)) return -1;
+    if (make_params(ctx, tp, fp, true, fp != nullptr, semantics, MV3D_STRATEGY_TILE, &p)) return -1;
     if (!cell_dev || (fp && (!pix_dev || !pix_exact_dev))) return fail("mv3d_debug_point_keys: output pointer is NULL");
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
@@ -539,12 +620,12 @@ extern "C" int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, c
     if (!ctx) return fail("mv3d_encode_batch_host: ctx is NULL");
     if (check_offsets(offsets_host, batch)) return -1;
     ViewParams p;
-    if (make_params(ctx, tp, fp, top_host != nullptr, front_host != nullptr, semantics, &p)) return -1;
+    const int strat = resolve_for_batch(ctx, tp, strategy, 1);  // the host pipeline encodes sweep by sweep
+    if (make_params(ctx, tp, fp, top_host != nullptr, front_host != nullptr, semantics, strat, &p)) return -1;
     if (batch == 0 || (!top_host && !front_host)) return 0;
     if (offsets_host[batch] > offsets_host[0] && !points_host) return fail("points_host is NULL");
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
-    const int strat = mv3d_resolve_strategy(ctx, tp, strategy);
     const size_t top_bytes = (size_t)p.top_frame_floats * 4, front_bytes = (size_t)p.front_frame_floats * 4;
 
     int rc = 0;
