@@ -263,17 +263,21 @@ def run_ours(args):
         enc.encode_host(h_pts, offs, top_p, front_p, top_out=h_top, front_out=h_front)  # warm-up (allocates slots)
         barrier()
         torch.cuda.synchronize()
+        enc.transfer_bytes(reset=True)
         t0 = time.perf_counter()
         for _ in range(args.steps):
             enc.encode_host(h_pts, offs, top_p, front_p, top_out=h_top, front_out=h_front)
         e2e_s = time.perf_counter() - t0
+        h2d_total, d2h_total = enc.transfer_bytes()
         checksum = float(h_top[0, :, :, top_p.zn + 1].sum()) + float(h_front[0].sum())  # touch the result
         if world > 1:
             t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             e2e_s = float(t.item())
         e2e = {"value": world * BATCH * args.steps / e2e_s, "unit": "sweeps/s",
-               "h2d_bytes_per_step": int(h_pts.nbytes), "d2h_bytes_per_step": int(h_top.nbytes + h_front.nbytes),
+               "h2d_bytes_per_step": h2d_total // args.steps, "d2h_bytes_per_step": d2h_total // args.steps,
+               "host_result_bytes_per_step": int(h_top.nbytes + h_front.nbytes),
+               "readback": os.environ.get("MV3D_HOST_READBACK", "compact"),
                "ms_per_step": e2e_s / args.steps * 1e3, "api": "mv3d_encode_batch_host (pinned host buffers)",
                "result_checksum": checksum}
 

@@ -100,9 +100,12 @@ int mv3d_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *off
                           const mv3d_top_params *tp, const mv3d_front_params *fp,
                           int semantics, int strategy, void *stream);
 
-/* Same, with host buffers: host->device copy, encode, device->host copy, pipelined frame by frame over
- * internal streams; returns after the outputs are complete in host memory. Pinned (page-locked) host
- * buffers (mv3d_host_alloc) are DMA'd directly; pageable ones go through the driver's staging path. */
+/* Same, with host buffers, pipelined sweep by sweep over internal streams; returns after the outputs are
+ * complete in host memory. The bird's-eye view is ~95 % zeros, so by default it is read back COMPACT: the
+ * device reports the finished values of the touched cells only and host threads (MV3D_HOST_THREADS, default
+ * min(16, cores)) rebuild the dense tensor in the caller's buffer -- a zero-fill plus a scatter, no encoding
+ * arithmetic on the host. MV3D_HOST_READBACK=dense copies the dense tensor over PCIe instead (pinned buffers
+ * from mv3d_host_alloc are then DMA'd directly, pageable ones go through the driver's staging path). */
 int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, const int *offsets_host, int batch,
                            float *top_host, float *front_host,
                            const mv3d_top_params *tp, const mv3d_front_params *fp,
@@ -114,6 +117,10 @@ void mv3d_host_free(void *p);
 
 /* Kernels launched by this context so far (bench.py's gpu_launches). */
 long long mv3d_ctx_launch_count(const mv3d_ctx *ctx);
+
+/* Bytes the host entry points of this context have moved over PCIe (host->device, device->host) since the last
+ * reset: what bench.py reports as h2d/d2h bytes per step. */
+int mv3d_ctx_transfer_bytes(mv3d_ctx *ctx, unsigned long long *h2d, unsigned long long *d2h, int reset);
 
 /* Optional per-kernel timing for bench.py's roofline: when enabled, CUDA events are recorded on the launching
  * stream around every kernel. mv3d_ctx_kernel_times() waits for the recorded events and reports, per kernel
@@ -131,6 +138,11 @@ int mv3d_ctx_kernel_times(mv3d_ctx *ctx, double *ms_out, long long *launches_out
 int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int num, const mv3d_top_params *tp,
                           const mv3d_front_params *fp, int semantics, int *cell_dev, int *pix_dev,
                           int *pix_exact_dev, void *stream);
+
+/* Test hook (no GPU needed): the host half of the compact read-back used by the host-buffer entry points.
+ * dst[cells][planes] is zero-filled by `threads` host threads, then every entry {cell, planes values}
+ * (planes + 1 words each) is copied to dst[cell]; entries with cell >= cells are ignored. */
+int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n, int threads);
 
 /* The strategy a request resolves to for a parameter set (tile strategies fall back to _ATOMIC when a tile
  * cannot fit shared memory). AUTO additionally switches _TILE to _PATCH per call for large batches. */

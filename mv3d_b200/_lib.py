@@ -13,8 +13,8 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libmv3d_encode.so")
-SOURCES = ["encode_kernels.cu", "mv3d_abi.cu"]
-HEADERS = ["encode_kernels.h", "view_math.cuh", os.path.join("..", "..", "include", "mv3d_encode.h")]
+SOURCES = ["encode_kernels.cu", "mv3d_abi.cu", "host_expand.cu"]
+HEADERS = ["encode_kernels.h", "view_math.cuh", "host_expand.h", os.path.join("..", "..", "include", "mv3d_encode.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
 
@@ -70,7 +70,7 @@ EXPORTED_SYMBOLS = (
     "mv3d_encode_batch_dev", "mv3d_encode_batch_host", "mv3d_host_alloc", "mv3d_host_free",
     "mv3d_ctx_launch_count", "mv3d_resolve_strategy", "mv3d_version",
     "mv3d_ctx_set_profiling", "mv3d_kernel_count", "mv3d_kernel_name", "mv3d_ctx_kernel_times",
-    "mv3d_debug_point_keys",
+    "mv3d_debug_point_keys", "mv3d_debug_expand_compact", "mv3d_ctx_transfer_bytes",
 )
 
 _lib = None
@@ -111,6 +111,8 @@ def load_library() -> ctypes.CDLL:
     lib.mv3d_ctx_kernel_times.argtypes = [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), ci]
     lib.mv3d_debug_point_keys.argtypes = [vp, vp, ci, ctypes.POINTER(TopParamsC), ctypes.POINTER(FrontParamsC), ci,
                                           vp, vp, vp, vp]
+    lib.mv3d_ctx_transfer_bytes.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong), ci]
+    lib.mv3d_debug_expand_compact.argtypes = [vp, ctypes.c_size_t, ci, vp, ctypes.c_uint, ci]
     _lib = lib
     return lib
 

@@ -224,9 +224,17 @@ bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
 // Empty tiles (the majority) skip everything but the store, straight from the all-zero image; a non-empty
 // tile first waits for those in-flight reads of the image before accumulating into it.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kTileThreads)
-tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
-                  ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles)
+// kCompact: instead of storing the dense tile, report the touched cells in a per-sweep list
+//   compact[f] = { cell index [cap] , values [cap][planes] }   (structure of arrays)
+// A tile with n records touches at most n cells, so it owns the slots [beg, beg + n) of its own bin range
+// (tile_off): the first nd hold its touched cells (any order), the rest are marked kNoCell. The list is therefore
+// ordered by tile with no atomics and no scan, and tile_off tells the reader where each tile's slots are. This is
+// what the host-buffer path reads back over PCIe instead of the 95 %-zero dense tensor.
+template <bool kCompact>
+__device__ __forceinline__ void
+tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
+          ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
+          unsigned *__restrict__ compact, unsigned compact_cap)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int T = p.tile_cells;
@@ -280,8 +288,10 @@ tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
         float *dst = top + (size_t)f * p.top_frame_floats + (size_t)cell0 * planes;
         const bool bulk = ((reinterpret_cast<uintptr_t>(dst) | (uintptr_t)bytes) & 15u) == 0;
 
-        if (n0 == 0) {
-            // Empty tile (the majority): stream the all-zero image; nothing is modified, so no barrier.
+        if (kCompact && n0 == 0) {
+            // nothing to report for an empty tile
+        } else if (n0 == 0) {
+            // Empty tile: stream the all-zero image; nothing is modified, so no barrier.
             if (bulk) {
                 if (tid == 0) { bulk_store(dst, img, bytes); bulk_commit(); }
             } else {
@@ -289,8 +299,10 @@ tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
             }
         } else {
             // Earlier (empty-tile) bulk stores may still be reading the image: wait before touching it.
-            if (tid == 0) bulk_wait_read_all();
-            __syncthreads();
+            if (!kCompact) {
+                if (tid == 0) bulk_wait_read_all();
+                __syncthreads();
+            }
 
             // accumulate
             for (int r = tid; r < n0; r += kTileThreads) {
@@ -326,11 +338,24 @@ tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
                     }
                 }
             }
-            fence_proxy_async_smem();
+            if (!kCompact) fence_proxy_async_smem();
             __syncthreads();
 
-            // store, then re-zero only what was touched once the bulk read of the image is done
-            if (bulk) {
+            if (kCompact) {
+                // the tile's slots are those of its records: touched cells first, one warp per cell
+                unsigned *out_idx = compact + (size_t)f * compact_cap * ((unsigned)planes + 1u);
+                unsigned *out_val = out_idx + compact_cap;
+                const unsigned beg = (unsigned)(rec0 - (binned + (size_t)offs.off[f]));
+                for (int d = warp; d < nd; d += kWarps) {
+                    const unsigned slot = beg + (unsigned)d;
+                    if (slot >= compact_cap) continue;  // cap >= points of the sweep: cannot happen, never overrun
+                    const unsigned local = dirty[d];
+                    if (lane == 0) out_idx[slot] = (unsigned)cell0 + local;
+                    for (int k = lane; k < planes; k += 32) out_val[(size_t)slot * planes + k] = img[local * planes + k];
+                }
+                for (int d = nd + tid; d < n0; d += kTileThreads)
+                    if (beg + (unsigned)d < compact_cap) out_idx[beg + (unsigned)d] = kNoCell;
+            } else if (bulk) {
                 if (tid == 0) { bulk_store(dst, img, bytes); bulk_commit(); bulk_wait_read_all(); }
             } else {
                 for (int w = tid; w < ncell * planes; w += kTileThreads) dst[w] = __uint_as_float(img[w]);
@@ -342,13 +367,29 @@ tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
                 if (lane == 0) key[local] = 0ull;
             }
             if (tid == 0) ndirty = 0;
-            fence_proxy_async_smem();
+            if (!kCompact) fence_proxy_async_smem();
             __syncthreads();
         }
         rec0 = rec1; n0 = n1; q0 = q1;
         rec1 = rec2; n1 = n2;
     }
-    if (tid == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
+    if (!kCompact && tid == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
+}
+
+__global__ void __launch_bounds__(kTileThreads)
+tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
+                  ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles)
+{
+    tile_body<false>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u);
+}
+
+// Same reduction, compact output (see tile_body).
+__global__ void __launch_bounds__(kTileThreads)
+tile_compact_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
+                    ViewParams p, const float *__restrict__ lut, int total_tiles, unsigned *__restrict__ compact,
+                    unsigned compact_cap)
+{
+    tile_body<true>(binned, tile_off, offs, p, lut, nullptr, total_tiles, compact, compact_cap);
 }
 
 
@@ -689,6 +730,18 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
     const int total = batch * p.tiles_per_frame;
     const int grid = grid_blocks < total ? grid_blocks : total;
     tile_build_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
+    return 1;
+}
+
+int launch_tile_compact(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
+                        const float *lut, int batch, int grid_blocks, unsigned *compact, unsigned compact_cap,
+                        cudaStream_t s)
+{
+    const int total = batch * p.tiles_per_frame;
+    const int grid = grid_blocks < total ? grid_blocks : total;
+    cudaFuncSetAttribute(tile_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(p));
+    tile_compact_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, total, compact,
+                                                                       compact_cap);
     return 1;
 }
 

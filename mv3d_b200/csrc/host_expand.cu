@@ -1,0 +1,289 @@
+// host_expand.cu -- fork-join pool and the dense rebuild of a compact read-back (see host_expand.h).
+// Host code only; compiled by nvcc together with the kernels so the library stays one translation toolchain.
+#include "host_expand.h"
+
+#include <stdint.h>
+#include <string.h>
+
+#include <algorithm>
+#include <chrono>
+
+#if defined(__SSE2__) || defined(__x86_64__)
+#include <emmintrin.h>
+#include <xmmintrin.h>
+#define MV3D_HAVE_NT_STORES 1
+#endif
+
+namespace mv3d {
+
+static inline void cpu_relax()
+{
+#ifdef MV3D_HAVE_NT_STORES
+    _mm_pause();
+#endif
+}
+
+// Spin for a short while (jobs of one host call follow each other within a few hundred microseconds, far less
+// than a futex sleep/wake round trip on a virtualised host), then give up and let the caller block.
+template <typename Pred>
+static bool spin_until(Pred pred)
+{
+    using clock = std::chrono::steady_clock;
+    const auto deadline = clock::now() + std::chrono::microseconds(300);
+    for (int i = 0;; i++) {
+        if (pred()) return true;
+        cpu_relax();
+        if ((i & 63) == 63 && clock::now() > deadline) return pred();
+    }
+}
+
+HostPool::HostPool(int threads)
+{
+    if (threads < 1) threads = 1;
+    for (int i = 0; i < threads - 1; i++) workers_.emplace_back([this] { worker(); });
+}
+
+HostPool::~HostPool()
+{
+    {
+        std::lock_guard<std::mutex> lock(mu_);
+        stop_.store(true, std::memory_order_release);
+    }
+    cv_work_.notify_all();
+    for (auto &t : workers_) t.join();
+}
+
+// Take parts of the current job until none are left.
+void HostPool::drain()
+{
+    for (;;) {
+        const int part = next_.fetch_add(1, std::memory_order_relaxed);
+        if (part >= parts_) break;
+        (*fn_)(part);
+    }
+}
+
+void HostPool::worker()
+{
+    unsigned long long seen = 0;
+    auto ready = [&] { return stop_.load(std::memory_order_acquire) || generation_.load(std::memory_order_acquire) != seen; };
+    for (;;) {
+        if (!spin_until(ready)) {
+            std::unique_lock<std::mutex> lock(mu_);
+            cv_work_.wait(lock, ready);
+        }
+        if (stop_.load(std::memory_order_acquire)) return;
+        seen = generation_.load(std::memory_order_acquire);
+        drain();
+        done_.fetch_add(1, std::memory_order_release);
+        { std::lock_guard<std::mutex> lock(mu_); }  // pairs with the caller's predicate check: no lost wake-up
+        cv_done_.notify_one();
+    }
+}
+
+void HostPool::parallel_for(int parts, const std::function<void(int)> &fn, const std::function<void()> *caller_first)
+{
+    if (parts <= 0) {
+        if (caller_first) (*caller_first)();
+        return;
+    }
+    if (workers_.empty()) {
+        if (caller_first) (*caller_first)();
+        for (int i = 0; i < parts; i++) fn(i);
+        return;
+    }
+    fn_ = &fn;
+    parts_ = parts;
+    next_.store(0, std::memory_order_relaxed);
+    done_.store(0, std::memory_order_relaxed);
+    {
+        std::lock_guard<std::mutex> lock(mu_);
+        generation_.fetch_add(1, std::memory_order_release);  // publishes fn_/parts_/next_/done_
+    }
+    cv_work_.notify_all();
+    if (caller_first) (*caller_first)();  // the caller's own errand (e.g. queueing GPU work) overlaps the workers
+    drain();
+    // every worker reports once per generation; wait for all of them so fn_ is never used after we return
+    auto all_done = [&] { return done_.load(std::memory_order_acquire) == (int)workers_.size(); };
+    if (!spin_until(all_done)) {
+        std::unique_lock<std::mutex> lock(mu_);
+        cv_done_.wait(lock, all_done);
+    }
+    fn_ = nullptr;
+}
+
+// ---- streaming writers -----------------------------------------------------------------------------------------
+// The destination is written exactly once, front to back, with non-temporal stores on whole 64-byte lines (no
+// read-for-ownership, no cache pollution); only the first and last partial line of a run use ordinary stores.
+
+// Zero [p, p + bytes).
+static void zero_stream(char *p, size_t bytes)
+{
+#ifdef MV3D_HAVE_NT_STORES
+    size_t head = (size_t)((64 - ((uintptr_t)p & 63)) & 63);
+    if (head > bytes) head = bytes;
+    memset(p, 0, head);
+    p += head;
+    bytes -= head;
+    const __m128i z = _mm_setzero_si128();
+    size_t i = 0;
+    for (; i + 64 <= bytes; i += 64) {
+        _mm_stream_si128(reinterpret_cast<__m128i *>(p + i), z);
+        _mm_stream_si128(reinterpret_cast<__m128i *>(p + i + 16), z);
+        _mm_stream_si128(reinterpret_cast<__m128i *>(p + i + 32), z);
+        _mm_stream_si128(reinterpret_cast<__m128i *>(p + i + 48), z);
+    }
+    memset(p + i, 0, bytes - i);
+#else
+    memset(p, 0, bytes);
+#endif
+}
+
+// Copy [src, src + bytes) to p.
+static void copy_stream(char *p, const char *src, size_t bytes)
+{
+#ifdef MV3D_HAVE_NT_STORES
+    size_t head = (size_t)((64 - ((uintptr_t)p & 63)) & 63);
+    if (head > bytes) head = bytes;
+    memcpy(p, src, head);
+    p += head;
+    src += head;
+    bytes -= head;
+    size_t i = 0;
+    for (; i + 64 <= bytes; i += 64) {
+        const __m128i a = _mm_loadu_si128(reinterpret_cast<const __m128i *>(src + i));
+        const __m128i b = _mm_loadu_si128(reinterpret_cast<const __m128i *>(src + i + 16));
+        const __m128i c = _mm_loadu_si128(reinterpret_cast<const __m128i *>(src + i + 32));
+        const __m128i d = _mm_loadu_si128(reinterpret_cast<const __m128i *>(src + i + 48));
+        _mm_stream_si128(reinterpret_cast<__m128i *>(p + i), a);
+        _mm_stream_si128(reinterpret_cast<__m128i *>(p + i + 16), b);
+        _mm_stream_si128(reinterpret_cast<__m128i *>(p + i + 32), c);
+        _mm_stream_si128(reinterpret_cast<__m128i *>(p + i + 48), d);
+    }
+    memcpy(p + i, src + i, bytes - i);
+#else
+    memcpy(p, src, bytes);
+#endif
+}
+
+static void store_fence()
+{
+#ifdef MV3D_HAVE_NT_STORES
+    _mm_sfence();
+#endif
+}
+
+void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
+                    unsigned n, const unsigned *tile_off, int tiles, int tile_cells,
+                    const std::function<void()> *caller_first)
+{
+    if (!dst || cells == 0 || planes <= 0) {
+        if (caller_first) (*caller_first)();
+        return;
+    }
+    // Parts are contiguous cell ranges, so no two threads ever write the same bytes. A part is emitted front to
+    // back in blocks that end on kBlock-byte boundaries of the destination ADDRESS, so every store inside a part is a
+    // whole 64-byte line (only the part's first and last line can be partial). The part's entries are grouped
+    // by the block their first byte falls into (counting sort); runs of untouched blocks are streamed as zeros,
+    // a touched block is composed in a cache-resident buffer (zeros + the finished values) and streamed out.
+    // A cell can straddle a block boundary: its tail is carried into the next block (at most one per boundary).
+#ifndef MV3D_EXPAND_BLOCK
+#define MV3D_EXPAND_BLOCK 256
+#endif
+    constexpr uintptr_t kBlock = MV3D_EXPAND_BLOCK;
+    // With tile_off (the list is ordered by tile: tile t owns the entries [tile_off[t], tile_off[t + 1])) a part is
+    // a run of whole tiles and looks only at its own entries; without it every part filters the whole list.
+    const int parts = pool.size() * 2;
+    const bool by_tile = tile_off && tiles > 0 && tile_cells > 0;
+    const size_t tiles_per_part = by_tile ? ((size_t)tiles + parts - 1) / parts : 0;
+    const size_t per = by_tile ? tiles_per_part * (size_t)tile_cells : (cells + parts - 1) / parts;
+    const size_t cell_bytes = (size_t)planes * 4;
+    const std::function<void(int)> body = [&](int part) {
+        const size_t c0 = (size_t)part * per;
+        if (c0 >= cells) return;
+        const size_t c1 = (c0 + per < cells) ? c0 + per : cells;
+        unsigned i0 = 0, i1 = n;  // the entries this part has to look at
+        if (by_tile) {
+            const size_t t0 = (size_t)part * tiles_per_part;
+            const size_t t1 = (t0 + tiles_per_part < (size_t)tiles) ? t0 + tiles_per_part : (size_t)tiles;
+            i0 = tile_off[t0] < n ? tile_off[t0] : n;
+            i1 = tile_off[t1] < n ? tile_off[t1] : n;
+#ifdef MV3D_HAVE_NT_STORES
+            // The values were just written by the GPU's DMA, so they are in no cache, and they are consumed below
+            // in block order, not list order: pull this part's (contiguous) slice in now, while the counting sort
+            // runs, instead of paying one memory round trip per cell later.
+            const char *pf0 = reinterpret_cast<const char *>(vals + (size_t)i0 * planes);
+            const char *pf1 = reinterpret_cast<const char *>(vals + (size_t)i1 * planes);
+            for (const char *q = pf0; q < pf1; q += 64) _mm_prefetch(q, _MM_HINT_T1);
+#endif
+        }
+        char *const base = reinterpret_cast<char *>(dst);
+        if (cell_bytes > kBlock / 2) {  // very deep grids: plain zero-fill, then scatter (a cell may span several blocks)
+            zero_stream(base + c0 * cell_bytes, (c1 - c0) * cell_bytes);
+            store_fence();
+            for (unsigned i = i0; i < i1; i++) {
+                const size_t cell = idx[i];
+                if (cell >= c0 && cell < c1) memcpy(base + cell * cell_bytes, vals + (size_t)i * planes, cell_bytes);
+            }
+            return;
+        }
+        const uintptr_t A0 = reinterpret_cast<uintptr_t>(base + c0 * cell_bytes);  // part = addresses [A0, A1)
+        const uintptr_t A1 = reinterpret_cast<uintptr_t>(base + c1 * cell_bytes);
+        const uintptr_t blk0 = A0 / kBlock;
+        const size_t nblocks = (size_t)((A1 - 1) / kBlock - blk0 + 1);
+        auto block_of = [&](size_t cell) { return (size_t)(reinterpret_cast<uintptr_t>(base + cell * cell_bytes) / kBlock - blk0); };
+
+        static thread_local std::vector<unsigned> first, cursor, order;  // first[b] .. first[b + 1]: entries of block b
+        static thread_local std::vector<char> block;
+        first.assign(nblocks + 1, 0u);
+        for (unsigned i = i0; i < i1; i++) {
+            const size_t cell = idx[i];
+            if (cell >= c0 && cell < c1) first[block_of(cell) + 1]++;
+        }
+        for (size_t b = 0; b < nblocks; b++) first[b + 1] += first[b];
+        order.resize(first[nblocks]);
+        cursor.assign(first.begin(), first.end() - 1);
+        if (first[nblocks])
+            for (unsigned i = i0; i < i1; i++) {
+                const size_t cell = idx[i];
+                if (cell >= c0 && cell < c1) order[cursor[block_of(cell)]++] = i;
+            }
+        block.resize(kBlock);
+
+        uintptr_t zero_from = A0;          // start of the pending run of untouched bytes
+        const char *carry = nullptr;       // tail of a cell that began in the previous block
+        size_t carry_bytes = 0;
+        for (size_t b = 0; b < nblocks; b++) {
+            const uintptr_t lo = (b == 0) ? A0 : (blk0 + b) * kBlock;
+            const uintptr_t hi = ((blk0 + b + 1) * kBlock < A1) ? (blk0 + b + 1) * kBlock : A1;
+            const unsigned e0 = first[b], e1 = first[b + 1];
+            if (e0 == e1 && !carry) continue;  // untouched: stays in the zero run
+            if (lo > zero_from) zero_stream(reinterpret_cast<char *>(zero_from), (size_t)(lo - zero_from));
+            const size_t len = (size_t)(hi - lo);
+            memset(block.data(), 0, len);
+            if (carry) {
+                memcpy(block.data(), carry, carry_bytes);  // carry_bytes < cell_bytes <= a block
+                carry = nullptr;
+            }
+            for (unsigned e = e0; e < e1; e++) {
+                const size_t i = order[e];
+                const uintptr_t at = reinterpret_cast<uintptr_t>(base + (size_t)idx[i] * cell_bytes);
+                const char *src = reinterpret_cast<const char *>(vals + i * planes);
+                size_t take = cell_bytes;
+                if (at + cell_bytes > hi) {  // straddles the block end (the part end is a cell boundary, so b + 1 exists)
+                    take = (size_t)(hi - at);
+                    carry = src + take;
+                    carry_bytes = cell_bytes - take;
+                }
+                memcpy(block.data() + (at - lo), src, take);
+            }
+            copy_stream(reinterpret_cast<char *>(lo), block.data(), len);
+            zero_from = hi;
+        }
+        if (A1 > zero_from) zero_stream(reinterpret_cast<char *>(zero_from), (size_t)(A1 - zero_from));
+        store_fence();
+    };
+    pool.parallel_for(parts, body, caller_first);
+}
+
+} // namespace mv3d

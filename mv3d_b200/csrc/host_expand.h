@@ -1,0 +1,51 @@
+// host_expand.h -- host side of the compact read-back (internal).
+//
+// The bird's-eye-view tensor is ~95 % zeros, so the host-buffer entry points do not drag the dense tensor over
+// PCIe: the GPU reports only the touched cells ({cell index, planes values}, fully computed on the device) and
+// the host rebuilds the dense layout the reference ABI promises -- a zero-fill plus a scatter of finished values.
+// No encoding arithmetic happens here; this is the delivery of a result, not a CPU implementation of the path.
+#pragma once
+#include <stddef.h>
+
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
+#include <thread>
+#include <vector>
+
+namespace mv3d {
+
+// A small fork-join pool: parallel_for(parts, fn) runs fn(0..parts-1) on the workers and the calling thread.
+class HostPool {
+public:
+    explicit HostPool(int threads);
+    ~HostPool();
+    int size() const { return (int)workers_.size() + 1; }
+    // `caller_first`, if given, runs on the calling thread after the workers have been released and before the
+    // caller joins them.
+    void parallel_for(int parts, const std::function<void(int)> &fn, const std::function<void()> *caller_first = nullptr);
+
+private:
+    void worker();
+    void drain();
+    std::vector<std::thread> workers_;
+    std::mutex mu_;
+    std::condition_variable cv_work_, cv_done_;
+    const std::function<void(int)> *fn_ = nullptr;
+    int parts_ = 0;
+    std::atomic<int> next_{0};
+    std::atomic<int> done_{0};
+    std::atomic<unsigned long long> generation_{0};
+    std::atomic<bool> stop_{false};
+};
+
+// dst[cells][planes] = 0 except dst[idx[i]][:] = vals[i][:] for the n entries (a cell appears at most once).
+// Entries with a cell index >= cells (kNoCell marks an unused slot) are ignored. The destination is written once,
+// with streaming stores. If the list is ordered by tile -- tile t (tile_cells consecutive cells) owns the entries
+// [tile_off[t], tile_off[t + 1]) -- pass tile_off/tiles/tile_cells and every thread reads only its own entries.
+void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
+                    unsigned n, const unsigned *tile_off = nullptr, int tiles = 0, int tile_cells = 0,
+                    const std::function<void()> *caller_first = nullptr);
+
+} // namespace mv3d

@@ -40,6 +40,7 @@ struct FrameOffsets {            // first point of each sweep in the packed poin
 constexpr int kDensityLutSize = 32;  // min(1, (float)(logf(c+1)/log(32))) for c = 0..31, built on the host with libm
 
 constexpr uint32_t kInvalidKey = 0xFFFFFFFFu;
+constexpr uint32_t kNoCell = 0xFFFFFFFFu;   // unused slot of the compact read-back list
 constexpr uint32_t kRawTag = 0x80000000u;   // marks an un-finalised height slot in the atomic strategy
 
 // x86 cvttss2si: NaN / out-of-range -> INT_MIN (CUDA's own conversion saturates and maps NaN to 0).

@@ -63,6 +63,13 @@ class ViewEncoder:
             raise RuntimeError("mv3d_ctx_kernel_times: " + _lib.last_error())
         return {self._lib.mv3d_kernel_name(k).decode(): (float(ms[k]), int(cnt[k])) for k in range(n)}
 
+    def transfer_bytes(self, reset: bool = False):
+        """(host->device, device->host) bytes moved by `encode_host` since the last reset."""
+        h2d, d2h = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+        if self._lib.mv3d_ctx_transfer_bytes(self._ctx, ctypes.byref(h2d), ctypes.byref(d2h), int(reset)) != 0:
+            raise RuntimeError("mv3d_ctx_transfer_bytes: " + _lib.last_error())
+        return int(h2d.value), int(d2h.value)
+
     def resolved_strategy(self, top: TopParams) -> str:
         code = self._lib.mv3d_resolve_strategy(self._ctx, ctypes.byref(_top_c(top)), self.strategy)
         return {v: k for k, v in _lib.STRATEGIES.items()}[code]
