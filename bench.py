@@ -203,10 +203,8 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        # keep stdout to the one JSON line: NCCL prints its version banner there at VERSION/INFO level
-        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "INFO"):
-            os.environ["NCCL_DEBUG"] = "WARN"
-        dist.init_process_group("nccl", device_id=dev)
+        from mv3d_b200.shard import init_process_group_quiet
+        init_process_group_quiet("nccl", dev)  # keeps NCCL's version banner off stdout (one JSON line only)
 
     def barrier():
         if world > 1:

@@ -89,6 +89,31 @@ def max_over_ranks(value: float, device=None, group=None) -> float:
     return float(t.item())
 
 
+def init_process_group_quiet(backend: str, device=None) -> None:
+    """`dist.init_process_group` with stdout (the file descriptor, not just sys.stdout) pointed at stderr while the
+    communicator comes up: NCCL writes a version banner to stdout from C, and bench.py's stdout must be exactly one
+    JSON line."""
+    import os
+    import sys
+    import torch.distributed as dist
+    sys.stdout.flush()
+    saved = os.dup(1)
+    try:
+        os.dup2(2, 1)
+        if backend == "nccl" and device is not None:
+            dist.init_process_group(backend, device_id=device)
+        else:
+            dist.init_process_group(backend)
+        dist.barrier()  # forces communicator creation now, inside the redirected region
+        if device is not None and backend == "nccl":
+            import torch
+            torch.cuda.synchronize(device)
+    finally:
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(saved)
+
+
 class ShardedStream:
     """Drives one rank's share of a sweep stream through a `ViewEncoder`, `batch` frames per launch.
 
@@ -110,5 +135,5 @@ class ShardedStream:
             yield group, top, front
 
 
-__all__ = ["owner_of", "frames_of", "local_index", "shard_sizes", "batches", "interleave", "gather_frames",
+__all__ = ["init_process_group_quiet", "owner_of", "frames_of", "local_index", "shard_sizes", "batches", "interleave", "gather_frames",
            "max_over_ranks", "ShardedStream"]

@@ -1,0 +1,142 @@
+#!/usr/bin/env python
+"""BASELINE.json config 4: a frame-sharded stream of sweeps over the GPUs of one box.
+
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+      tests/run_config4.py --frames 4096 [--gather]
+
+Frame i -> rank i mod N (mv3d_b200/shard.py), no collective on the encode path. Every rank streams its frames
+through SweepStream (ring of output slots; the consumer is a per-frame checksum kernel, so 4096 x 60.8 MB is never
+resident at once). Rank 0 then
+  * collects the per-frame checksums (a few bytes per frame, torch.distributed.gather) and checks a sample of
+    frames bit-for-bit: the frame is re-encoded on rank 0 alone and, if oracle/ is built, compared with the oracle;
+  * with --gather also times the optional delivery of whole encoded tensors to rank 0 (shard.gather_frames, NCCL).
+Prints one JSON line on rank 0. Frames repeat with period --distinct (generating 4096 distinct synthetic sweeps on
+the host would dominate the run; the encoder never sees which frames repeat).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--frames", type=int, default=4096)
+    ap.add_argument("--distinct", type=int, default=128)
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--gather", action="store_true")
+    ap.add_argument("--check", type=int, default=8, help="frames re-checked on rank 0")
+    args = ap.parse_args()
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from mv3d_b200 import shard
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.params import KITTI_FRONT_64x512, KITTI_PAPER_TOP
+    from mv3d_b200.stream import SweepStream
+    from mv3d_b200.sweeps import hdl64_sweep, pack_sweeps
+
+    rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        shard.init_process_group_quiet("nccl", dev)
+    top_p, front_p = KITTI_PAPER_TOP, KITTI_FRONT_64x512
+
+    mine = list(shard.frames_of(rank, world, args.frames))
+    cache = {}
+
+    def load(frame):
+        key = frame % args.distinct
+        if key not in cache:
+            cache[key] = hdl64_sweep(key)
+        return cache[key]
+
+    for f in mine[: args.distinct]:  # generate outside the timed region
+        load(f)
+    stream = SweepStream(local, top_p, front_p, batch=args.batch, depth=2)
+    sums = torch.zeros((len(mine), 2), dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    done = 0
+    for frames, top, front in stream.run(mine, load):
+        nb = len(frames)
+        # the consumer: one checksum per frame and view, computed where the tensors live
+        sums[done:done + nb, 0] = top.view(nb, -1).sum(dim=1, dtype=torch.float64)
+        sums[done:done + nb, 1] = front.view(nb, -1).sum(dim=1, dtype=torch.float64)
+        done += nb
+    torch.cuda.synchronize()
+    elapsed = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
+    launches = stream.launch_count
+    stream.close()
+
+    # per-frame checksums to rank 0, in stream order
+    if world > 1:
+        all_sums = shard.gather_frames(sums, args.frames, dst=0)
+    else:
+        all_sums = sums
+    gather = None
+    if args.gather and world > 1:
+        enc = ViewEncoder(local)
+        ids = mine[: args.batch]
+        pts, offs = pack_sweeps([load(f) for f in ids])
+        top, _ = enc.encode_device(torch.from_numpy(pts).to(dev), offs, top_p, None)
+        n_g = world * len(ids)
+        torch.cuda.synchronize()
+        dist.barrier()
+        t1 = time.perf_counter()
+        full = shard.gather_frames(top, n_g, dst=0)
+        torch.cuda.synchronize()
+        dt = shard.max_over_ranks(time.perf_counter() - t1, device=dev)
+        nbytes = n_g * top[0].numel() * 4
+        gather = {"frames": n_g, "bytes": nbytes, "seconds": dt, "frames_per_s": n_g / dt,
+                  "ingress_GBps": nbytes * (world - 1) / world / dt / 1e9}
+        if rank == 0:  # gathered frame j must be the encoding of stream frame j
+            for j in (0, 1, n_g - 1):
+                p, o = pack_sweeps([load(j)])
+                t, _ = enc.encode_device(torch.from_numpy(p).to(dev), o, top_p, None)
+                assert torch.equal(full[j], t[0]), f"gathered frame {j} differs"
+        enc.close()
+
+    if rank == 0:
+        all_sums = all_sums.cpu().numpy()
+        # frames repeat with period `distinct`: equal inputs must give equal checksums on whatever rank
+        for f in range(args.frames):
+            assert (all_sums[f] == all_sums[f % args.distinct]).all(), f"frame {f} differs from frame {f % args.distinct}"
+        checked = 0
+        try:
+            import oracle
+            oracle.build()
+        except Exception:
+            oracle = None
+        enc = ViewEncoder(local)
+        rng = np.random.default_rng(0)
+        for f in rng.choice(args.frames, size=min(args.check, args.frames), replace=False):
+            p, o = pack_sweeps([load(int(f))])
+            t, fr = enc.encode_device(torch.from_numpy(p).to(dev), o, top_p, front_p)
+            assert float(t.sum(dtype=torch.float64)) == all_sums[f, 0] and float(fr.sum(dtype=torch.float64)) == all_sums[f, 1]
+            if oracle is not None:
+                et, ef = oracle.top_and_front_maps(load(int(f)), top_p, front_p)
+                assert np.array_equal(t[0].cpu().numpy(), et) and np.array_equal(fr[0].cpu().numpy(), ef), f"frame {f} vs oracle"
+            checked += 1
+        enc.close()
+        print(json.dumps({"workload": "configs[3] (config 4): frame-sharded stream, host-staged input, device-resident output ring",
+                          "n_gpus": world, "frames": args.frames, "batch": args.batch, "seconds": elapsed,
+                          "sweeps_per_s": args.frames / elapsed, "gpu_launches": launches,
+                          "frames_checked_bit_exact": checked, "oracle": oracle is not None, "gather": gather}), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -264,3 +264,60 @@ def test_size_independent_properties(torch_cuda):
     keep = (X >= 1) & (Y >= 1) & (Z >= 0) & (X < k.xn) & (Y < k.yn) & (Z < k.zn)
     assert np.count_nonzero(top[0][..., zn + 1]) == len(set(zip(X[keep].tolist(), Y[keep].tolist())))
     enc.close()
+
+
+def test_config3_front_only_stream_1k(torch_cuda, oracle_mod):
+    """BASELINE config 3: 1000 sweeps streamed in batches of 64, front view only (BEV gate applied, BEV tensor not
+    produced). Every frame is checked against a direct batched encode of the same frames (streaming must not
+    change a bit); a 32-frame subset is checked against the oracle."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.stream import SweepStream
+    n_frames = 1000
+    cache = {}
+
+    def load(f):
+        if f not in cache:
+            cache[f] = hdl64_sweep(f)
+        return cache[f]
+
+    stream = SweepStream(0, KITTI_PAPER_TOP, KITTI_FRONT_64x512, batch=64, want_top=False, depth=3)
+    fronts = torch.empty((n_frames, *KITTI_FRONT_64x512.shape), dtype=torch.float32, device="cuda")
+    seen = []
+    for frames, top, front in stream.run(range(n_frames), load):
+        assert top is None and front.shape[0] == len(frames)
+        fronts[frames[0]:frames[0] + len(frames)].copy_(front)
+        seen += list(frames)
+    assert seen == list(range(n_frames))
+    assert stream.launch_count > 0
+    stream.close()
+    fronts = fronts.cpu().numpy()
+    # (a) streaming == one direct call, on 3 of the batches
+    enc = ViewEncoder(0)
+    for b0 in (0, 448, 960):
+        ids = list(range(b0, min(b0 + 64, n_frames)))
+        pts, offs = pack_sweeps([load(f) for f in ids])
+        _, f = enc.encode_device(torch.from_numpy(pts).cuda(), offs, KITTI_PAPER_TOP, KITTI_FRONT_64x512, want_top=False)
+        assert_same(fronts[b0:b0 + len(ids)], f.cpu().numpy(), f"streamed batch at {b0}")
+    enc.close()
+    # (b) the oracle, on 32 frames spread over the stream
+    for f in range(7, n_frames, 31)[:32]:
+        _, ef = oracle_mod.top_and_front_maps(load(f), KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+        assert_same(fronts[f], ef, f"streamed frame {f}")
+
+
+def test_stream_with_top_ragged_tail(torch_cuda, oracle_mod):
+    """The same stream with the bird's-eye view on, a batch size that does not divide the stream, depth 2."""
+    from mv3d_b200.stream import SweepStream
+    frames = list(range(100, 111))
+    stream = SweepStream(0, KITTI_PAPER_TOP, KITTI_FRONT_64x512, batch=4, depth=2)
+    got = 0
+    for ids, top, front in stream.run(frames, hdl64_sweep):
+        top, front = top.cpu().numpy(), front.cpu().numpy()
+        for j, f in enumerate(ids):
+            et, ef = oracle_mod.top_and_front_maps(hdl64_sweep(f), KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+            assert_same(top[j], et, f"stream frame {f} top")
+            assert_same(front[j], ef, f"stream frame {f} front")
+            got += 1
+    assert got == len(frames)
+    stream.close()
