@@ -125,6 +125,7 @@ struct mv3d_ctx {
     int fill_chunk = 0;                   // sweeps per zero-fill launch of the PATCH strategy
     int fill_ctas = 0;                    // fill CTAs per SM (one issuing thread each)
     int fill_pending = 0;                 // bulk stores each fill CTA keeps in flight (> 16: unbounded)
+    int front_aside = 1;                  // TILE: finish the front view on the side stream (MV3D_FRONT_ASIDE=0: in line)
     int atomic_overlap = 0;               // ATOMIC: TMA zero-fill on the side stream, chunked (MV3D_ATOMIC_OVERLAP=1)
     size_t smem_per_sm = 0;
     int patch_min_batch = 0;              // AUTO picks PATCH from this batch size on
@@ -219,6 +220,8 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     const char *fa = getenv("MV3D_FILL_CTAS");
     ctx->fill_ctas = fa ? atoi(fa) : 2;
     if (ctx->fill_ctas < 1) ctx->fill_ctas = 1;
+    const char *fs = getenv("MV3D_FRONT_ASIDE");
+    ctx->front_aside = fs ? atoi(fs) : 1;
     const char *ao = getenv("MV3D_ATOMIC_OVERLAP");
     ctx->atomic_overlap = ao ? atoi(ao) : 0;
     const char *fpn = getenv("MV3D_FILL_PENDING");
@@ -555,6 +558,8 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
         // while the memory-bound tile kernel of sub-batch j streams its output on the caller's stream.
         const int sub = (ctx->sub_batch > 0 && ctx->sub_batch < batch && ctx->side_stream) ? ctx->sub_batch : batch;
         const bool piped = sub < batch;
+        const bool front_aside = !piped && !compact && ctx->front_aside && ctx->side_stream && p.want_front &&
+                                 p.front_pixels > 0 && batch >= 8;
         cudaStream_t sp = piped ? ctx->side_stream : s;
         if (piped) {
             CUDA_TRY(cudaEventRecord(ctx->ev_fork, s));
@@ -570,6 +575,16 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
             unsigned *tc = tcount + (size_t)j0 * (p.tiles_per_frame + 1), *to = toff + (size_t)j0 * (p.tiles_per_frame + 1);
             unsigned *win = winners ? winners + (size_t)j0 * p.front_pixels : nullptr;
             timed_launch(ctx, K_CLASSIFY, sp, [&] { return launch_classify(pts, so, p, nb, sub_max, keys, tc, win, sp); });
+            if (front_aside) {
+                // The front view only needs the winners classify just elected: finish it on the side stream, beside
+                // scan / bin / tile build, instead of after them.
+                CUDA_TRY(cudaEventRecord(ctx->ev_fork, s));
+                CUDA_TRY(cudaStreamWaitEvent(ctx->side_stream, ctx->ev_fork, 0));
+                timed_launch(ctx, K_FRONT_FINALIZE, ctx->side_stream, [&] {
+                    return launch_front_finalize(pts, offs, p, batch, winners, front_dev, ctx->side_stream);
+                });
+                CUDA_TRY(cudaEventRecord(ctx->ev_join, ctx->side_stream));
+            }
             timed_launch(ctx, K_TILE_SCAN, sp, [&] { return launch_tile_scan(tc, to, p.tiles_per_frame, nb, sp); });
             timed_launch(ctx, K_BIN, sp, [&] { return launch_bin(pts, so, p, nb, sub_max, keys, to, binned, sp); });
             if (piped) {
@@ -587,6 +602,11 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
             timed_launch(ctx, K_TILE_BUILD, s, [&] {
                 return launch_tile_build(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
             });
+        }
+        if (front_aside) {
+            CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_join, 0));
+            CUDA_TRY(cudaGetLastError());
+            return 0;
         }
         if (piped) {
             if (p.want_front && p.front_pixels > 0)

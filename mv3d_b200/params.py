@@ -108,3 +108,63 @@ PRESETS = {
 
 __all__ = ["TopParams", "FrontParams", "KITTI_PAPER_TOP", "KITTI_FRONT_64x512", "DENSE_TOP",
            "REFERENCE_KITTI_TOP", "REFERENCE_DIDI_TOP", "REFERENCE_DIDI2_TOP", "PRESETS", "replace"]
+
+
+@dataclass(frozen=True)
+class PyTwinParams:
+    """Parameter set of the reference's PYTHON encoders (`src/data.py:113-180` `lidar_to_front_fast`, `:296-367`
+    `lidar_to_top`): the module-level `TOP_*` constants of `src/config.py:154-189` plus the front-view constants of
+    `src/config.py:32-42`. Values are Python floats (doubles), as in the reference; the encoders narrow them to
+    float32 where numpy does."""
+
+    x_min: float
+    x_max: float
+    y_min: float
+    y_max: float
+    z_min: float
+    z_max: float
+    x_div: float
+    y_div: float
+    z_div: float
+    filter_center_car: bool = False            # src/data.py:313-314 (didi / didi2 / test data sets only)
+    ang_res: float = 0.08 / 180 * math.pi      # VELODYNE_ANGULAR_RESOLUTION
+    vert_res: float = 0.4 / 180 * math.pi      # VELODYNE_VERTICAL_RESOLUTION
+    velodyne_height: float = 1.73
+    front_r_offset: int = 70
+    front_c_offset: int = 750
+    front_r_min: int = -70
+    front_r_max: int = 30
+    front_c_min: int = -750
+    front_c_max: int = 750
+    front_width: int = 1500
+    front_height: int = 100
+
+    @property
+    def xn(self):
+        """src/data.py:327: `int((TOP_X_MAX-TOP_X_MIN)//TOP_X_DIVISION)+1`, in double."""
+        return int((self.x_max - self.x_min) // self.x_div) + 1
+
+    @property
+    def yn(self):
+        return int((self.y_max - self.y_min) // self.y_div) + 1
+
+    @property
+    def zn(self):
+        """src/data.py:329: true division, truncated."""
+        return int((self.z_max - self.z_min) / self.z_div)
+
+    @property
+    def top_shape(self):
+        return (self.xn, self.yn, self.zn + 2)
+
+    @property
+    def front_shape(self):
+        """`[FRONT_WIDTH][FRONT_HEIGHT][3]`, indexed `[c][r]` (src/data.py:167)."""
+        return (self.front_width, self.front_height, 3)
+
+
+# The reference's data-set presets (src/config.py:154-187) for the Python encoders.
+PYTWIN_KITTI = PyTwinParams(0, 80, -30, 30, -4.2, 0.8, 0.1, 0.1, 0.2)
+PYTWIN_DIDI = PyTwinParams(-45, 45, -10, 10, -3.0, 0.7, 0.2, 0.2, 0.3, filter_center_car=True)
+PYTWIN_DIDI2 = PyTwinParams(-50, 50, -30, 30, -3.5, 0.6, 0.2, 0.2, 0.3, filter_center_car=True)
+PYTWIN_PRESETS = {"kitti": PYTWIN_KITTI, "didi": PYTWIN_DIDI, "didi2": PYTWIN_DIDI2}
