@@ -111,6 +111,35 @@ int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, const int *o
                            const mv3d_top_params *tp, const mv3d_front_params *fp,
                            int semantics, int strategy);
 
+/* ------------------------------------------------------------------------------------------------
+ * Python-twin mode: the reference's PYTHON encoders, which is what src/preprocess_for_mv3d.py:30-32 and the
+ * training loaders (src/utils/batch_loading.py:659-672) actually run. They differ from the C routine above
+ *  and are reproduced as numpy computes them, on float32:
+ *   lidar_to_top          src/data.py:296-367  -> top   [xn][yn][zn+2], written already flipped in X and Y
+ *   lidar_to_front_fast   src/data.py:113-180  -> front [front_width][front_height][3], indexed [c][r], MEAN per pixel
+ * The struct carries the module-level TOP_* constants (src/config.py:154-189) narrowed to float32, the grid sizes
+ * as the reference derives them (xn = int((x_max-x_min)//x_div)+1 in double, zn = int((z_max-z_min)/z_div)) and the
+ * front-view constants of src/config.py:32-42. filter_center_car: src/data.py:224-227 (didi data sets).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct mv3d_pytwin_params {
+    float x_min, x_max, y_min, y_max, z_min, z_max;
+    float x_div, y_div, z_div;
+    int xn, yn, zn;
+    int filter_center_car;
+    float ang_res, vert_res, velodyne_height;
+    int front_r_offset, front_c_offset, front_r_min, front_r_max, front_c_min, front_c_max;
+    int front_width, front_height;
+} mv3d_pytwin_params;
+
+/* Device-resident sweeps, like mv3d_encode_batch_dev; top_dev or front_dev may be NULL to skip that view. */
+int mv3d_pytwin_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *offsets_host, int batch,
+                                 float *top_dev, float *front_dev, const mv3d_pytwin_params *pp, void *stream);
+/* Host buffers (numpy arrays): copy in, encode, copy out, pipelined sweep by sweep. */
+int mv3d_pytwin_encode_batch_host(mv3d_ctx *ctx, const float *points_host, const int *offsets_host, int batch,
+                                  float *top_host, float *front_host, const mv3d_pytwin_params *pp);
+/* Test hook: out[i] = the device restatement of the C library's float atan2f (what np.arctan2 on float32 was). */
+int mv3d_debug_atan2f(mv3d_ctx *ctx, const float *y_dev, const float *x_dev, float *out_dev, int n, void *stream);
+
 /* Page-locked host memory for the buffers above (NULL on failure). */
 void *mv3d_host_alloc(size_t bytes);
 void mv3d_host_free(void *p);

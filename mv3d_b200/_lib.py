@@ -60,6 +60,15 @@ class FrontParamsC(ctypes.Structure):
                 ("phi_min", "phi_max", "theta_min", "theta_max", "phi_div", "theta_div", "c_size", "r_size", "f_size")]
 
 
+class PyTwinParamsC(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_float) for n in
+                ("x_min", "x_max", "y_min", "y_max", "z_min", "z_max", "x_div", "y_div", "z_div")] + \
+               [(n, ctypes.c_int) for n in ("xn", "yn", "zn", "filter_center_car")] + \
+               [(n, ctypes.c_float) for n in ("ang_res", "vert_res", "velodyne_height")] + \
+               [(n, ctypes.c_int) for n in ("front_r_offset", "front_c_offset", "front_r_min", "front_r_max",
+                                            "front_c_min", "front_c_max", "front_width", "front_height")]
+
+
 SEM_TOP, SEM_TOPFRONT = 0, 1
 STRATEGY_AUTO, STRATEGY_ATOMIC, STRATEGY_TILE, STRATEGY_PATCH = 0, 1, 2, 3
 STRATEGIES = {"auto": STRATEGY_AUTO, "atomic": STRATEGY_ATOMIC, "tile": STRATEGY_TILE, "patch": STRATEGY_PATCH}
@@ -71,6 +80,7 @@ EXPORTED_SYMBOLS = (
     "mv3d_ctx_launch_count", "mv3d_resolve_strategy", "mv3d_version",
     "mv3d_ctx_set_profiling", "mv3d_kernel_count", "mv3d_kernel_name", "mv3d_ctx_kernel_times",
     "mv3d_debug_point_keys", "mv3d_debug_expand_compact", "mv3d_ctx_transfer_bytes",
+    "mv3d_pytwin_encode_batch_dev", "mv3d_pytwin_encode_batch_host", "mv3d_debug_atan2f",
 )
 
 _lib = None
@@ -111,6 +121,9 @@ def load_library() -> ctypes.CDLL:
     lib.mv3d_ctx_kernel_times.argtypes = [vp, ctypes.POINTER(ctypes.c_double), ctypes.POINTER(ctypes.c_longlong), ci]
     lib.mv3d_debug_point_keys.argtypes = [vp, vp, ci, ctypes.POINTER(TopParamsC), ctypes.POINTER(FrontParamsC), ci,
                                           vp, vp, vp, vp]
+    lib.mv3d_pytwin_encode_batch_dev.argtypes = [vp, vp, ctypes.POINTER(ci), ci, vp, vp, ctypes.POINTER(PyTwinParamsC), vp]
+    lib.mv3d_pytwin_encode_batch_host.argtypes = [vp, vp, ctypes.POINTER(ci), ci, vp, vp, ctypes.POINTER(PyTwinParamsC)]
+    lib.mv3d_debug_atan2f.argtypes = [vp, vp, vp, vp, ci, vp]
     lib.mv3d_ctx_transfer_bytes.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong), ci]
     lib.mv3d_debug_expand_compact.argtypes = [vp, ctypes.c_size_t, ci, vp, ctypes.c_uint, ci]
     _lib = lib

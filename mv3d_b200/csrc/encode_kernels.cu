@@ -203,10 +203,20 @@ bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
         const float4 pt = load_point(pts + base + i);
         const uint32_t tile = k.x / (uint32_t)p.tile_cells;
         const uint32_t local = k.x - tile * (uint32_t)p.tile_cells;
-        const int Z = quantise(pt.z, p.z_min, p.z_div, p.quant_floor);
-        const float h = __fsub_rn(pt.z, p.z_min);
+        uint32_t zfield;
+        float key;
+        if (p.py) {
+            // Python twin: key = qz; slice field = floor(qz) (kNoSlice when it is past the last slice, such a point
+            // still counts and can win the intensity), top bit = "also closes the slice below"
+            const CellHit c = py_classify(pt, p);
+            key = c.h;
+            zfield = (c.slice < p.zn ? (uint32_t)c.slice : kNoSlice) | ((c.lower && c.slice <= p.zn) ? kLowerFlag : 0u);
+        } else {
+            zfield = (uint32_t)quantise(pt.z, p.z_min, p.z_div, p.quant_floor);
+            key = __fsub_rn(pt.z, p.z_min);
+        }
         binned[(size_t)base + off[tile] + k.y] =
-            make_uint4(local | ((uint32_t)Z << 16), __float_as_uint(h), (uint32_t)i, __float_as_uint(pt.w));
+            make_uint4(local | (zfield << 16), __float_as_uint(key), (uint32_t)i, __float_as_uint(pt.w));
     }
 }
 
@@ -311,7 +321,16 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 unsigned *cellw = img + local * planes;
                 if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(&ndirty, 1u)] = local;
                 if ((int)q.y > 0) {  // h > 0: the reference's maps start at 0 and update on strict '>'
-                    atomicMax(cellw + Z, q.y);
+                    if (p.py) {  // slice = floor(qz) if it exists, and the one below when qz is integral
+                        const unsigned zs = Z & (kLowerFlag - 1u);
+                        if (zs != kNoSlice) atomicMax(cellw + zs, q.y);
+                        if (Z & kLowerFlag) {
+                            const unsigned below = (zs == kNoSlice) ? (unsigned)zn - 1u : zs - 1u;  // qz == zn closes the last slice
+                            if (below < (unsigned)zn) atomicMax(cellw + below, q.y);
+                        }
+                    } else {
+                        atomicMax(cellw + Z, q.y);
+                    }
                     atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
                 }
             }
@@ -331,7 +350,8 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 for (int k = lane; k < planes; k += 32) {
                     if (k < zn) {
                         const unsigned raw = cellw[k];
-                        if (raw) cellw[k] = __float_as_uint(slice_value(__uint_as_float(raw), p.z_div, k));
+                        if (raw) cellw[k] = __float_as_uint(p.py ? __fsub_rn(__uint_as_float(raw), (float)k)  // max(qz) - z
+                                                                 : slice_value(__uint_as_float(raw), p.z_div, k));
                     } else if (k == zn + 1) {
                         const unsigned c = cellw[k];
                         cellw[k] = __float_as_uint(__ldg(lut + (c < 31u ? c : 31u)));
@@ -579,6 +599,90 @@ front_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPar
 }
 
 // ------------------------------------------------------------------------------------------------
+// Python-twin front view (src/data.py:113-180 lidar_to_front_fast): per pixel, the MEAN of the channel values of
+// its points, accumulated by the reference as a float32 running sum in input order. Same three-pass shape as the
+// bird's-eye view -- count per pixel, scan (tile_scan_kernel with one "tile" per pixel), scatter -- then one
+// thread per pixel replays its points in input order.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kPointThreads)
+pyfront_count_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p, PyFrontParams fp,
+                     uint2 *__restrict__ keys, unsigned *__restrict__ pix_count)
+{
+    const int f = blockIdx.y;
+    const int base = offs.off[f];
+    const int n = offs.off[f + 1] - base;
+    unsigned *counts = pix_count + (size_t)f * (fp.pixels + 1);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 pt = load_point(pts + base + i);
+        int pix = -1;
+        if (py_crop(pt, p)) pix = py_front_pixel(pt, fp);
+        unsigned rank = 0;
+        if (pix >= 0) rank = atomicAdd(counts + pix, 1u);
+        keys[base + i] = make_uint2((unsigned)pix, rank);
+    }
+}
+
+//   record = { point index, height, distance, intensity }
+__global__ void __launch_bounds__(kPointThreads)
+pyfront_bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, PyFrontParams fp, const uint2 *__restrict__ keys,
+                   const unsigned *__restrict__ pix_off, uint4 *__restrict__ binned)
+{
+    const int f = blockIdx.y;
+    const int base = offs.off[f];
+    const int n = offs.off[f + 1] - base;
+    const unsigned *off = pix_off + (size_t)f * (fp.pixels + 1);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint2 k = keys[base + i];
+        if (k.x == kInvalidKey) continue;
+        const float4 pt = load_point(pts + base + i);
+        const float3 v = py_front_values(pt, fp);
+        binned[(size_t)base + off[k.x] + k.y] =
+            make_uint4((uint32_t)i, __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z));
+    }
+}
+
+// One thread per pixel. The records of a pixel sit in arbitrary order; they are replayed by increasing point index
+// (selection by "smallest index above the last one": pixels hold a handful of points), summed in float32 one by one
+// as `front[c, r, :] += x[2:]` does (:172-177), then divided by the float32 count (:178).
+__global__ void __launch_bounds__(kPointThreads)
+pyfront_reduce_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ pix_off, FrameOffsets offs,
+                      PyFrontParams fp, float *__restrict__ front)
+{
+    const int f = blockIdx.y;
+    const unsigned *off = pix_off + (size_t)f * (fp.pixels + 1);
+    const uint4 *rec = binned + offs.off[f];
+    float *out = front + (size_t)f * fp.pixels * 3;
+    for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < fp.pixels; pix += gridDim.x * blockDim.x) {
+        const unsigned beg = off[pix], n = off[pix + 1] - beg;
+        float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f;
+        long long last = -1;
+        for (unsigned k = 0; k < n; k++) {
+            unsigned best = 0xFFFFFFFFu, at = 0;
+            if (n == 1) {
+                at = 0;
+            } else {
+                for (unsigned j = 0; j < n; j++) {
+                    const unsigned idx = __ldg(&rec[beg + j].x);
+                    if ((long long)idx > last && idx < best) { best = idx; at = j; }
+                }
+                last = best;
+            }
+            const uint4 q = __ldg(rec + beg + at);
+            s0 = __fadd_rn(s0, __uint_as_float(q.y));
+            s1 = __fadd_rn(s1, __uint_as_float(q.z));
+            s2 = __fadd_rn(s2, __uint_as_float(q.w));
+        }
+        if (n) {
+            const float c = (float)n;
+            s0 = __fdiv_rn(s0, c); s1 = __fdiv_rn(s1, c); s2 = __fdiv_rn(s2, c);
+        }
+        out[(size_t)pix * 3 + 0] = s0;
+        out[(size_t)pix * 3 + 1] = s1;
+        out[(size_t)pix * 3 + 2] = s2;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // ATOMIC strategy
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) fill_zero_kernel(float *__restrict__ dst, size_t count)
@@ -781,6 +885,30 @@ int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const Vie
 {
     dim3 grid(point_blocks(p.front_pixels), batch);
     front_finalize_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, fv_winner, front);
+    return 1;
+}
+
+int launch_pyfront_count(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const PyFrontParams &fp,
+                         int batch, int max_points, uint2 *keys, unsigned *pix_count, cudaStream_t s)
+{
+    dim3 grid(point_blocks(max_points), batch);
+    pyfront_count_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, fp, keys, pix_count);
+    return 1;
+}
+
+int launch_pyfront_bin(const float4 *pts, const FrameOffsets &offs, const PyFrontParams &fp, int batch, int max_points,
+                       const uint2 *keys, const unsigned *pix_off, uint4 *binned, cudaStream_t s)
+{
+    dim3 grid(point_blocks(max_points), batch);
+    pyfront_bin_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, fp, keys, pix_off, binned);
+    return 1;
+}
+
+int launch_pyfront_reduce(const uint4 *binned, const unsigned *pix_off, const FrameOffsets &offs, const PyFrontParams &fp,
+                          int batch, float *front, cudaStream_t s)
+{
+    dim3 grid(point_blocks(fp.pixels), batch);
+    pyfront_reduce_kernel<<<grid, kPointThreads, 0, s>>>(binned, pix_off, offs, fp, front);
     return 1;
 }
 

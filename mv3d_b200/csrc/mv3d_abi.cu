@@ -15,6 +15,7 @@
 #include <cstdlib>
 #include <chrono>
 #include <cstring>
+#include <algorithm>
 #include <memory>
 #include <mutex>
 #include <vector>
@@ -91,11 +92,13 @@ struct HostSlot {
 
 // Kernel classes, in the order mv3d_kernel_name() reports them.
 enum KernelId { K_CLASSIFY = 0, K_TILE_SCAN, K_BIN, K_TILE_BUILD, K_FRONT_FINALIZE, K_FILL_ZERO, K_ATOMIC_SCATTER,
-                K_ATOMIC_FINALIZE, K_FILL_TMA, K_WARP_PATCH, K_TILE_COMPACT, K_COUNT };
+                K_ATOMIC_FINALIZE, K_FILL_TMA, K_WARP_PATCH, K_TILE_COMPACT, K_PYFRONT_COUNT,
+                K_PYFRONT_BIN, K_PYFRONT_REDUCE, K_COUNT };
 static const char *const kKernelNames[K_COUNT] = {"classify_kernel", "tile_scan_kernel", "bin_kernel",
                                                   "tile_build_kernel", "front_finalize_kernel", "fill_zero_kernel",
                                                   "atomic_scatter_kernel", "atomic_finalize_kernel",
-                                                  "fill_tma_kernel", "warp_patch_kernel", "tile_compact_kernel"};
+                                                  "fill_tma_kernel", "warp_patch_kernel", "tile_compact_kernel",
+                                                  "pyfront_count_kernel", "pyfront_bin_kernel", "pyfront_reduce_kernel"};
 
 struct TimedLaunch {
     cudaEvent_t start, stop;
@@ -111,7 +114,8 @@ struct mv3d_ctx {
     int device = 0;
     int sm_count = 0;
     size_t smem_optin = 0;
-    float *lut = nullptr;
+    float *lut = nullptr;     // density table of the C routines
+    float *lut_py = nullptr;  // density table of the Python encoder (all-double log)
     Workspace ws;            // used by mv3d_encode_batch_dev (one call in flight per context)
     HostSlot slots[kSlots];  // used by mv3d_encode_batch_host
     std::unique_ptr<mv3d::HostPool> pool;  // host threads of the compact read-back (created on first use)
@@ -178,6 +182,16 @@ static void release(Workspace &w)
 {
     release(w.keys); release(w.binned); release(w.tile_count); release(w.tile_off);
     release(w.fv_winner); release(w.cellkey);
+}
+
+static void build_density_lut_py(float *v)
+{
+    // src/data.py:354: min(1, np.log(count+1)/math.log(32)) -- all double, then stored into a float32 array
+    for (int c = 0; c < kDensityLutSize; c++) {
+        volatile double arg = (double)c + 1.0, base = 32.0;
+        const double val = log(arg) / log(base);
+        v[c] = (float)(val < 1.0 ? val : 1.0);
+    }
 }
 
 static void build_density_lut(float *v)
@@ -258,6 +272,13 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
         delete ctx;
         return -1;
     }
+    build_density_lut_py(lut);
+    if (cudaMalloc(&ctx->lut_py, sizeof(lut)) != cudaSuccess ||
+        cudaMemcpy(ctx->lut_py, lut, sizeof(lut), cudaMemcpyHostToDevice) != cudaSuccess) {
+        fail("mv3d_ctx_create: cannot allocate the density table: %s", cudaGetErrorString(cudaGetLastError()));
+        mv3d_ctx_destroy(ctx);
+        return -1;
+    }
     *out = ctx;
     return 0;
 }
@@ -279,6 +300,7 @@ extern "C" void mv3d_ctx_destroy(mv3d_ctx *ctx)
         if (s.stream) cudaStreamDestroy(s.stream);
     }
     if (ctx->lut) cudaFree(ctx->lut);
+    if (ctx->lut_py) cudaFree(ctx->lut_py);
     if (ctx->side_stream) cudaStreamDestroy(ctx->side_stream);
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
@@ -923,6 +945,190 @@ extern "C" int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, c
             if (e != cudaSuccess && rc == 0) rc = fail("pipeline failed: %s", cudaGetErrorString(e));
         }
     return rc;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Python-twin semantics: the reference's PYTHON encoders, src/data.py:296-367
+// lidar_to_top and :113-180 lidar_to_front_fast -- what preprocess_for_mv3d.py and the training loaders run.
+// ------------------------------------------------------------------------------------------------
+static int make_py_params(const mv3d_ctx *ctx, const mv3d_pytwin_params *pp, bool want_top, ViewParams *out,
+                          PyFrontParams *fout)
+{
+    if (!pp) return fail("pytwin parameters are required");
+    if (pp->xn < 0 || pp->yn < 0 || pp->zn < 0) return fail("negative grid size %d x %d x %d", pp->xn, pp->yn, pp->zn);
+    if (pp->zn >= (int)kNoSlice) return fail("too many height slices (%d)", pp->zn);
+    const long long cells = (long long)pp->xn * pp->yn;
+    if (cells >= (1LL << 31) - 8) return fail("grid %d x %d has too many cells", pp->xn, pp->yn);
+    ViewParams p;
+    memset(&p, 0, sizeof(p));
+    p.py = 1;
+    p.py_center_car = pp->filter_center_car ? 1 : 0;
+    p.x_min = pp->x_min; p.y_min = pp->y_min; p.z_min = pp->z_min;
+    p.x_max = pp->x_max; p.y_max = pp->y_max; p.z_max = pp->z_max;
+    p.x_div = pp->x_div; p.y_div = pp->y_div; p.z_div = pp->z_div;
+    p.xn = pp->xn; p.yn = pp->yn; p.zn = pp->zn; p.planes = pp->zn + 2;
+    p.want_top = want_top ? 1 : 0;
+    p.want_front = 0;  // the C routine's front view is not part of this mode
+    p.top_frame_floats = cells * p.planes;
+    p.tile_cells = pick_tile_cells(ctx->tile_bytes_target, p.planes, cells);
+    p.tiles_per_frame = cells ? (int)((cells + p.tile_cells - 1) / p.tile_cells) : 0;
+    PyFrontParams f;
+    memset(&f, 0, sizeof(f));
+    f.ang_res = pp->ang_res; f.vert_res = pp->vert_res; f.velodyne_height = pp->velodyne_height;
+    f.r_offset = pp->front_r_offset; f.c_offset = pp->front_c_offset;
+    f.r_min = pp->front_r_min; f.r_max = pp->front_r_max; f.c_min = pp->front_c_min; f.c_max = pp->front_c_max;
+    f.width = pp->front_width; f.height = pp->front_height;
+    if (f.width < 0 || f.height < 0 || (long long)f.width * f.height > (1LL << 28))
+        return fail("front view %d x %d is out of range", f.width, f.height);
+    f.pixels = f.width * f.height;
+    *out = p;
+    *fout = f;
+    return 0;
+}
+
+static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
+                            float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp, cudaStream_t s)
+{
+    FrameOffsets offs;
+    memset(&offs, 0, sizeof(offs));
+    const int origin = offsets[0];
+    int max_points = 0;
+    for (int i = 0; i <= batch; i++) offs.off[i] = offsets[i] - origin;
+    for (int i = 0; i < batch; i++) max_points = std::max(max_points, offs.off[i + 1] - offs.off[i]);
+    const size_t total = (size_t)offs.off[batch];
+    const float4 *pts = reinterpret_cast<const float4 *>(points_dev) + origin;
+    if (ensure(ws.keys, total * sizeof(uint2) + 16, false, s)) return -1;
+    if (ensure(ws.binned, total * sizeof(uint4) + 16, false, s)) return -1;
+    uint2 *keys = static_cast<uint2 *>(ws.keys.ptr);
+    uint4 *binned = static_cast<uint4 *>(ws.binned.ptr);
+
+    if (top_dev && p.top_frame_floats > 0) {
+        mv3d_top_params tp;
+        memset(&tp, 0, sizeof(tp));
+        tp.xn = p.xn; tp.yn = p.yn; tp.zn = p.zn;
+        if (!tile_feasible(ctx, &tp, false)) return fail("python-twin mode needs the tile strategy: a tile of this grid does not fit shared memory");
+        const size_t hist = (size_t)batch * (p.tiles_per_frame + 1) * 4;
+        if (ensure(ws.tile_count, hist, true, s)) return -1;
+        if (ensure(ws.tile_off, hist, false, s)) return -1;
+        unsigned *tcount = static_cast<unsigned *>(ws.tile_count.ptr), *toff = static_cast<unsigned *>(ws.tile_off.ptr);
+        int blocks_per_sm = 0;
+        CUDA_TRY(tile_build_configure(p, &blocks_per_sm));
+        if (blocks_per_sm < 1) return fail("tile kernel does not fit: %zu bytes of shared memory", tile_smem_bytes(p));
+        timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, nullptr, s); });
+        timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
+        timed_launch(ctx, K_BIN, s, [&] { return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s); });
+        timed_launch(ctx, K_TILE_BUILD, s, [&] {
+            return launch_tile_build(binned, toff, offs, p, ctx->lut_py, top_dev, batch, blocks_per_sm * ctx->sm_count, s);
+        });
+    }
+    if (front_dev && fp.pixels > 0) {
+        // same scratch, reused in stream order; the pixel histogram is self-cleaning like the tile histogram
+        const size_t hist = (size_t)batch * (fp.pixels + 1) * 4;
+        if (ensure(ws.tile_count, hist, true, s)) return -1;
+        if (ensure(ws.tile_off, hist, false, s)) return -1;
+        unsigned *pcount = static_cast<unsigned *>(ws.tile_count.ptr), *poff = static_cast<unsigned *>(ws.tile_off.ptr);
+        timed_launch(ctx, K_PYFRONT_COUNT, s, [&] { return launch_pyfront_count(pts, offs, p, fp, batch, max_points, keys, pcount, s); });
+        timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(pcount, poff, fp.pixels, batch, s); });
+        timed_launch(ctx, K_PYFRONT_BIN, s, [&] { return launch_pyfront_bin(pts, offs, fp, batch, max_points, keys, poff, binned, s); });
+        timed_launch(ctx, K_PYFRONT_REDUCE, s, [&] { return launch_pyfront_reduce(binned, poff, offs, fp, batch, front_dev, s); });
+    }
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+static int py_encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
+                                float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp, cudaStream_t s)
+{
+    if (offsets[batch] > offsets[0] && (reinterpret_cast<uintptr_t>(points_dev) & 15u))
+        return fail("points_dev must be 16-byte aligned");
+    for (int c0 = 0; c0 < batch; c0 += kMaxBatchPerLaunch) {
+        const int nb = std::min(batch - c0, kMaxBatchPerLaunch);
+        float *top_c = top_dev ? top_dev + (size_t)c0 * (size_t)p.top_frame_floats : nullptr;
+        float *front_c = front_dev ? front_dev + (size_t)c0 * (size_t)fp.pixels * 3 : nullptr;
+        if (enqueue_py_chunk(ctx, ws, points_dev, offsets + c0, nb, top_c, front_c, p, fp, s)) return -1;
+    }
+    return 0;
+}
+
+extern "C" int mv3d_pytwin_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *offsets_host, int batch,
+                                            float *top_dev, float *front_dev, const mv3d_pytwin_params *pp, void *stream)
+{
+    if (!ctx) return fail("mv3d_pytwin_encode_batch_dev: ctx is NULL");
+    if (check_offsets(offsets_host, batch)) return -1;
+    ViewParams p;
+    PyFrontParams fp;
+    if (make_py_params(ctx, pp, top_dev != nullptr, &p, &fp)) return -1;
+    if (batch == 0 || (!top_dev && !front_dev)) return 0;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    return py_encode_dev_locked(ctx, ctx->ws, points_dev, offsets_host, batch, top_dev, front_dev, p, fp,
+                                static_cast<cudaStream_t>(stream));
+}
+
+// Host buffers: sweep by sweep over the slot streams (H2D, encode, dense D2H).
+extern "C" int mv3d_pytwin_encode_batch_host(mv3d_ctx *ctx, const float *points_host, const int *offsets_host, int batch,
+                                             float *top_host, float *front_host, const mv3d_pytwin_params *pp)
+{
+    if (!ctx) return fail("mv3d_pytwin_encode_batch_host: ctx is NULL");
+    if (check_offsets(offsets_host, batch)) return -1;
+    ViewParams p;
+    PyFrontParams fp;
+    if (make_py_params(ctx, pp, top_host != nullptr, &p, &fp)) return -1;
+    if (batch == 0 || (!top_host && !front_host)) return 0;
+    if (offsets_host[batch] > offsets_host[0] && !points_host) return fail("points_host is NULL");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    const size_t top_bytes = (size_t)p.top_frame_floats * 4, front_bytes = (size_t)fp.pixels * 3 * 4;
+    int rc = 0;
+    for (int i = 0; i < batch && rc == 0; i++) {
+        HostSlot &slot = ctx->slots[i % kSlots];
+        if (!slot.stream) CUDA_TRY(cudaStreamCreateWithFlags(&slot.stream, cudaStreamNonBlocking));
+        cudaStream_t s = slot.stream;
+        const int n = offsets_host[i + 1] - offsets_host[i];
+        if (ensure(slot.points, (size_t)n * 16 + 16, false, s)) { rc = -1; break; }
+        if (top_host && ensure(slot.top, top_bytes + 16, false, s)) { rc = -1; break; }
+        if (front_host && ensure(slot.front, front_bytes + 16, false, s)) { rc = -1; break; }
+        if (n > 0)
+            CUDA_TRY(cudaMemcpyAsync(slot.points.ptr, points_host + (size_t)offsets_host[i] * 4, (size_t)n * 16,
+                                     cudaMemcpyHostToDevice, s));
+        const int local_off[2] = {0, n};
+        float *top_d = top_host ? static_cast<float *>(slot.top.ptr) : nullptr;
+        float *front_d = front_host ? static_cast<float *>(slot.front.ptr) : nullptr;
+        if (py_encode_dev_locked(ctx, slot.ws, static_cast<const float *>(slot.points.ptr), local_off, 1, top_d, front_d,
+                                 p, fp, s)) { rc = -1; break; }
+        ctx->h2d_bytes += (size_t)n * 16;
+        ctx->d2h_bytes += (top_host ? top_bytes : 0) + (front_host ? front_bytes : 0);
+        if (top_host && top_bytes)
+            CUDA_TRY(cudaMemcpyAsync(top_host + (size_t)i * (size_t)p.top_frame_floats, top_d, top_bytes,
+                                     cudaMemcpyDeviceToHost, s));
+        if (front_host && front_bytes)
+            CUDA_TRY(cudaMemcpyAsync(front_host + (size_t)i * (size_t)fp.pixels * 3, front_d, front_bytes,
+                                     cudaMemcpyDeviceToHost, s));
+    }
+    for (auto &slot : ctx->slots)
+        if (slot.stream) {
+            cudaError_t e = cudaStreamSynchronize(slot.stream);
+            if (e != cudaSuccess && rc == 0) rc = fail("pipeline failed: %s", cudaGetErrorString(e));
+        }
+    return rc;
+}
+
+// Test hook: the device restatement of the C library's atan2f that the Python front view uses (fd_atan2f).
+__global__ void atan2f_probe_kernel(const float *y, const float *x, float *out, int n)
+{
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) out[i] = fd_atan2f(y[i], x[i]);
+}
+
+extern "C" int mv3d_debug_atan2f(mv3d_ctx *ctx, const float *y_dev, const float *x_dev, float *out_dev, int n, void *stream)
+{
+    if (!ctx) return fail("mv3d_debug_atan2f: ctx is NULL");
+    if (n <= 0) return 0;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    atan2f_probe_kernel<<<1184, 256, 0, static_cast<cudaStream_t>(stream)>>>(y_dev, x_dev, out_dev, n);
+    ctx->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
 }
 
 // Test hook for the host half of the compact read-back (needs no GPU).

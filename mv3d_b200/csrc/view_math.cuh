@@ -18,6 +18,9 @@ struct ViewParams {
     float x_div, y_div, z_div;
     int xn, yn, zn, planes;       // planes = zn + 2
     int quant_floor;              // 0: (int)q [T:107-109]   1: (int)floor(q) [TF:124-126]
+    int py;                       // 1: semantics of the reference's PYTHON lidar_to_top (src/data.py:296-367), see py_classify
+    int py_center_car;            // src/data.py:224-227,313-314
+    float x_max, y_max, z_max;    // the Python encoders crop with open intervals on all three axes
     int want_top, want_front;
     long long top_frame_floats;   // xn*yn*planes
     // output tiling (tile strategy): a tile is tile_cells consecutive output cells = one contiguous chunk
@@ -40,6 +43,8 @@ struct FrameOffsets {            // first point of each sweep in the packed poin
 constexpr int kDensityLutSize = 32;  // min(1, (float)(logf(c+1)/log(32))) for c = 0..31, built on the host with libm
 
 constexpr uint32_t kInvalidKey = 0xFFFFFFFFu;
+constexpr uint32_t kLowerFlag = 0x8000u;     // Python twin, slice field of a binned record: also closes the slice below
+constexpr uint32_t kNoSlice = 0x7FFFu;       // Python twin: floor(qz) is past the last slice
 constexpr uint32_t kNoCell = 0xFFFFFFFFu;   // unused slot of the compact read-back list
 constexpr uint32_t kRawTag = 0x80000000u;   // marks an un-finalised height slot in the atomic strategy
 
@@ -67,11 +72,68 @@ struct CellHit {
     uint32_t cell;   // output cell (X-1)*yn + (Y-1)
     int slice;       // Z
     float h;         // z - z_MIN, the comparison key of T:115,141 / TF:133,159
+    bool lower;      // Python twin only: the point also closes slice Z-1 (its qz is integral)
 };
+
+// ---- the reference's PYTHON bird's-eye view (src/data.py:296-367), on float32 like numpy computes it ----
+
+// numpy's float32 floor_divide (npy_divmodf): the quotient is rebuilt from fmodf, it is NOT floorf(a / b).
+// fmodf is exact in CUDA as in C. Restated on the CPU in oracle/pytwin_oracle.c and checked against numpy.
+__device__ __forceinline__ float npy_floor_dividef(float a, float b)
+{
+    if (b == 0.0f) return __fdiv_rn(a, b);
+    const float mod = fmodf(a, b);
+    float div = __fdiv_rn(__fsub_rn(a, mod), b);
+    if (mod != 0.0f && ((b < 0.0f) != (mod < 0.0f))) div = __fsub_rn(div, 1.0f);
+    if (div != 0.0f) {
+        float fl = floorf(div);
+        if (__fsub_rn(div, fl) > 0.5f) fl = __fadd_rn(fl, 1.0f);
+        return fl;
+    }
+    return copysignf(0.0f, __fdiv_rn(a, b));
+}
+
+// Open-interval crop on all three axes (src/data.py:298-311 = :130-143); NaN fails every comparison.
+__device__ __forceinline__ bool py_crop(const float4 &pt, const ViewParams &p)
+{
+    return pt.x > p.x_min && pt.x < p.x_max && pt.y > p.y_min && pt.y < p.y_max && pt.z > p.z_min && pt.z < p.z_max;
+}
+
+
+// Gate, cell and slice key of the Python encoder:
+//   crop (open intervals) [+ centre-car filter], qx/qy by numpy floor_divide, qz = (z - z_MIN) / z_DIV kept fractional
+//   (:321-324); only 0 <= qx < Xn, 0 <= qy < Yn are ever visited (:341,:347); the cell is written flipped at
+//   top[-qx-1, -qy-1] (:345,:352). The comparison key is qz (> 0 after the crop): slice z takes every point with
+//   z <= qz <= z + 1, BOTH ends inclusive (:359), so an integral qz also closes the slice below. qz bits order
+//   like unsigned integers, exactly as h does for the C routine, so the same reduction serves both.
+__device__ __forceinline__ CellHit py_classify(const float4 &pt, const ViewParams &p)
+{
+    CellHit c;
+    c.keep = false;
+    c.cell = kInvalidKey;
+    c.slice = 0;
+    c.h = 0.0f;
+    c.lower = false;
+    if (!py_crop(pt, p)) return c;
+    if (p.py_center_car && !(fabsf(pt.x) > 2.35f || fabsf(pt.y) > 1.05f)) return c;  // f32(4.7/2), f32(2.1/2)
+    const int qx = cvtt_f32(npy_floor_dividef(__fsub_rn(pt.x, p.x_min), p.x_div));
+    const int qy = cvtt_f32(npy_floor_dividef(__fsub_rn(pt.y, p.y_min), p.y_div));
+    if (!(qx >= 0 && qx < p.xn && qy >= 0 && qy < p.yn)) return c;
+    const float qz = __fdiv_rn(__fsub_rn(pt.z, p.z_min), p.z_div);
+    const float fl = floorf(qz);
+    c.keep = true;
+    c.cell = (uint32_t)((p.xn - 1 - qx) * p.yn + (p.yn - 1 - qy));
+    c.slice = cvtt_f32(fl);
+    c.h = qz;
+    c.lower = (qz == fl) && c.slice >= 1;
+    return c;
+}
 
 __device__ __forceinline__ CellHit classify(const float4 &pt, const ViewParams &p)
 {
+    if (p.py) return py_classify(pt, p);
     CellHit c;
+    c.lower = false;
     const int X = quantise(pt.x, p.x_min, p.x_div, p.quant_floor);
     const int Y = quantise(pt.y, p.y_min, p.y_div, p.quant_floor);
     const int Z = quantise(pt.z, p.z_min, p.z_div, p.quant_floor);
@@ -161,6 +223,114 @@ __device__ __forceinline__ void front_values(const float4 &pt, const ViewParams 
     v0 = (float)cvtt_f32(__fmul_rn(__fdiv_rn(__fsub_rn(pt.z, p.z_min), p.z_span), 255.0f));
     v1 = (float)cvtt_f64(__dmul_rn(__ddiv_rn(planar, 120.0), 255.0));
     v2 = (float)cvtt_f32(__fmul_rn(__fsub_rn(pt.w, 0.0f), 255.0f));
+}
+
+// ---- the reference's PYTHON front view (src/data.py:113-180) ---------------------------------------------------
+// np.arctan2 on float32 was the C library's atan2f when the reference was written; glibc's (<= 2.40) is the fdlibm
+// single-precision routine, which is not correctly rounded. This is that routine, operation for operation
+// (e_atan2f.c / s_atanf.c; restated on the CPU in oracle/pytwin_oracle.c and pinned there to libm's atan2f).
+__device__ __forceinline__ float fd_atanf(float x)
+{
+    const float atanhi[4] = {4.6364760399e-01f, 7.8539812565e-01f, 9.8279368877e-01f, 1.5707962513e+00f};
+    const float atanlo[4] = {5.0121582440e-09f, 3.7748947079e-08f, 3.4473217170e-08f, 7.5497894159e-08f};
+    const int32_t hx = __float_as_int(x);
+    const int32_t ix = hx & 0x7fffffff;
+    int id;
+    if (ix >= 0x4c000000) {  // |x| >= 2^25
+        if (ix > 0x7f800000) return __fadd_rn(x, x);
+        const float r = __fadd_rn(atanhi[3], atanlo[3]);
+        return hx > 0 ? r : -r;
+    }
+    if (ix < 0x3ee00000) {  // |x| < 0.4375
+        if (ix < 0x31000000) return x;
+        id = -1;
+    } else {
+        x = fabsf(x);
+        if (ix < 0x3f980000) {
+            if (ix < 0x3f300000) { id = 0; x = __fdiv_rn(__fsub_rn(__fmul_rn(2.0f, x), 1.0f), __fadd_rn(2.0f, x)); }
+            else { id = 1; x = __fdiv_rn(__fsub_rn(x, 1.0f), __fadd_rn(x, 1.0f)); }
+        } else {
+            if (ix < 0x401c0000) { id = 2; x = __fdiv_rn(__fsub_rn(x, 1.5f), __fadd_rn(1.0f, __fmul_rn(1.5f, x))); }
+            else { id = 3; x = __fdiv_rn(-1.0f, x); }
+        }
+    }
+    const float z = __fmul_rn(x, x);
+    const float w = __fmul_rn(z, z);
+#define MV3D_H(c, t) __fadd_rn(c, __fmul_rn(w, t))
+    const float s1 = __fmul_rn(z, MV3D_H(3.3333334327e-01f, MV3D_H(1.4285714924e-01f, MV3D_H(9.0908870101e-02f,
+                     MV3D_H(6.6610731184e-02f, MV3D_H(4.9768779427e-02f, 1.6285819933e-02f))))));
+    const float s2 = __fmul_rn(w, MV3D_H(-2.0000000298e-01f, MV3D_H(-1.1111110449e-01f, MV3D_H(-7.6918758452e-02f,
+                     MV3D_H(-5.8335702866e-02f, -3.6531571299e-02f)))));
+#undef MV3D_H
+    const float xs = __fmul_rn(x, __fadd_rn(s1, s2));
+    if (id < 0) return __fsub_rn(x, xs);
+    const float r = __fsub_rn(atanhi[id], __fsub_rn(__fsub_rn(xs, atanlo[id]), x));
+    return hx < 0 ? -r : r;
+}
+
+__device__ __forceinline__ float fd_atan2f(float y, float x)
+{
+    const float tiny = 1.0e-30f, pi_o_4 = 7.8539818525e-01f, pi_o_2 = 1.5707963705e+00f, pi = 3.1415927410e+00f,
+                pi_lo = -8.7422776573e-08f;
+    const int32_t hx = __float_as_int(x), hy = __float_as_int(y);
+    const int32_t ix = hx & 0x7fffffff, iy = hy & 0x7fffffff;
+    if (ix > 0x7f800000 || iy > 0x7f800000) return __fadd_rn(x, y);
+    if (hx == 0x3f800000) return fd_atanf(y);
+    const int m = ((hy >> 31) & 1) | ((hx >> 30) & 2);
+    if (iy == 0) return m < 2 ? y : (m == 2 ? __fadd_rn(pi, tiny) : __fsub_rn(-pi, tiny));
+    if (ix == 0) return hy < 0 ? __fsub_rn(-pi_o_2, tiny) : __fadd_rn(pi_o_2, tiny);
+    if (ix == 0x7f800000) {
+        if (iy == 0x7f800000) {
+            const float q3 = __fmul_rn(3.0f, pi_o_4);
+            return m == 0 ? __fadd_rn(pi_o_4, tiny) : m == 1 ? __fsub_rn(-pi_o_4, tiny)
+                 : m == 2 ? __fadd_rn(q3, tiny) : __fsub_rn(-q3, tiny);
+        }
+        return m == 0 ? 0.0f : m == 1 ? -0.0f : m == 2 ? __fadd_rn(pi, tiny) : __fsub_rn(-pi, tiny);
+    }
+    if (iy == 0x7f800000) return hy < 0 ? __fsub_rn(-pi_o_2, tiny) : __fadd_rn(pi_o_2, tiny);
+    const int32_t k = (iy - ix) >> 23;
+    float z;
+    if (k > 60) z = __fadd_rn(pi_o_2, __fmul_rn(0.5f, pi_lo));
+    else if (hx < 0 && k < -60) z = 0.0f;
+    else z = fd_atanf(fabsf(__fdiv_rn(y, x)));
+    switch (m) {
+    case 0: return z;
+    case 1: return -z;
+    case 2: return __fsub_rn(pi, __fsub_rn(z, pi_lo));
+    default: return __fsub_rn(__fsub_rn(z, pi_lo), pi);
+    }
+}
+
+// Parameters of the Python front view (src/config.py:32-42), by value in the kernel parameter space.
+struct PyFrontParams {
+    float ang_res, vert_res, velodyne_height;   // narrowed to float32 like numpy does with a Python scalar
+    int r_offset, c_offset, r_min, r_max, c_min, c_max, width, height;
+    int pixels;                                  // width * height
+};
+
+// Pixel c * HEIGHT + r of a point that passed the crop, or -1 (src/data.py:121-126,145-166): float32 atan2 over the
+// float32 resolution, truncated; open-interval window on the bins, offsets, then the image bounds.
+__device__ __forceinline__ int py_front_pixel(const float4 &pt, const PyFrontParams &f)
+{
+    const int c = cvtt_f32(__fdiv_rn(fd_atan2f(pt.y, pt.x), f.ang_res));
+    const float planar = __fsqrt_rn(__fadd_rn(__fmul_rn(pt.x, pt.x), __fmul_rn(pt.y, pt.y)));
+    const int r = cvtt_f32(__fdiv_rn(fd_atan2f(pt.z, planar), f.vert_res));
+    if (!(f.c_min < c && c < f.c_max && f.r_min < r && r < f.r_max)) return -1;
+    const int cc = c + f.c_offset, rr = r + f.r_offset;
+    if (!(cc >= 0 && cc < f.width && rr >= 0 && rr < f.height)) return -1;
+    return cc * f.height + rr;
+}
+
+// The three channel values a point adds to its pixel (src/data.py:115-120): clip(z + 1.73, 0), the norm of
+// (x, y, z, intensity) -- sic, the intensity is inside the norm --, the intensity. All float32.
+__device__ __forceinline__ float3 py_front_values(const float4 &pt, const PyFrontParams &f)
+{
+    float3 v;
+    v.x = fmaxf(__fadd_rn(pt.z, f.velodyne_height), 0.0f);
+    v.y = __fsqrt_rn(__fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(pt.x, pt.x), __fmul_rn(pt.y, pt.y)), __fmul_rn(pt.z, pt.z)),
+                               __fmul_rn(pt.w, pt.w)));
+    v.z = pt.w;
+    return v;
 }
 
 // Streaming 128-bit point load: every point is read once per pass, keep it out of L1.

@@ -89,11 +89,11 @@ def test_known_answers(pytwin):
     top = pytwin.lidar_to_top(qc["crop_edges"][1], k)
     assert np.count_nonzero(top[..., k.zn + 1]) == 5
     # output is written flipped: the point at x -> 0+, y = 0 lands in the last row
-    assert top[k.xn - 1, k.yn - 1 - 300, k.zn + 1] > 0
+    assert top[k.xn - 1, k.yn - 1 - int(np.float32(30) // np.float32(0.1)), k.zn + 1] > 0
     # an integral qz closes the slice below with 1.0
     t = pytwin.lidar_to_top(qc["integral_qz"][1], k)
-    cell = t[k.xn - 1 - 101, k.yn - 1 - 320]  # qz = 1 exactly: slice 0 holds 1.0, slice 1 holds 0
-    assert cell[0] == 1.0 and cell[1] == 0.0
+    cell = t[k.xn - 1 - 105, k.yn - 1 - 320]  # qz = 5 exactly: slice 4 holds 1.0, slice 5 holds 0
+    assert cell[4] == 1.0 and cell[5] == 0.0 and not cell[:4].any()
     # density saturates at 31 points; intensity is the first of the tied maxima
     lut = pytwin.density_table()
     t = pytwin.lidar_to_top(qc["ties_density"][1], k)
