@@ -142,6 +142,9 @@ classify_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
 // Writes tiles_per_frame+1 offsets and clears the histogram for the next call (self-cleaning workspace).
 // ------------------------------------------------------------------------------------------------
 constexpr int kScanThreads = 1024;
+// kScanItems consecutive entries per thread and round (2 for the tile histograms, 32 for the 150k-pixel histogram of
+// the Python front view: one CTA per sweep, so the number of rounds is what costs).
+template <int kScanItems>
 __global__ void __launch_bounds__(kScanThreads)
 tile_scan_kernel(unsigned *__restrict__ tile_count, unsigned *__restrict__ tile_off, int tiles_per_frame)
 {
@@ -152,11 +155,17 @@ tile_scan_kernel(unsigned *__restrict__ tile_count, unsigned *__restrict__ tile_
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
-    for (int t0 = 0; t0 < tiles_per_frame; t0 += kScanThreads) {
-        const int t = t0 + threadIdx.x;
-        unsigned v = 0;
-        if (t < tiles_per_frame) { v = cnt[t]; cnt[t] = 0; }
-        unsigned incl = v;
+    for (int t0 = 0; t0 < tiles_per_frame; t0 += kScanThreads * kScanItems) {
+        const int first = t0 + (int)threadIdx.x * kScanItems;
+        unsigned v[kScanItems];
+        unsigned sum = 0;
+#pragma unroll
+        for (int j = 0; j < kScanItems; j++) {
+            v[j] = 0;
+            if (first + j < tiles_per_frame) { v[j] = cnt[first + j]; cnt[first + j] = 0; }
+            sum += v[j];
+        }
+        unsigned incl = sum;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             const unsigned up = __shfl_up_sync(0xFFFFFFFFu, incl, d);
@@ -175,10 +184,14 @@ tile_scan_kernel(unsigned *__restrict__ tile_count, unsigned *__restrict__ tile_
             if (lane < kScanThreads / 32) warp_sums[lane] = wincl - w;  // exclusive prefix of the warp totals
         }
         __syncthreads();
-        const unsigned excl = carry + warp_sums[warp] + incl - v;
-        if (t < tiles_per_frame) off[t] = excl;
+        unsigned excl = carry + warp_sums[warp] + incl - sum;  // entries before this thread's first one
+#pragma unroll
+        for (int j = 0; j < kScanItems; j++) {
+            if (first + j < tiles_per_frame) off[first + j] = excl;
+            excl += v[j];
+        }
         __syncthreads();
-        if (threadIdx.x == kScanThreads - 1) carry = excl + v;
+        if (threadIdx.x == kScanThreads - 1) carry = excl;
         __syncthreads();
     }
     if (threadIdx.x == 0) off[tiles_per_frame] = carry;
@@ -600,80 +613,71 @@ front_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPar
 
 // ------------------------------------------------------------------------------------------------
 // Python-twin front view (src/data.py:113-180 lidar_to_front_fast): per pixel, the MEAN of the channel values of
-// its points, accumulated by the reference as a float32 running sum in input order. Same three-pass shape as the
-// bird's-eye view -- count per pixel, scan (tile_scan_kernel with one "tile" per pixel), scatter -- then one
-// thread per pixel replays its points in input order.
+// its points, accumulated by the reference as a float32 running sum in input order.
+//   link   : every point that lands in the image is pushed on its pixel's list (atomicExch on the list head)
+//   reduce : one thread per pixel walks its list, puts the (few) point indices in increasing order, replays them
+//            -- values recomputed from the points, which sit in L2 -- and writes the whole image, zeros included.
+// No histogram, scan or scatter: a 1500 x 100 image would need a 150 k-entry scan per sweep for ~50 k points.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kPointThreads)
-pyfront_count_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p, PyFrontParams fp,
-                     uint2 *__restrict__ keys, unsigned *__restrict__ pix_count)
+pyfront_link_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p, PyFrontParams fp,
+                    unsigned *__restrict__ head, unsigned *__restrict__ next)
 {
     const int f = blockIdx.y;
     const int base = offs.off[f];
     const int n = offs.off[f + 1] - base;
-    unsigned *counts = pix_count + (size_t)f * (fp.pixels + 1);
+    unsigned *heads = head + (size_t)f * fp.pixels;
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float4 pt = load_point(pts + base + i);
-        int pix = -1;
-        if (py_crop(pt, p)) pix = py_front_pixel(pt, fp);
-        unsigned rank = 0;
-        if (pix >= 0) rank = atomicAdd(counts + pix, 1u);
-        keys[base + i] = make_uint2((unsigned)pix, rank);
+        if (!py_crop(pt, p)) continue;
+        const int pix = py_front_pixel(pt, fp);
+        if (pix >= 0) next[base + i] = atomicExch(heads + pix, (unsigned)i + 1u);  // 0 ends a list
     }
 }
 
-//   record = { point index, height, distance, intensity }
 __global__ void __launch_bounds__(kPointThreads)
-pyfront_bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, PyFrontParams fp, const uint2 *__restrict__ keys,
-                   const unsigned *__restrict__ pix_off, uint4 *__restrict__ binned)
+pyfront_reduce_kernel(const float4 *__restrict__ pts, FrameOffsets offs, PyFrontParams fp, unsigned *__restrict__ head,
+                      const unsigned *__restrict__ next, float *__restrict__ front)
 {
+    constexpr int kSmall = 16;
     const int f = blockIdx.y;
     const int base = offs.off[f];
-    const int n = offs.off[f + 1] - base;
-    const unsigned *off = pix_off + (size_t)f * (fp.pixels + 1);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint2 k = keys[base + i];
-        if (k.x == kInvalidKey) continue;
-        const float4 pt = load_point(pts + base + i);
-        const float3 v = py_front_values(pt, fp);
-        binned[(size_t)base + off[k.x] + k.y] =
-            make_uint4((uint32_t)i, __float_as_uint(v.x), __float_as_uint(v.y), __float_as_uint(v.z));
-    }
-}
-
-// One thread per pixel. The records of a pixel sit in arbitrary order; they are replayed by increasing point index
-// (selection by "smallest index above the last one": pixels hold a handful of points), summed in float32 one by one
-// as `front[c, r, :] += x[2:]` does (:172-177), then divided by the float32 count (:178).
-__global__ void __launch_bounds__(kPointThreads)
-pyfront_reduce_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ pix_off, FrameOffsets offs,
-                      PyFrontParams fp, float *__restrict__ front)
-{
-    const int f = blockIdx.y;
-    const unsigned *off = pix_off + (size_t)f * (fp.pixels + 1);
-    const uint4 *rec = binned + offs.off[f];
+    unsigned *heads = head + (size_t)f * fp.pixels;
     float *out = front + (size_t)f * fp.pixels * 3;
     for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < fp.pixels; pix += gridDim.x * blockDim.x) {
-        const unsigned beg = off[pix], n = off[pix + 1] - beg;
+        const unsigned h = heads[pix];
         float s0 = 0.0f, s1 = 0.0f, s2 = 0.0f;
-        long long last = -1;
-        for (unsigned k = 0; k < n; k++) {
-            unsigned best = 0xFFFFFFFFu, at = 0;
-            if (n == 1) {
-                at = 0;
-            } else {
-                for (unsigned j = 0; j < n; j++) {
-                    const unsigned idx = __ldg(&rec[beg + j].x);
-                    if ((long long)idx > last && idx < best) { best = idx; at = j; }
-                }
-                last = best;
+        if (h) {
+            heads[pix] = 0u;  // self-cleaning
+            unsigned idx[kSmall];
+            int n = 0;
+            for (unsigned e = h; e; e = next[base + (int)e - 1]) {
+                if (n < kSmall) idx[n] = e - 1u;
+                n++;
             }
-            const uint4 q = __ldg(rec + beg + at);
-            s0 = __fadd_rn(s0, __uint_as_float(q.y));
-            s1 = __fadd_rn(s1, __uint_as_float(q.z));
-            s2 = __fadd_rn(s2, __uint_as_float(q.w));
-        }
-        if (n) {
-            const float c = (float)n;
+            auto add = [&](unsigned i) {  // `front[c, r, :] += x[2:]` (:172-177): float32, one point at a time
+                const float3 v = py_front_values(pts[base + (int)i], fp);
+                s0 = __fadd_rn(s0, v.x); s1 = __fadd_rn(s1, v.y); s2 = __fadd_rn(s2, v.z);
+            };
+            if (n <= kSmall) {
+                for (int a = 1; a < n; a++) {  // insertion sort by point index = input order
+                    const unsigned v = idx[a];
+                    int b = a - 1;
+                    while (b >= 0 && idx[b] > v) { idx[b + 1] = idx[b]; b--; }
+                    idx[b + 1] = v;
+                }
+                for (int a = 0; a < n; a++) add(idx[a]);
+            } else {
+                long long last = -1;  // crowded pixel: repeatedly take the smallest index above the last one
+                for (int k = 0; k < n; k++) {
+                    unsigned best = 0xFFFFFFFFu;
+                    for (unsigned e = h; e; e = next[base + (int)e - 1])
+                        if ((long long)(e - 1u) > last && e - 1u < best) best = e - 1u;
+                    add(best);
+                    last = best;
+                }
+            }
+            const float c = (float)n;  // `front /= weight_mask` (:178)
             s0 = __fdiv_rn(s0, c); s1 = __fdiv_rn(s1, c); s2 = __fdiv_rn(s2, c);
         }
         out[(size_t)pix * 3 + 0] = s0;
@@ -816,7 +820,10 @@ int launch_classify(const float4 *pts, const FrameOffsets &offs, const ViewParam
 
 int launch_tile_scan(unsigned *tile_count, unsigned *tile_off, int tiles_per_frame, int batch, cudaStream_t s)
 {
-    tile_scan_kernel<<<batch, kScanThreads, 0, s>>>(tile_count, tile_off, tiles_per_frame);
+    if (tiles_per_frame > 16 * kScanThreads)
+        tile_scan_kernel<8><<<batch, kScanThreads, 0, s>>>(tile_count, tile_off, tiles_per_frame);
+    else
+        tile_scan_kernel<2><<<batch, kScanThreads, 0, s>>>(tile_count, tile_off, tiles_per_frame);
     return 1;
 }
 
@@ -888,27 +895,19 @@ int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const Vie
     return 1;
 }
 
-int launch_pyfront_count(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const PyFrontParams &fp,
-                         int batch, int max_points, uint2 *keys, unsigned *pix_count, cudaStream_t s)
+int launch_pyfront_link(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const PyFrontParams &fp,
+                        int batch, int max_points, unsigned *head, unsigned *next, cudaStream_t s)
 {
     dim3 grid(point_blocks(max_points), batch);
-    pyfront_count_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, fp, keys, pix_count);
+    pyfront_link_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, fp, head, next);
     return 1;
 }
 
-int launch_pyfront_bin(const float4 *pts, const FrameOffsets &offs, const PyFrontParams &fp, int batch, int max_points,
-                       const uint2 *keys, const unsigned *pix_off, uint4 *binned, cudaStream_t s)
-{
-    dim3 grid(point_blocks(max_points), batch);
-    pyfront_bin_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, fp, keys, pix_off, binned);
-    return 1;
-}
-
-int launch_pyfront_reduce(const uint4 *binned, const unsigned *pix_off, const FrameOffsets &offs, const PyFrontParams &fp,
-                          int batch, float *front, cudaStream_t s)
+int launch_pyfront_reduce(const float4 *pts, const FrameOffsets &offs, const PyFrontParams &fp, int batch, unsigned *head,
+                          const unsigned *next, float *front, cudaStream_t s)
 {
     dim3 grid(point_blocks(fp.pixels), batch);
-    pyfront_reduce_kernel<<<grid, kPointThreads, 0, s>>>(binned, pix_off, offs, fp, front);
+    pyfront_reduce_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, fp, head, next, front);
     return 1;
 }
 

@@ -32,12 +32,10 @@ int launch_warp_patch(const uint4 *binned, const unsigned *tile_off, const Frame
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
 int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch,
                           unsigned *fv_winner, float *front, cudaStream_t s);
-int launch_pyfront_count(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const PyFrontParams &fp,
-                         int batch, int max_points, uint2 *keys, unsigned *pix_count, cudaStream_t s);
-int launch_pyfront_bin(const float4 *pts, const FrameOffsets &offs, const PyFrontParams &fp, int batch, int max_points,
-                       const uint2 *keys, const unsigned *pix_off, uint4 *binned, cudaStream_t s);
-int launch_pyfront_reduce(const uint4 *binned, const unsigned *pix_off, const FrameOffsets &offs, const PyFrontParams &fp,
-                          int batch, float *front, cudaStream_t s);
+int launch_pyfront_link(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const PyFrontParams &fp,
+                        int batch, int max_points, unsigned *head, unsigned *next, cudaStream_t s);
+int launch_pyfront_reduce(const float4 *pts, const FrameOffsets &offs, const PyFrontParams &fp, int batch, unsigned *head,
+                          const unsigned *next, float *front, cudaStream_t s);
 int launch_point_keys(const float4 *pts, int n, const ViewParams &p, int *cell, int *pix, int *pix_exact, cudaStream_t s);
 int launch_fill_zero(float *dst, size_t count, int sm_count, cudaStream_t s);
 int launch_atomic_scatter(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,

@@ -92,13 +92,13 @@ struct HostSlot {
 
 // Kernel classes, in the order mv3d_kernel_name() reports them.
 enum KernelId { K_CLASSIFY = 0, K_TILE_SCAN, K_BIN, K_TILE_BUILD, K_FRONT_FINALIZE, K_FILL_ZERO, K_ATOMIC_SCATTER,
-                K_ATOMIC_FINALIZE, K_FILL_TMA, K_WARP_PATCH, K_TILE_COMPACT, K_PYFRONT_COUNT,
-                K_PYFRONT_BIN, K_PYFRONT_REDUCE, K_COUNT };
+                K_ATOMIC_FINALIZE, K_FILL_TMA, K_WARP_PATCH, K_TILE_COMPACT, K_PYFRONT_LINK,
+                K_PYFRONT_REDUCE, K_COUNT };
 static const char *const kKernelNames[K_COUNT] = {"classify_kernel", "tile_scan_kernel", "bin_kernel",
                                                   "tile_build_kernel", "front_finalize_kernel", "fill_zero_kernel",
                                                   "atomic_scatter_kernel", "atomic_finalize_kernel",
                                                   "fill_tma_kernel", "warp_patch_kernel", "tile_compact_kernel",
-                                                  "pyfront_count_kernel", "pyfront_bin_kernel", "pyfront_reduce_kernel"};
+                                                  "pyfront_link_kernel", "pyfront_reduce_kernel"};
 
 struct TimedLaunch {
     cudaEvent_t start, stop;
@@ -1022,15 +1022,12 @@ static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_de
         });
     }
     if (front_dev && fp.pixels > 0) {
-        // same scratch, reused in stream order; the pixel histogram is self-cleaning like the tile histogram
-        const size_t hist = (size_t)batch * (fp.pixels + 1) * 4;
-        if (ensure(ws.tile_count, hist, true, s)) return -1;
-        if (ensure(ws.tile_off, hist, false, s)) return -1;
-        unsigned *pcount = static_cast<unsigned *>(ws.tile_count.ptr), *poff = static_cast<unsigned *>(ws.tile_off.ptr);
-        timed_launch(ctx, K_PYFRONT_COUNT, s, [&] { return launch_pyfront_count(pts, offs, p, fp, batch, max_points, keys, pcount, s); });
-        timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(pcount, poff, fp.pixels, batch, s); });
-        timed_launch(ctx, K_PYFRONT_BIN, s, [&] { return launch_pyfront_bin(pts, offs, fp, batch, max_points, keys, poff, binned, s); });
-        timed_launch(ctx, K_PYFRONT_REDUCE, s, [&] { return launch_pyfront_reduce(binned, poff, offs, fp, batch, front_dev, s); });
+        // list heads per pixel (self-cleaning, zero between calls) and one link per point (reuses the key scratch)
+        if (ensure(ws.fv_winner, (size_t)batch * fp.pixels * 4, true, s)) return -1;
+        unsigned *head = static_cast<unsigned *>(ws.fv_winner.ptr);
+        unsigned *next = reinterpret_cast<unsigned *>(keys);
+        timed_launch(ctx, K_PYFRONT_LINK, s, [&] { return launch_pyfront_link(pts, offs, p, fp, batch, max_points, head, next, s); });
+        timed_launch(ctx, K_PYFRONT_REDUCE, s, [&] { return launch_pyfront_reduce(pts, offs, fp, batch, head, next, front_dev, s); });
     }
     CUDA_TRY(cudaGetLastError());
     return 0;
