@@ -13,8 +13,9 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libmv3d_encode.so")
-SOURCES = ["encode_kernels.cu", "mv3d_abi.cu", "host_expand.cu"]
-HEADERS = ["encode_kernels.h", "view_math.cuh", "host_expand.h", os.path.join("..", "..", "include", "mv3d_encode.h")]
+SOURCES = ["encode_kernels.cu", "mv3d_abi.cu", "host_expand.cu", "anchor_kernels.cu", "anchor_abi.cu"]
+HEADERS = ["encode_kernels.h", "view_math.cuh", "host_expand.h", "ctx.h", "anchor_kernels.h",
+           os.path.join("..", "..", "include", "mv3d_encode.h"), os.path.join("..", "..", "include", "mv3d_anchors.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
 
@@ -81,7 +82,10 @@ EXPORTED_SYMBOLS = (
     "mv3d_ctx_set_profiling", "mv3d_kernel_count", "mv3d_kernel_name", "mv3d_ctx_kernel_times",
     "mv3d_debug_point_keys", "mv3d_debug_expand_compact", "mv3d_ctx_transfer_bytes",
     "mv3d_pytwin_encode_batch_dev", "mv3d_pytwin_encode_batch_host", "mv3d_debug_atan2f",
+    "mv3d_ctx_set_anchors", "mv3d_remove_empty_anchor_dev", "mv3d_remove_empty_anchor_host",
 )
+ANCHORS_AUTO, ANCHORS_EXACT = 0, 1
+ANCHOR_MAX_LINES = 50
 
 _lib = None
 
@@ -126,6 +130,9 @@ def load_library() -> ctypes.CDLL:
     lib.mv3d_debug_atan2f.argtypes = [vp, vp, vp, vp, ci, vp]
     lib.mv3d_ctx_transfer_bytes.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong), ci]
     lib.mv3d_debug_expand_compact.argtypes = [vp, ctypes.c_size_t, ci, vp, ctypes.c_uint, ci]
+    lib.mv3d_ctx_set_anchors.argtypes = [vp, vp, ci]
+    lib.mv3d_remove_empty_anchor_dev.argtypes = [vp, vp, ci, ci, ci, ci, cf, ci, vp, vp, vp, vp]
+    lib.mv3d_remove_empty_anchor_host.argtypes = [vp, vp, ci, ci, ci, vp, ci, cf, ci, vp, ctypes.POINTER(ci)]
     _lib = lib
     return lib
 

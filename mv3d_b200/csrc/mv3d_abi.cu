@@ -4,10 +4,7 @@
 //
 // There is no CPU implementation in this library: every path ends in the sm_100a kernels of
 // encode_kernels.cu, and every failure is reported through mv3d_last_error().
-#include "../../include/mv3d_encode.h"
-#include "encode_kernels.h"
-#include "host_expand.h"
-#include "view_math.cuh"
+#include "ctx.h"
 
 #include <cmath>
 #include <cstdarg>
@@ -27,7 +24,7 @@ using namespace mv3d;
 // ------------------------------------------------------------------------------------------------
 static thread_local char g_error[512] = "";
 
-static int fail(const char *fmt, ...)
+int mv3d_fail(const char *fmt, ...)
 {
     va_list ap;
     va_start(ap, fmt);
@@ -36,153 +33,8 @@ static int fail(const char *fmt, ...)
     return -1;
 }
 
-#define CUDA_TRY(expr)                                                                              \
-    do {                                                                                            \
-        cudaError_t _e = (expr);                                                                    \
-        if (_e != cudaSuccess)                                                                      \
-            return fail("%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, __LINE__); \
-    } while (0)
-
 extern "C" const char *mv3d_last_error(void) { return g_error; }
 extern "C" const char *mv3d_version(void) { return "mv3d_encode 0.1 sm_100a"; }
-
-// ------------------------------------------------------------------------------------------------
-// context
-// ------------------------------------------------------------------------------------------------
-namespace {
-
-struct DeviceBuffer {
-    void *ptr = nullptr;
-    size_t bytes = 0;
-};
-
-// Scratch for one in-flight encode call. Zero-initialised where the kernels rely on it (tile histogram,
-// front-view winners) and left zero by them, so no per-call memset is needed on the tile path.
-struct Workspace {
-    DeviceBuffer keys, binned, tile_count, tile_off, fv_winner, cellkey;
-};
-
-constexpr int kSlots = 4;  // host pipeline depth: copy-in / encode / copy-out / host rebuild of consecutive sweeps overlap
-
-// Page-locked host staging that grows on demand.
-struct PinnedBuffer {
-    void *ptr = nullptr;
-    size_t bytes = 0;
-};
-
-// Where the compact variant of the tile kernel reports the touched cells of ONE sweep (device memory).
-struct CompactOut {
-    unsigned *entries = nullptr;  // cell indices [cap], then values [cap][planes]; slots follow the sweep's tile_off
-    unsigned cap = 0;             // >= points of the sweep
-};
-
-struct HostSlot {
-    cudaStream_t stream = nullptr;
-    Workspace ws;
-    DeviceBuffer points, top, front;
-    // compact read-back
-    DeviceBuffer compact;
-    PinnedBuffer stage, front_stage, toff_stage;
-    cudaEvent_t done = nullptr;
-    unsigned copied = 0;          // entries already copied to `stage` by the speculative D2H
-    unsigned cap = 0;             // entry capacity of the sweep in flight (indices [cap], then values [cap][planes])
-};
-
-} // namespace
-
-// Kernel classes, in the order mv3d_kernel_name() reports them.
-enum KernelId { K_CLASSIFY = 0, K_TILE_SCAN, K_BIN, K_TILE_BUILD, K_FRONT_FINALIZE, K_FILL_ZERO, K_ATOMIC_SCATTER,
-                K_ATOMIC_FINALIZE, K_FILL_TMA, K_WARP_PATCH, K_TILE_COMPACT, K_PYFRONT_LINK,
-                K_PYFRONT_REDUCE, K_COUNT };
-static const char *const kKernelNames[K_COUNT] = {"classify_kernel", "tile_scan_kernel", "bin_kernel",
-                                                  "tile_build_kernel", "front_finalize_kernel", "fill_zero_kernel",
-                                                  "atomic_scatter_kernel", "atomic_finalize_kernel",
-                                                  "fill_tma_kernel", "warp_patch_kernel", "tile_compact_kernel",
-                                                  "pyfront_link_kernel", "pyfront_reduce_kernel"};
-
-struct TimedLaunch {
-    cudaEvent_t start, stop;
-    int kernel;
-};
-
-struct mv3d_ctx {
-    bool profiling = false;
-    std::vector<TimedLaunch> timed;        // pending (not yet accumulated) event pairs
-    std::vector<cudaEvent_t> event_pool;   // recycled events
-    double kernel_ms[K_COUNT] = {0};
-    long long kernel_launches[K_COUNT] = {0};
-    int device = 0;
-    int sm_count = 0;
-    size_t smem_optin = 0;
-    float *lut = nullptr;     // density table of the C routines
-    float *lut_py = nullptr;  // density table of the Python encoder (all-double log)
-    Workspace ws;            // used by mv3d_encode_batch_dev (one call in flight per context)
-    HostSlot slots[kSlots];  // used by mv3d_encode_batch_host
-    std::unique_ptr<mv3d::HostPool> pool;  // host threads of the compact read-back (created on first use)
-    int host_threads = 0;
-    int host_compact = 1;    // MV3D_HOST_READBACK=dense switches the host entry points back to a dense D2H copy
-    unsigned long long h2d_bytes = 0, d2h_bytes = 0;  // moved by the host entry points since the last reset
-    unsigned compact_est = 0;  // entries the previous sweep produced: sizes the speculative copy of the next one
-    long long launches = 0;
-    size_t tile_bytes_target = 0;
-    size_t patch_tile_bytes = 0;          // tile size of the PATCH strategy (no tile store: smaller tiles, more CTAs)
-    int fill_chunk = 0;                   // sweeps per zero-fill launch of the PATCH strategy
-    int fill_ctas = 0;                    // fill CTAs per SM (one issuing thread each)
-    int fill_pending = 0;                 // bulk stores each fill CTA keeps in flight (> 16: unbounded)
-    int front_aside = 1;                  // TILE: finish the front view on the side stream (MV3D_FRONT_ASIDE=0: in line)
-    int atomic_overlap = 0;               // ATOMIC: TMA zero-fill on the side stream, chunked (MV3D_ATOMIC_OVERLAP=1)
-    size_t smem_per_sm = 0;
-    int patch_min_batch = 0;              // AUTO picks PATCH from this batch size on
-    int sub_batch = 0;                    // sweeps per pipeline stage of the tile strategy (0 = no pipelining)
-    cudaStream_t side_stream = nullptr;   // runs the point passes ahead of the tile kernel
-    cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_ready[kMaxBatchPerLaunch] = {nullptr};
-    std::mutex mu;
-};
-
-static int ensure(DeviceBuffer &b, size_t bytes, bool zero, cudaStream_t s)
-{
-    if (bytes <= b.bytes) return 0;
-    // Growing is rare (first call / larger batch); make sure nothing still uses the old allocation.
-    CUDA_TRY(cudaStreamSynchronize(s));
-    if (b.ptr) CUDA_TRY(cudaFree(b.ptr));
-    b.ptr = nullptr;
-    b.bytes = 0;
-    size_t want = bytes + bytes / 8;
-    want = (want + 255) & ~(size_t)255;
-    CUDA_TRY(cudaMalloc(&b.ptr, want));
-    b.bytes = want;
-    if (zero) {
-        CUDA_TRY(cudaMemsetAsync(b.ptr, 0, want, s));
-        CUDA_TRY(cudaStreamSynchronize(s));
-    }
-    return 0;
-}
-
-static int ensure_pinned(PinnedBuffer &b, size_t bytes)
-{
-    if (bytes <= b.bytes) return 0;
-    if (b.ptr) CUDA_TRY(cudaFreeHost(b.ptr));
-    b.ptr = nullptr;
-    b.bytes = 0;
-    size_t want = bytes + bytes / 4;
-    want = (want + 4095) & ~(size_t)4095;
-    CUDA_TRY(cudaHostAlloc(&b.ptr, want, cudaHostAllocDefault));
-    b.bytes = want;
-    return 0;
-}
-
-static void release(DeviceBuffer &b)
-{
-    if (b.ptr) cudaFree(b.ptr);
-    b.ptr = nullptr;
-    b.bytes = 0;
-}
-
-static void release(Workspace &w)
-{
-    release(w.keys); release(w.binned); release(w.tile_count); release(w.tile_off);
-    release(w.fv_winner); release(w.cellkey);
-}
 
 static void build_density_lut_py(float *v)
 {
@@ -289,6 +141,11 @@ extern "C" void mv3d_ctx_destroy(mv3d_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     release(ctx->ws);
+    {
+        AnchorState &a = ctx->anchors;
+        release(a.boxes); release(a.occupancy); release(a.flags); release(a.keep);
+        release(a.view); release(a.idx); release(a.count);
+    }
     for (auto &s : ctx->slots) {
         release(s.ws);
         release(s.points); release(s.top); release(s.front);
@@ -458,37 +315,6 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
     }
     *out = p;
     return 0;
-}
-
-// Optional per-kernel timing: CUDA events recorded on the launching stream around each kernel.
-static cudaEvent_t take_event(mv3d_ctx *ctx)
-{
-    cudaEvent_t e = nullptr;
-    if (!ctx->event_pool.empty()) {
-        e = ctx->event_pool.back();
-        ctx->event_pool.pop_back();
-    } else if (cudaEventCreate(&e) != cudaSuccess) {
-        e = nullptr;
-    }
-    return e;
-}
-
-template <typename F>
-static void timed_launch(mv3d_ctx *ctx, int kernel, cudaStream_t s, F &&launch)
-{
-    TimedLaunch t{nullptr, nullptr, kernel};
-    if (ctx->profiling) {
-        t.start = take_event(ctx);
-        t.stop = take_event(ctx);
-        if (t.start && t.stop) cudaEventRecord(t.start, s);
-    }
-    const int n = launch();
-    ctx->launches += n;
-    ctx->kernel_launches[kernel] += n;
-    if (ctx->profiling && t.start && t.stop) {
-        cudaEventRecord(t.stop, s);
-        ctx->timed.push_back(t);
-    }
 }
 
 // ------------------------------------------------------------------------------------------------
