@@ -48,6 +48,19 @@ int mv3d_remove_empty_anchor_dev(mv3d_ctx *ctx, const float *views_dev, int fram
                                  float limit, int mode, int *keep_dev, int *count_dev, float *totals_dev,
                                  void *stream);
 
+/* Encode and filter in one call: mv3d_encode_batch_dev (resp. mv3d_pytwin_encode_batch_dev) followed by
+ * mv3d_remove_empty_anchor_dev on the views it wrote -- same arguments, same results -- except that the kernel that
+ * builds the view also reports which cells it touched, so the filter does not read the 52 MB view again. Applies
+ * when limit == 0, mode is _AUTO and the tile strategy is in use; otherwise the two steps simply run back to back.
+ * top_dev is required. */
+int mv3d_encode_filter_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *offsets_host, int batch,
+                                 float *top_dev, float *front_dev, const mv3d_top_params *tp,
+                                 const mv3d_front_params *fp, int semantics, int strategy, float limit, int mode,
+                                 int *keep_dev, int *count_dev, void *stream);
+int mv3d_pytwin_encode_filter_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *offsets_host, int batch,
+                                        float *top_dev, float *front_dev, const mv3d_pytwin_params *pp, float limit,
+                                        int mode, int *keep_dev, int *count_dev, void *stream);
+
 /* The reference's call, with host buffers: uploads the view and the anchors, filters, returns after keep_host
  * (int32, room for n) and *count_host are complete. */
 int mv3d_remove_empty_anchor_host(mv3d_ctx *ctx, const float *view_host, int xn, int yn, int planes,

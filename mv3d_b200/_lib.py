@@ -83,6 +83,7 @@ EXPORTED_SYMBOLS = (
     "mv3d_debug_point_keys", "mv3d_debug_expand_compact", "mv3d_ctx_transfer_bytes",
     "mv3d_pytwin_encode_batch_dev", "mv3d_pytwin_encode_batch_host", "mv3d_debug_atan2f",
     "mv3d_ctx_set_anchors", "mv3d_remove_empty_anchor_dev", "mv3d_remove_empty_anchor_host",
+    "mv3d_encode_filter_batch_dev", "mv3d_pytwin_encode_filter_batch_dev",
 )
 ANCHORS_AUTO, ANCHORS_EXACT = 0, 1
 ANCHOR_MAX_LINES = 50
@@ -133,6 +134,10 @@ def load_library() -> ctypes.CDLL:
     lib.mv3d_ctx_set_anchors.argtypes = [vp, vp, ci]
     lib.mv3d_remove_empty_anchor_dev.argtypes = [vp, vp, ci, ci, ci, ci, cf, ci, vp, vp, vp, vp]
     lib.mv3d_remove_empty_anchor_host.argtypes = [vp, vp, ci, ci, ci, vp, ci, cf, ci, vp, ctypes.POINTER(ci)]
+    lib.mv3d_encode_filter_batch_dev.argtypes = [vp, vp, ctypes.POINTER(ci), ci, vp, vp, ctypes.POINTER(TopParamsC),
+                                                 ctypes.POINTER(FrontParamsC), ci, ci, cf, ci, vp, vp, vp]
+    lib.mv3d_pytwin_encode_filter_batch_dev.argtypes = [vp, vp, ctypes.POINTER(ci), ci, vp, vp,
+                                                        ctypes.POINTER(PyTwinParamsC), cf, ci, vp, vp, vp]
     _lib = lib
     return lib
 

@@ -87,6 +87,53 @@ class AnchorFilter:
             raise RuntimeError("mv3d_remove_empty_anchor_dev: " + _lib.last_error())
         return (keep, count, totals) if want_totals else (keep, count)
 
+    def encode_and_filter(self, points, offsets, params, front=None, limit: float = 0.0, top_out=None, front_out=None,
+                          want_front: bool = True, stream=None):
+        """Encode `len(offsets)-1` device-resident sweeps with the owning encoder and filter the views it writes, in
+        one library call: the kernel that builds a view also reports which cells it touched, so the filter does not
+        read the view again. `params`: `TopParams` (+ optional `front`: `FrontParams`) for a `ViewEncoder`, a
+        `PyTwinParams` for a `PyTwinEncoder`. Returns `(top, front, keep, count)` -- the same tensors `encode_device`
+        followed by `filter_device` would give."""
+        import torch
+        from .params import PyTwinParams
+        assert points.is_cuda and points.dtype == torch.float32 and points.is_contiguous()
+        offs = np.ascontiguousarray(offsets, dtype=np.int32)
+        batch = len(offs) - 1
+        offs_p = offs.ctypes.data_as(ctypes.POINTER(ctypes.c_int))
+        dev = points.device
+        keep = torch.empty((batch, self.n), dtype=torch.int32, device=dev)
+        count = torch.empty((batch,), dtype=torch.int32, device=dev)
+        if stream is None:
+            stream = torch.cuda.current_stream(dev).cuda_stream
+        if isinstance(params, PyTwinParams):
+            from .pytwin import _params_c
+            if top_out is None:
+                top_out = torch.empty((batch, *params.top_shape), dtype=torch.float32, device=dev)
+            if want_front and front_out is None:
+                front_out = torch.empty((batch, *params.front_shape), dtype=torch.float32, device=dev)
+            pc = _params_c(params)
+            rc = self._lib.mv3d_pytwin_encode_filter_batch_dev(
+                self._ctx, points.data_ptr(), offs_p, batch, top_out.data_ptr(),
+                front_out.data_ptr() if want_front else None, ctypes.byref(pc), float(limit), self.mode,
+                keep.data_ptr(), count.data_ptr(), ctypes.c_void_p(stream))
+            name = "mv3d_pytwin_encode_filter_batch_dev"
+        else:
+            from .encoder import _front_c, _top_c
+            if top_out is None:
+                top_out = torch.empty((batch, *params.shape), dtype=torch.float32, device=dev)
+            if front is not None and front_out is None:
+                front_out = torch.empty((batch, *front.shape), dtype=torch.float32, device=dev)
+            rc = self._lib.mv3d_encode_filter_batch_dev(
+                self._ctx, points.data_ptr(), offs_p, batch, top_out.data_ptr(),
+                front_out.data_ptr() if front is not None else None, ctypes.byref(_top_c(params)),
+                ctypes.byref(_front_c(front)) if front is not None else None, self._owner.semantics,
+                self._owner.strategy, float(limit), self.mode, keep.data_ptr(), count.data_ptr(),
+                ctypes.c_void_p(stream))
+            name = "mv3d_encode_filter_batch_dev"
+        if rc != 0:
+            raise RuntimeError(name + ": " + _lib.last_error())
+        return top_out, front_out, keep, count
+
     def filter_host(self, view: np.ndarray, anchors, limit: float = 0.0) -> np.ndarray:
         """The reference's call: numpy in, kept indices (int64, ascending) out."""
         view = np.ascontiguousarray(view, dtype=np.float32)

@@ -39,17 +39,13 @@ extern "C" int mv3d_ctx_set_anchors(mv3d_ctx *ctx, const int *anchors_host, int 
     return 0;
 }
 
-// Enqueue the filter for `frames` views on `s`. The context lock is held by the caller.
-static int filter_locked(mv3d_ctx *ctx, const float *views_dev, int frames, int xn, int yn, int planes, float limit,
-                         int mode, int *keep_dev, int *count_dev, float *totals_dev, cudaStream_t s)
+// Size and clear the scratch of one filter call over `frames` views (context lock held). With want_sink the
+// occupancy map is cleared too and *sink tells the tile kernel where to report into it.
+int anchor_plan_locked(mv3d_ctx *ctx, int frames, int xn, int yn, int planes, float limit, int mode, bool want_totals,
+                       cudaStream_t s, AnchorPlan *plan, OccupancySink *sink)
 {
     AnchorState &st = ctx->anchors;
-    if (frames == 0) return 0;
-    if (st.n == 0) {
-        CUDA_TRY(cudaMemsetAsync(count_dev, 0, (size_t)frames * sizeof(int), s));
-        return 0;
-    }
-    AnchorGeometry g;
+    AnchorGeometry &g = plan->g;
     g.xn = xn;
     g.yn = yn;
     g.planes = planes;
@@ -60,32 +56,74 @@ static int filter_locked(mv3d_ctx *ctx, const float *views_dev, int frames, int 
     g.max_lines = MV3D_ANCHOR_MAX_LINES;
     // The occupancy map decides only "total > 0"; any other threshold, a NaN threshold or a request for the totals
     // themselves takes the sums for every frame.
-    const bool exact_all = mode == MV3D_ANCHORS_EXACT || totals_dev != nullptr || !(limit == 0.0f);
+    plan->exact_all = mode == MV3D_ANCHORS_EXACT || want_totals || !(limit == 0.0f);
+    plan->frames = frames;
+    if (frames == 0 || st.n == 0) return 0;
     // flags [frames] and chunk counts [frames][chunks] share one buffer so that one memset clears both
     const size_t flag_words = (size_t)frames, count_words = (size_t)frames * g.chunks;
     if (ensure(st.flags, (flag_words + count_words) * sizeof(unsigned), false, s)) return -1;
     if (ensure(st.keep, (size_t)frames * st.n, false, s)) return -1;
-    unsigned *flags = static_cast<unsigned *>(st.flags.ptr);
-    unsigned *chunk_count = flags + flag_words;
-    unsigned char *keep = static_cast<unsigned char *>(st.keep.ptr);
-    const int4 *boxes = static_cast<const int4 *>(st.boxes.ptr);
-    CUDA_TRY(cudaMemsetAsync(flags, 0, (flag_words + count_words) * sizeof(unsigned), s));
-    if (!exact_all) {
+    plan->flags = static_cast<unsigned *>(st.flags.ptr);
+    plan->chunk_count = plan->flags + flag_words;
+    plan->keep = static_cast<unsigned char *>(st.keep.ptr);
+    CUDA_TRY(cudaMemsetAsync(plan->flags, 0, (flag_words + count_words) * sizeof(unsigned), s));
+    plan->occupancy = nullptr;
+    if (!plan->exact_all) {
         if (ensure(st.occupancy, (size_t)frames * g.words * sizeof(unsigned), false, s)) return -1;
-        unsigned *occ = static_cast<unsigned *>(st.occupancy.ptr);
-        timed_launch(ctx, K_ANCHOR_OCCUPANCY, s,
-                     [&] { return launch_anchor_occupancy(views_dev, g, frames, occ, flags, ctx->sm_count, s); });
-        timed_launch(ctx, K_ANCHOR_TEST, s,
-                     [&] { return launch_anchor_test(boxes, g, frames, occ, flags, keep, chunk_count, s); });
+        plan->occupancy = static_cast<unsigned *>(st.occupancy.ptr);
+        if (sink) {
+            CUDA_TRY(cudaMemsetAsync(plan->occupancy, 0, (size_t)frames * g.words * sizeof(unsigned), s));
+            sink->words = plan->occupancy;
+            sink->flags = plan->flags;
+            sink->words_per_frame = g.words;
+        }
+    }
+    return 0;
+}
+
+// Enqueue the filter on `s`. have_occupancy: the tile kernel already filled the occupancy map and the flags while
+// it built these views, so the view is not read again.
+int anchor_run_locked(mv3d_ctx *ctx, const AnchorPlan &plan, const float *views_dev, float limit, int *keep_dev,
+                      int *count_dev, float *totals_dev, cudaStream_t s, bool have_occupancy)
+{
+    AnchorState &st = ctx->anchors;
+    const AnchorGeometry &g = plan.g;
+    const int frames = plan.frames;
+    if (frames == 0) return 0;
+    if (st.n == 0) {
+        CUDA_TRY(cudaMemsetAsync(count_dev, 0, (size_t)frames * sizeof(int), s));
+        return 0;
+    }
+    const int4 *boxes = static_cast<const int4 *>(st.boxes.ptr);
+    if (!plan.exact_all) {
+        if (!have_occupancy)
+            timed_launch(ctx, K_ANCHOR_OCCUPANCY, s, [&] {
+                return launch_anchor_occupancy(views_dev, g, frames, plan.occupancy, plan.flags, ctx->sm_count, s);
+            });
+        timed_launch(ctx, K_ANCHOR_TEST, s, [&] {
+            return launch_anchor_test(boxes, g, frames, plan.occupancy, plan.flags, plan.keep, plan.chunk_count, s);
+        });
     }
     // In AUTO mode this launch exits at once for every frame the occupancy map could decide (the usual case).
     timed_launch(ctx, K_ANCHOR_SUM, s, [&] {
-        return launch_anchor_sum(views_dev, boxes, g, frames, limit, flags, exact_all, keep, chunk_count, totals_dev, s);
+        return launch_anchor_sum(views_dev, boxes, g, frames, limit, plan.flags, plan.exact_all, plan.keep,
+                                 plan.chunk_count, totals_dev, ctx->sm_count, s);
     });
-    timed_launch(ctx, K_ANCHOR_COMPACT, s,
-                 [&] { return launch_anchor_compact(g, frames, keep, chunk_count, keep_dev, count_dev, s); });
+    timed_launch(ctx, K_ANCHOR_COMPACT, s, [&] {
+        return launch_anchor_compact(g, frames, plan.keep, plan.chunk_count, keep_dev, count_dev, s);
+    });
     CUDA_TRY(cudaGetLastError());
     return 0;
+}
+
+int anchor_check_view(const char *who, int frames, int xn, int yn, int planes) { return check_view(who, frames, xn, yn, planes); }
+
+static int filter_locked(mv3d_ctx *ctx, const float *views_dev, int frames, int xn, int yn, int planes, float limit,
+                         int mode, int *keep_dev, int *count_dev, float *totals_dev, cudaStream_t s)
+{
+    AnchorPlan plan;
+    if (anchor_plan_locked(ctx, frames, xn, yn, planes, limit, mode, totals_dev != nullptr, s, &plan, nullptr)) return -1;
+    return anchor_run_locked(ctx, plan, views_dev, limit, keep_dev, count_dev, totals_dev, s, false);
 }
 
 extern "C" int mv3d_remove_empty_anchor_dev(mv3d_ctx *ctx, const float *views_dev, int frames, int xn, int yn,

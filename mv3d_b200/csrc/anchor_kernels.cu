@@ -186,8 +186,10 @@ __global__ void __launch_bounds__(kAnchorSumWarps * 32) anchor_sum_kernel(const 
     const unsigned frame = blockIdx.y;
     if (!always && flags[frame] == 0u) return;  // decided by the occupancy map
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int a = blockIdx.x * kAnchorSumWarps + warp;
     float *sums = channel_sums + (size_t)warp * g.planes;
+    const int groups = (g.n + kAnchorSumWarps - 1) / kAnchorSumWarps;
+    for (int group = blockIdx.x; group < groups; group += gridDim.x) {
+    const int a = group * kAnchorSumWarps + warp;
     int hit = 0;
     if (a < g.n) {
         const Box b = clamp_box(boxes[a], g.xn, g.yn, g.max_lines);
@@ -217,8 +219,10 @@ __global__ void __launch_bounds__(kAnchorSumWarps * 32) anchor_sum_kernel(const 
         int sum = 0;
 #pragma unroll
         for (int w = 0; w < kAnchorSumWarps; w++) sum += kept[w];
-        // the anchors of one block share a chunk: kAnchorChunk is a multiple of kAnchorSumWarps
-        if (sum) atomicAdd(chunk_count + (size_t)frame * g.chunks + (blockIdx.x * kAnchorSumWarps) / kAnchorChunk, sum);
+        // the anchors of one group share a chunk: kAnchorChunk is a multiple of kAnchorSumWarps
+        if (sum) atomicAdd(chunk_count + (size_t)frame * g.chunks + (group * kAnchorSumWarps) / kAnchorChunk, sum);
+    }
+    __syncthreads();  // kept[] is reused by the next group
     }
 }
 
@@ -296,9 +300,13 @@ int launch_anchor_test(const int4 *boxes, const AnchorGeometry &g, int frames, c
 
 int launch_anchor_sum(const float *views, const int4 *boxes, const AnchorGeometry &g, int frames, float limit,
                       const unsigned *flags, bool always, unsigned char *keep, unsigned *chunk_count, float *totals,
-                      cudaStream_t s)
+                      int sm_count, cudaStream_t s)
 {
-    const unsigned blocks = (g.n + kAnchorSumWarps - 1) / kAnchorSumWarps;
+    // Blocks walk the anchors 8 at a time. A grid of about four waves over all frames keeps the launch that finds
+    // nothing to do (every frame decided by the occupancy map) down to a few microseconds.
+    unsigned blocks = (g.n + kAnchorSumWarps - 1) / kAnchorSumWarps;
+    const unsigned cap = std::max(1u, (unsigned)sm_count * 32u / (unsigned)frames);
+    if (blocks > cap) blocks = cap;
     const size_t smem = (size_t)kAnchorSumWarps * g.planes * sizeof(float);
     anchor_sum_kernel<<<dim3(blocks, frames), kAnchorSumWarps * 32, smem, s>>>(views, boxes, g, limit, flags,
                                                                                always ? 1 : 0, keep, chunk_count, totals);

@@ -26,7 +26,7 @@ int launch_anchor_test(const int4 *boxes, const AnchorGeometry &g, int frames, c
                        const unsigned *flags, unsigned char *keep, unsigned *chunk_count, cudaStream_t s);
 int launch_anchor_sum(const float *views, const int4 *boxes, const AnchorGeometry &g, int frames, float limit,
                       const unsigned *flags, bool always, unsigned char *keep, unsigned *chunk_count, float *totals,
-                      cudaStream_t s);
+                      int sm_count, cudaStream_t s);
 int launch_anchor_compact(const AnchorGeometry &g, int frames, const unsigned char *keep, const unsigned *chunk_count,
                           int *keep_idx, int *count, cudaStream_t s);
 

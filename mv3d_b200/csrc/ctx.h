@@ -1,6 +1,7 @@
 // ctx.h -- the context behind the C ABI (internal; shared by mv3d_abi.cu and anchor_abi.cu).
 #pragma once
 #include "../../include/mv3d_encode.h"
+#include "anchor_kernels.h"
 #include "encode_kernels.h"
 #include "host_expand.h"
 #include "view_math.cuh"
@@ -202,3 +203,17 @@ inline void timed_launch(mv3d_ctx *ctx, int kernel, cudaStream_t s, F &&launch)
         ctx->timed.push_back(t);
     }
 }
+
+// Empty-anchor filter internals shared with the fused encode+filter entry points (anchor_abi.cu).
+struct AnchorPlan {
+    AnchorGeometry g;
+    int frames = 0;
+    bool exact_all = false;
+    unsigned *flags = nullptr, *chunk_count = nullptr, *occupancy = nullptr;
+    unsigned char *keep = nullptr;
+};
+int anchor_check_view(const char *who, int frames, int xn, int yn, int planes);
+int anchor_plan_locked(mv3d_ctx *ctx, int frames, int xn, int yn, int planes, float limit, int mode, bool want_totals,
+                       cudaStream_t s, AnchorPlan *plan, OccupancySink *sink);
+int anchor_run_locked(mv3d_ctx *ctx, const AnchorPlan &plan, const float *views_dev, float limit, int *keep_dev,
+                      int *count_dev, float *totals_dev, cudaStream_t s, bool have_occupancy);

@@ -253,11 +253,16 @@ bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
 // (tile_off): the first nd hold its touched cells (any order), the rest are marked kNoCell. The list is therefore
 // ordered by tile with no atomics and no scan, and tile_off tells the reader where each tile's slots are. This is
 // what the host-buffer path reads back over PCIe instead of the 95 %-zero dense tensor.
-template <bool kCompact>
+// kOccupancy (dense output only): also report, for the empty-anchor filter that consumes the view next
+// (anchor_kernels.cu), one bit per cell "touched" -- touched cells carry a density > 0, untouched cells are all
+// zero -- into a pre-zeroed per-frame bit map, and raise the frame's flag when an intensity is negative, -0 or NaN
+// (the only values of a view that can be; then the filter must take exact sums). The bits of a tile are gathered
+// in shared memory; the first and last word of a tile may be shared with its neighbours and go out as atomics.
+template <bool kCompact, bool kOccupancy = false>
 __device__ __forceinline__ void
 tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
           ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
-          unsigned *__restrict__ compact, unsigned compact_cap)
+          unsigned *__restrict__ compact, unsigned compact_cap, OccupancySink sink = OccupancySink())
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int T = p.tile_cells;
@@ -267,12 +272,15 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
     const size_t img_bytes = ((size_t)T * planes * 4 + 15) & ~(size_t)15;
     unsigned long long *key = reinterpret_cast<unsigned long long *>(smem_raw + img_bytes);
     unsigned *dirty = reinterpret_cast<unsigned *>(key + T);
+    unsigned *occ_tile = dirty + T;  // [T/32 + 2], all-zero between tiles (kOccupancy)
     __shared__ unsigned ndirty;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int kWarps = kTileThreads / 32;
 
     for (int w = tid; w < T * planes; w += kTileThreads) img[w] = 0u;
     for (int w = tid; w < T; w += kTileThreads) key[w] = 0ull;
+    if (kOccupancy)
+        for (int w = tid; w < T / 32 + 2; w += kTileThreads) occ_tile[w] = 0u;
     if (tid == 0) ndirty = 0;
     fence_proxy_async_smem();
     __syncthreads();
@@ -355,11 +363,18 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 const uint4 q = (r == tid) ? q0 : __ldg(rec0 + r);
                 const unsigned local = q.x & 0xFFFFu;
                 if ((int)q.y > 0 &&
-                    key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z)))
+                    key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z))) {
                     img[local * planes + zn] = q.w;
+                    if (kOccupancy && ((q.w >> 31) != 0u || (q.w & 0x7fffffffu) > 0x7f800000u))
+                        atomicOr(sink.flags + f, 1u);
+                }
             }
             for (int d = warp; d < nd; d += kWarps) {  // one warp per touched cell, lanes over planes
                 unsigned *cellw = img + dirty[d] * planes;
+                if (kOccupancy && lane == 0) {
+                    const unsigned g = (unsigned)cell0 + dirty[d];
+                    atomicOr(occ_tile + ((g >> 5) - ((unsigned)cell0 >> 5)), 1u << (g & 31u));
+                }
                 for (int k = lane; k < planes; k += 32) {
                     if (k < zn) {
                         const unsigned raw = cellw[k];
@@ -393,6 +408,18 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
             } else {
                 for (int w = tid; w < ncell * planes; w += kTileThreads) dst[w] = __uint_as_float(img[w]);
             }
+            if (kOccupancy) {
+                const unsigned w_first = (unsigned)cell0 >> 5, w_last = ((unsigned)cell0 + (unsigned)ncell - 1u) >> 5;
+                unsigned *out = sink.words + (size_t)f * sink.words_per_frame + w_first;
+                for (unsigned w = tid; w <= w_last - w_first; w += kTileThreads) {
+                    const unsigned bits = occ_tile[w];
+                    if (bits) {
+                        if (w == 0 || w == w_last - w_first) atomicOr(out + w, bits);
+                        else out[w] = bits;
+                        occ_tile[w] = 0u;
+                    }
+                }
+            }
             __syncthreads();
             for (int d = warp; d < nd; d += kWarps) {
                 const unsigned local = dirty[d];
@@ -414,6 +441,15 @@ tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
                   ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles)
 {
     tile_body<false>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u);
+}
+
+// Same, and the occupancy bits / flag of every frame for the empty-anchor filter (see tile_body).
+__global__ void __launch_bounds__(kTileThreads)
+tile_build_occupancy_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
+                            ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
+                            OccupancySink sink)
+{
+    tile_body<false, true>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u, sink);
 }
 
 // Same reduction, compact output (see tile_body).
@@ -547,8 +583,9 @@ warp_patch_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
                 const uint4 q = (r == lane) ? q0 : __ldg(rec + r);
                 const unsigned local = q.x & 0xFFFFu;
                 if ((int)q.y > 0 &&
-                    key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z)))
+                    key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z))) {
                     img[local * planes + zn] = q.w;
+                }
             }
             // heights and density of the touched cells (lanes over planes; the intensity slot is not touched here)
             for (int d = 0; d < nd; d++) {
@@ -799,7 +836,7 @@ static inline int point_blocks(int max_points)
 size_t tile_smem_bytes(const ViewParams &p)
 {
     const size_t img = ((size_t)p.tile_cells * p.planes * 4 + 15) & ~(size_t)15;
-    return img + (size_t)p.tile_cells * 8 + (size_t)p.tile_cells * 4;
+    return img + (size_t)p.tile_cells * 8 + (size_t)p.tile_cells * 4 + ((size_t)p.tile_cells / 32 + 2) * 4;
 }
 
 cudaError_t tile_build_configure(const ViewParams &p, int *blocks_per_sm)
@@ -836,11 +873,18 @@ int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p,
 }
 
 int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
-                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s)
+                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s, const OccupancySink *sink)
 {
     const int total = batch * p.tiles_per_frame;
     const int grid = grid_blocks < total ? grid_blocks : total;
-    tile_build_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
+    if (sink && sink->words) {
+        cudaFuncSetAttribute(tile_build_occupancy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int)tile_smem_bytes(p));
+        tile_build_occupancy_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top,
+                                                                                   total, *sink);
+    } else {
+        tile_build_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
+    }
     return 1;
 }
 

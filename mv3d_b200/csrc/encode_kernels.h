@@ -10,6 +10,14 @@ struct ViewParams;
 struct FrameOffsets;
 struct PyFrontParams;
 
+// Where the tile kernel reports cell occupancy for the empty-anchor filter (anchor_kernels.cu): one bit per cell in
+// a PRE-ZEROED map of words_per_frame words per frame, and a per-frame flag "an intensity is negative, -0 or NaN".
+struct OccupancySink {
+    unsigned *words = nullptr;
+    unsigned *flags = nullptr;
+    unsigned words_per_frame = 0;
+};
+
 // Each launcher enqueues on `s` and returns the number of kernels it launched.
 size_t tile_smem_bytes(const ViewParams &p);
 cudaError_t tile_build_configure(const ViewParams &p, int *blocks_per_sm);
@@ -20,7 +28,8 @@ int launch_tile_scan(unsigned *tile_count, unsigned *tile_off, int tiles_per_fra
 int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
                const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s);
 int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
-                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
+                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s,
+                      const OccupancySink *sink = nullptr);
 int launch_tile_compact(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                         const float *lut, int batch, int grid_blocks, unsigned *compact, unsigned compact_cap,
                         cudaStream_t s);

@@ -5,6 +5,7 @@
 // There is no CPU implementation in this library: every path ends in the sm_100a kernels of
 // encode_kernels.cu, and every failure is reported through mv3d_last_error().
 #include "ctx.h"
+#include "../../include/mv3d_anchors.h"
 
 #include <cmath>
 #include <cstdarg>
@@ -322,7 +323,7 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
 // ------------------------------------------------------------------------------------------------
 static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
                          float *top_dev, float *front_dev, const ViewParams &p, int strategy, cudaStream_t s,
-                         const CompactOut *compact = nullptr)
+                         const CompactOut *compact = nullptr, const OccupancySink *sink = nullptr)
 {
     FrameOffsets offs;
     memset(&offs, 0, sizeof(offs));
@@ -447,8 +448,14 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
                 continue;
             }
             float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
+            OccupancySink sink_j;
+            if (sink && strategy == MV3D_STRATEGY_TILE) {
+                sink_j = *sink;
+                sink_j.words += (size_t)j0 * sink->words_per_frame;
+                sink_j.flags += j0;
+            }
             timed_launch(ctx, K_TILE_BUILD, s, [&] {
-                return launch_tile_build(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
+                return launch_tile_build(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s, &sink_j);
             });
         }
         if (front_aside) {
@@ -541,7 +548,7 @@ static int check_offsets(const int *offsets, int batch)
 
 static int encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
                              float *top_dev, float *front_dev, const ViewParams &p, int strategy, cudaStream_t s,
-                             const CompactOut *compact = nullptr)
+                             const CompactOut *compact = nullptr, const OccupancySink *sink = nullptr)
 {
     if (offsets[batch] > offsets[0] && (reinterpret_cast<uintptr_t>(points_dev) & 15u))
         return fail("points_dev must be 16-byte aligned");
@@ -549,7 +556,15 @@ static int encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *points_d
         const int nb = (batch - c0 < kMaxBatchPerLaunch) ? batch - c0 : kMaxBatchPerLaunch;
         float *top_c = top_dev ? top_dev + (size_t)c0 * (size_t)p.top_frame_floats : nullptr;
         float *front_c = front_dev ? front_dev + (size_t)c0 * (size_t)p.front_frame_floats : nullptr;
-        if (enqueue_chunk(ctx, ws, points_dev, offsets + c0, nb, top_c, front_c, p, strategy, s, compact)) return -1;
+        OccupancySink sink_c;
+        if (sink) {
+            sink_c = *sink;
+            sink_c.words += (size_t)c0 * sink->words_per_frame;
+            sink_c.flags += c0;
+        }
+        if (enqueue_chunk(ctx, ws, points_dev, offsets + c0, nb, top_c, front_c, p, strategy, s, compact,
+                          sink ? &sink_c : nullptr))
+            return -1;
     }
     return 0;
 }
@@ -813,7 +828,8 @@ static int make_py_params(const mv3d_ctx *ctx, const mv3d_pytwin_params *pp, boo
 }
 
 static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
-                            float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp, cudaStream_t s)
+                            float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp, cudaStream_t s,
+                            const OccupancySink *sink = nullptr)
 {
     FrameOffsets offs;
     memset(&offs, 0, sizeof(offs));
@@ -844,7 +860,7 @@ static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_de
         timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
         timed_launch(ctx, K_BIN, s, [&] { return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s); });
         timed_launch(ctx, K_TILE_BUILD, s, [&] {
-            return launch_tile_build(binned, toff, offs, p, ctx->lut_py, top_dev, batch, blocks_per_sm * ctx->sm_count, s);
+            return launch_tile_build(binned, toff, offs, p, ctx->lut_py, top_dev, batch, blocks_per_sm * ctx->sm_count, s, sink);
         });
     }
     if (front_dev && fp.pixels > 0) {
@@ -860,7 +876,8 @@ static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_de
 }
 
 static int py_encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
-                                float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp, cudaStream_t s)
+                                float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp, cudaStream_t s,
+                                const OccupancySink *sink = nullptr)
 {
     if (offsets[batch] > offsets[0] && (reinterpret_cast<uintptr_t>(points_dev) & 15u))
         return fail("points_dev must be 16-byte aligned");
@@ -868,7 +885,14 @@ static int py_encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *point
         const int nb = std::min(batch - c0, kMaxBatchPerLaunch);
         float *top_c = top_dev ? top_dev + (size_t)c0 * (size_t)p.top_frame_floats : nullptr;
         float *front_c = front_dev ? front_dev + (size_t)c0 * (size_t)fp.pixels * 3 : nullptr;
-        if (enqueue_py_chunk(ctx, ws, points_dev, offsets + c0, nb, top_c, front_c, p, fp, s)) return -1;
+        OccupancySink sink_c;
+        if (sink) {
+            sink_c = *sink;
+            sink_c.words += (size_t)c0 * sink->words_per_frame;
+            sink_c.flags += c0;
+        }
+        if (enqueue_py_chunk(ctx, ws, points_dev, offsets + c0, nb, top_c, front_c, p, fp, s, sink ? &sink_c : nullptr))
+            return -1;
     }
     return 0;
 }
@@ -886,6 +910,79 @@ extern "C" int mv3d_pytwin_encode_batch_dev(mv3d_ctx *ctx, const float *points_d
     CUDA_TRY(cudaSetDevice(ctx->device));
     return py_encode_dev_locked(ctx, ctx->ws, points_dev, offsets_host, batch, top_dev, front_dev, p, fp,
                                 static_cast<cudaStream_t>(stream));
+}
+
+// ------------------------------------------------------------------------------------------------
+// encode + empty-anchor filter in one call (include/mv3d_anchors.h): the tile kernel reports cell occupancy while it
+// builds the view, so the filter never reads the view. Falls back to encode, then the stand-alone filter, whenever
+// the occupancy map cannot decide (limit != 0, exact mode) or the strategy in use is not the tile strategy.
+// ------------------------------------------------------------------------------------------------
+static int check_filter_args(const char *who, mv3d_ctx *ctx, int batch, float *top_dev, int mode, int *keep_dev,
+                             int *count_dev)
+{
+    if (!top_dev) return fail("%s: top_dev is NULL (the filter works on the bird's-eye view)", who);
+    if (mode != MV3D_ANCHORS_AUTO && mode != MV3D_ANCHORS_EXACT) return fail("%s: unknown mode %d", who, mode);
+    if (batch > 0 && (!count_dev || (ctx->anchors.n > 0 && !keep_dev))) return fail("%s: NULL output buffer", who);
+    if (batch > 65535) return fail("%s: at most 65535 frames per call (got %d)", who, batch);
+    return 0;
+}
+
+extern "C" int mv3d_encode_filter_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *offsets_host, int batch,
+                                            float *top_dev, float *front_dev, const mv3d_top_params *tp,
+                                            const mv3d_front_params *fp, int semantics, int strategy, float limit,
+                                            int mode, int *keep_dev, int *count_dev, void *stream)
+{
+    const char *who = "mv3d_encode_filter_batch_dev";
+    if (!ctx) return fail("%s: ctx is NULL", who);
+    if (check_offsets(offsets_host, batch)) return -1;
+    if (check_filter_args(who, ctx, batch, top_dev, mode, keep_dev, count_dev)) return -1;
+    ViewParams p;
+    const int strat = resolve_for_batch(ctx, tp, strategy, batch);
+    if (make_params(ctx, tp, fp, true, front_dev != nullptr, semantics, strat, &p)) return -1;
+    if (anchor_check_view(who, batch, p.xn, p.yn, p.planes)) return -1;
+    if (batch == 0) return 0;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    AnchorPlan plan;
+    OccupancySink sink;
+    const bool fused = strat == MV3D_STRATEGY_TILE && ctx->anchors.n > 0;
+    if (anchor_plan_locked(ctx, batch, p.xn, p.yn, p.planes, limit, mode, false, s, &plan, fused ? &sink : nullptr))
+        return -1;
+    const bool have = fused && sink.words != nullptr;
+    if (encode_dev_locked(ctx, ctx->ws, points_dev, offsets_host, batch, top_dev, front_dev, p, strat, s, nullptr,
+                          have ? &sink : nullptr))
+        return -1;
+    return anchor_run_locked(ctx, plan, top_dev, limit, keep_dev, count_dev, nullptr, s, have);
+}
+
+extern "C" int mv3d_pytwin_encode_filter_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *offsets_host,
+                                                   int batch, float *top_dev, float *front_dev,
+                                                   const mv3d_pytwin_params *pp, float limit, int mode, int *keep_dev,
+                                                   int *count_dev, void *stream)
+{
+    const char *who = "mv3d_pytwin_encode_filter_batch_dev";
+    if (!ctx) return fail("%s: ctx is NULL", who);
+    if (check_offsets(offsets_host, batch)) return -1;
+    if (check_filter_args(who, ctx, batch, top_dev, mode, keep_dev, count_dev)) return -1;
+    ViewParams p;
+    PyFrontParams fp;
+    if (make_py_params(ctx, pp, true, &p, &fp)) return -1;
+    if (anchor_check_view(who, batch, p.xn, p.yn, p.planes)) return -1;
+    if (batch == 0) return 0;
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    AnchorPlan plan;
+    OccupancySink sink;
+    const bool fused = ctx->anchors.n > 0;  // the Python-twin mode always runs the tile strategy
+    if (anchor_plan_locked(ctx, batch, p.xn, p.yn, p.planes, limit, mode, false, s, &plan, fused ? &sink : nullptr))
+        return -1;
+    const bool have = fused && sink.words != nullptr;
+    if (py_encode_dev_locked(ctx, ctx->ws, points_dev, offsets_host, batch, top_dev, front_dev, p, fp, s,
+                             have ? &sink : nullptr))
+        return -1;
+    return anchor_run_locked(ctx, plan, top_dev, limit, keep_dev, count_dev, nullptr, s, have);
 }
 
 // Host buffers: sweep by sweep over the slot streams (H2D, encode, dense D2H).

@@ -183,3 +183,63 @@ def test_filters_the_encoders_output_in_place(filt, oracle_anchors, oracle_mod):
         assert 0 < len(want) < 30000
         assert np.array_equal(keep[f, : int(count[f])].cpu().numpy(), want), f
     enc.close()
+
+
+@pytest.mark.parametrize("strategy", ["tile", "atomic"])
+@pytest.mark.parametrize("with_front", [False, True])
+def test_fused_encode_and_filter_equals_two_calls(oracle_anchors, oracle_mod, strategy, with_front):
+    """One call (the tile kernel reports occupancy while it builds the view) == encode, then filter == the oracle.
+    70 sweeps: more than one launch chunk, so the per-chunk offsets into the occupancy map are exercised."""
+    import torch
+    from mv3d_b200.anchors import AnchorFilter, make_anchors
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.params import KITTI_FRONT_64x512 as front_p, REFERENCE_KITTI_TOP as top_p
+    from mv3d_b200.sweeps import pack_sweeps, uniform_in_box
+    sweeps = [uniform_in_box(3000 + 900 * i, top_p, seed=100 + i, margin=2.0) for i in range(70)]
+    sweeps[5] = sweeps[5][:0]                                  # an empty sweep keeps nothing
+    sweeps[9] = sweeps[9].copy()
+    sweeps[9][:, 3] -= np.float32(0.5)                         # negative intensities: this frame needs the sums
+    pts, offs = pack_sweeps(sweeps)
+    boxes = make_anchors(top_p.shape[:2], stride=8)
+    enc = ViewEncoder(0, semantics="topfront", strategy=strategy)
+    filt = AnchorFilter(enc, anchors=boxes)
+    d = torch.from_numpy(pts).cuda()
+    fp = front_p if with_front else None
+    top, front, keep, count = filt.encode_and_filter(d, offs, top_p, front=fp)
+    top2, front2 = enc.encode_device(d, offs, top_p, fp)
+    keep2, count2 = filt.filter_device(top2)
+    torch.cuda.synchronize()
+    assert torch.equal(top, top2) and torch.equal(count, count2)
+    if with_front:
+        assert torch.equal(front, front2)
+    count = count.cpu().numpy()
+    assert count[5] == 0
+    for f in range(70):
+        assert torch.equal(keep[f, : count[f]], keep2[f, : count[f]]), f
+    for f in (0, 9, 69):
+        et, _ = oracle_mod.top_and_front_maps(sweeps[f], top_p, front_p)
+        want = oracle_anchors.remove_empty_anchor(et, boxes, 0.0)
+        assert np.array_equal(keep[f, : count[f]].cpu().numpy(), want), f
+    enc.close()
+
+
+def test_fused_python_twin(oracle_anchors):
+    import torch
+    from oracle import pytwin
+    from mv3d_b200.anchors import AnchorFilter, make_anchors
+    from mv3d_b200.params import PYTWIN_KITTI as P
+    from mv3d_b200.pytwin import PyTwinEncoder
+    from mv3d_b200.sweeps import hdl64_sweep, pack_sweeps
+    sweeps = [hdl64_sweep(f)[::7] for f in range(3)]
+    pts, offs = pack_sweeps(sweeps)
+    boxes = make_anchors(P.top_shape[:2], stride=8)
+    enc = PyTwinEncoder(0)
+    filt = AnchorFilter(enc, anchors=boxes)
+    top, front, keep, count = filt.encode_and_filter(torch.from_numpy(pts).cuda(), offs, P)
+    torch.cuda.synchronize()
+    for f, s in enumerate(sweeps):
+        et = pytwin.lidar_to_top(s, P)
+        assert np.array_equal(top[f].cpu().numpy(), et)
+        want = oracle_anchors.remove_empty_anchor(et, boxes, 0.0)
+        assert np.array_equal(keep[f, : int(count[f])].cpu().numpy(), want), f
+    enc.close()
