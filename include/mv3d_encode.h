@@ -52,11 +52,19 @@ void createTopAndFrontMaps(const void *raw_data, int num, const void *top_data, 
 /* Error text of the last failing call on this thread ("" if none). Never NULL. */
 const char *mv3d_last_error(void);
 
-/* The 9 floats + 3 ints of createTopMaps, in the reference's argument order. */
+/* What the reference's Python wrapper does around the C call (src/data.py:265-291 `clidar_to_top`), fused into it:
+ *   _FLIP_XY            write cell (X-1, Y-1) at [xn-X][yn-Y]: the result of `np.flipud(np.fliplr(top_flip))` (:290)
+ *   _FILTER_CENTER_CAR  drop the points with |x| <= 4.7/2 and |y| <= 2.1/2 first: `filter_center_car` (:224-227),
+ *                       applied for the didi data sets (:266-267); the kept points keep their order */
+enum { MV3D_TOP_FLIP_XY = 1, MV3D_TOP_FILTER_CENTER_CAR = 2 };
+
+/* The 9 floats + 3 ints of createTopMaps, in the reference's argument order, then MV3D_TOP_* flags (0 = exactly the
+ * C routine). */
 typedef struct mv3d_top_params {
     float x_min, x_max, y_min, y_max, z_min, z_max;
     float x_div, y_div, z_div;
     int xn, yn, zn;
+    int flags;
 } mv3d_top_params;
 
 /* The 9 trailing floats of createTopAndFrontMaps, in the reference's argument order. */

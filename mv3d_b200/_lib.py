@@ -53,7 +53,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
 class TopParamsC(ctypes.Structure):
     _fields_ = [(n, ctypes.c_float) for n in
                 ("x_min", "x_max", "y_min", "y_max", "z_min", "z_max", "x_div", "y_div", "z_div")] + \
-               [(n, ctypes.c_int) for n in ("xn", "yn", "zn")]
+               [(n, ctypes.c_int) for n in ("xn", "yn", "zn", "flags")]
 
 
 class FrontParamsC(ctypes.Structure):

@@ -289,6 +289,9 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
     p.x_div = tp->x_div; p.y_div = tp->y_div; p.z_div = tp->z_div;
     p.xn = tp->xn; p.yn = tp->yn; p.zn = tp->zn; p.planes = tp->zn + 2;
     p.quant_floor = (semantics == MV3D_SEM_TOPFRONT) ? 1 : 0;
+    if (tp->flags & ~(MV3D_TOP_FLIP_XY | MV3D_TOP_FILTER_CENTER_CAR)) return fail("unknown top flags 0x%x", tp->flags);
+    p.flip_xy = (tp->flags & MV3D_TOP_FLIP_XY) ? 1 : 0;
+    p.center_car = (tp->flags & MV3D_TOP_FILTER_CENTER_CAR) ? 1 : 0;
     p.want_top = want_top ? 1 : 0;
     p.want_front = want_front ? 1 : 0;
     p.top_frame_floats = cells * p.planes;
@@ -803,7 +806,7 @@ static int make_py_params(const mv3d_ctx *ctx, const mv3d_pytwin_params *pp, boo
     ViewParams p;
     memset(&p, 0, sizeof(p));
     p.py = 1;
-    p.py_center_car = pp->filter_center_car ? 1 : 0;
+    p.center_car = pp->filter_center_car ? 1 : 0;
     p.x_min = pp->x_min; p.y_min = pp->y_min; p.z_min = pp->z_min;
     p.x_max = pp->x_max; p.y_max = pp->y_max; p.z_max = pp->z_max;
     p.x_div = pp->x_div; p.y_div = pp->y_div; p.z_div = pp->z_div;

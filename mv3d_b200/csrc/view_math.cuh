@@ -19,7 +19,8 @@ struct ViewParams {
     int xn, yn, zn, planes;       // planes = zn + 2
     int quant_floor;              // 0: (int)q [T:107-109]   1: (int)floor(q) [TF:124-126]
     int py;                       // 1: semantics of the reference's PYTHON lidar_to_top (src/data.py:296-367), see py_classify
-    int py_center_car;            // src/data.py:224-227,313-314
+    int center_car;               // drop points with |x| <= 2.35 and |y| <= 1.05 first (filter_center_car, src/data.py:224-227,266-267,313-314)
+    int flip_xy;                  // C routine only: store cell (X-1, Y-1) at [xn-X][yn-Y], the np.flipud(np.fliplr(.)) of src/data.py:290
     float x_max, y_max, z_max;    // the Python encoders crop with open intervals on all three axes
     int want_top, want_front;
     long long top_frame_floats;   // xn*yn*planes
@@ -115,7 +116,7 @@ __device__ __forceinline__ CellHit py_classify(const float4 &pt, const ViewParam
     c.h = 0.0f;
     c.lower = false;
     if (!py_crop(pt, p)) return c;
-    if (p.py_center_car && !(fabsf(pt.x) > 2.35f || fabsf(pt.y) > 1.05f)) return c;  // f32(4.7/2), f32(2.1/2)
+    if (p.center_car && !(fabsf(pt.x) > 2.35f || fabsf(pt.y) > 1.05f)) return c;  // f32(4.7/2), f32(2.1/2)
     const int qx = cvtt_f32(npy_floor_dividef(__fsub_rn(pt.x, p.x_min), p.x_div));
     const int qy = cvtt_f32(npy_floor_dividef(__fsub_rn(pt.y, p.y_min), p.y_div));
     if (!(qx >= 0 && qx < p.xn && qy >= 0 && qy < p.yn)) return c;
@@ -134,11 +135,19 @@ __device__ __forceinline__ CellHit classify(const float4 &pt, const ViewParams &
     if (p.py) return py_classify(pt, p);
     CellHit c;
     c.lower = false;
+    if (p.center_car && !(fabsf(pt.x) > 2.35f || fabsf(pt.y) > 1.05f)) {  // removed before the C routine is called
+        c.keep = false;
+        c.cell = kInvalidKey;
+        c.slice = 0;
+        c.h = 0.0f;
+        return c;
+    }
     const int X = quantise(pt.x, p.x_min, p.x_div, p.quant_floor);
     const int Y = quantise(pt.y, p.y_min, p.y_div, p.quant_floor);
     const int Z = quantise(pt.z, p.z_min, p.z_div, p.quant_floor);
     c.keep = (X >= 1 && Y >= 1 && Z >= 0 && X < p.xn && Y < p.yn && Z < p.zn);
-    c.cell = c.keep ? (uint32_t)((X - 1) * p.yn + (Y - 1)) : kInvalidKey;
+    c.cell = !c.keep ? kInvalidKey
+                     : p.flip_xy ? (uint32_t)((p.xn - X) * p.yn + (p.yn - Y)) : (uint32_t)((X - 1) * p.yn + (Y - 1));
     c.slice = Z;
     c.h = __fsub_rn(pt.z, p.z_min);
     return c;

@@ -14,7 +14,7 @@ from .params import FrontParams, TopParams
 
 
 def _top_c(top: TopParams) -> _lib.TopParamsC:
-    return _lib.TopParamsC(*top.floats, top.xn, top.yn, top.zn)
+    return _lib.TopParamsC(*top.floats, top.xn, top.yn, top.zn, top.flags)
 
 
 def _front_c(front: FrontParams) -> _lib.FrontParamsC:

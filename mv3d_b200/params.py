@@ -27,6 +27,13 @@ class TopParams:
     xn: int = -1
     yn: int = -1
     zn: int = -1
+    # What `clidar_to_top` (src/data.py:265-291) does around the C call, fused into the encode (MV3D_TOP_* flags):
+    flip: bool = False               # np.flipud(np.fliplr(top_flip)), :290
+    filter_center_car: bool = False  # filter_center_car, :224-227, for the didi data sets (:266-267)
+
+    @property
+    def flags(self) -> int:
+        return (1 if self.flip else 0) | (2 if self.filter_center_car else 0)
 
     def __post_init__(self):
         # Grid sizes as the reference caller computes them, in double (src/data.py:270-272).
@@ -98,6 +105,13 @@ REFERENCE_KITTI_TOP = TopParams(0.0, 80.0, -30.0, 30.0, -4.2, 0.8, 0.1, 0.1, 0.2
 REFERENCE_DIDI_TOP = TopParams(-45.0, 45.0, -10.0, 10.0, -3.0, 0.7, 0.2, 0.2, 0.3)
 REFERENCE_DIDI2_TOP = TopParams(-50.0, 50.0, -30.0, 30.0, -3.5, 0.6, 0.2, 0.2, 0.3)
 
+# `clidar_to_top` per data set (src/data.py:265-291): the C routine, flipped; the centre-car filter only for `didi`
+# (and `test`) -- unlike the Python encoder, which also filters `didi2` (:313).
+CLIDAR_KITTI = replace(REFERENCE_KITTI_TOP, flip=True)
+CLIDAR_DIDI = replace(REFERENCE_DIDI_TOP, flip=True, filter_center_car=True)
+CLIDAR_DIDI2 = replace(REFERENCE_DIDI2_TOP, flip=True)
+CLIDAR_PRESETS = {"kitti": CLIDAR_KITTI, "didi": CLIDAR_DIDI, "test": CLIDAR_DIDI, "didi2": CLIDAR_DIDI2}
+
 PRESETS = {
     "kitti_paper": KITTI_PAPER_TOP,
     "dense": DENSE_TOP,
@@ -107,7 +121,8 @@ PRESETS = {
 }
 
 __all__ = ["TopParams", "FrontParams", "KITTI_PAPER_TOP", "KITTI_FRONT_64x512", "DENSE_TOP",
-           "REFERENCE_KITTI_TOP", "REFERENCE_DIDI_TOP", "REFERENCE_DIDI2_TOP", "PRESETS", "replace"]
+           "REFERENCE_KITTI_TOP", "REFERENCE_DIDI_TOP", "REFERENCE_DIDI2_TOP", "PRESETS", "replace",
+           "CLIDAR_KITTI", "CLIDAR_DIDI", "CLIDAR_DIDI2", "CLIDAR_PRESETS"]
 
 
 @dataclass(frozen=True)

@@ -74,16 +74,32 @@ def createTopAndFrontMaps(raw, num, top_flip, front_flip, top_paras, front_paras
         raise RuntimeError("createTopAndFrontMaps: " + err)
 
 
-def clidar_to_top(lidar, top=None):
-    """`src/data.py:265-291` on the new library: encode, then view the result flipped in X and Y.
+_clidar_encoder = None
 
-    Deviation from the reference, on purpose: the output is allocated as float32, the type
-    the C symbol writes; the reference allocates float64 there and reads back garbage. The didi-only
-    centre-car filter (`src/data.py:224-227`) is applied by the caller, as it is a dataset choice.
+
+def clidar_to_top(lidar, top=None):
+    """`src/data.py:265-291` on the new library: [centre-car filter,] `createTopMaps`, `np.flipud(np.fliplr(.))`.
+
+    `top`: a `TopParams`; default `CLIDAR_KITTI` (the reference picks the TOP_* constants and the filter from
+    `cfg.DATA_SETS_TYPE`: see `params.CLIDAR_PRESETS`). With `top.flip` / `top.filter_center_car` set, both steps
+    happen inside the encode (MV3D_TOP_FLIP_XY / MV3D_TOP_FILTER_CENTER_CAR) and the result is a contiguous array;
+    a parameter set without the flags is encoded as the C routine does and flipped as a numpy view, like the
+    reference.
+
+    Deviation from the reference, on purpose (SURVEY.md Q12): the output is float32, the type the C symbol writes;
+    the reference allocates float64 there and reads back garbage.
     """
-    from .params import REFERENCE_KITTI_TOP
-    top = top or REFERENCE_KITTI_TOP
+    global _clidar_encoder
+    from .params import CLIDAR_KITTI
+    top = top or CLIDAR_KITTI
     lidar = np.ascontiguousarray(lidar, dtype=np.float32)
+    if top.flags:
+        if _clidar_encoder is None:
+            import os
+            from .encoder import ViewEncoder
+            _clidar_encoder = ViewEncoder(int(os.environ.get("MV3D_DEVICE", "0")), semantics="top")
+        out, _ = _clidar_encoder.encode_host(lidar, [0, lidar.shape[0]], top)
+        return out[0]
     top_flip = np.ones(top.shape, dtype=np.float32)
     createTopMaps(lidar, lidar.shape[0], top_flip, top.as_top_paras())
     return np.flipud(np.fliplr(top_flip))
