@@ -13,9 +13,11 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libmv3d_encode.so")
-SOURCES = ["encode_kernels.cu", "mv3d_abi.cu", "host_expand.cu", "anchor_kernels.cu", "anchor_abi.cu"]
+SOURCES = ["encode_kernels.cu", "mv3d_abi.cu", "host_expand.cu", "anchor_kernels.cu", "anchor_abi.cu",
+           "sweep_io.cu"]
 HEADERS = ["encode_kernels.h", "view_math.cuh", "host_expand.h", "ctx.h", "anchor_kernels.h",
-           os.path.join("..", "..", "include", "mv3d_encode.h"), os.path.join("..", "..", "include", "mv3d_anchors.h")]
+           os.path.join("..", "..", "include", "mv3d_encode.h"), os.path.join("..", "..", "include", "mv3d_anchors.h"),
+           os.path.join("..", "..", "include", "mv3d_io.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-fmad=false", "-Xcompiler", "-fPIC", "-shared"]
 
@@ -39,7 +41,7 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     """Compile csrc/*.cu into mv3d_b200/libmv3d_encode.so for sm_100a (nvcc cross-compiles without a GPU)."""
     if not force and not _stale():
         return LIB_PATH
-    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH] + [os.path.join(CSRC, s) for s in SOURCES]
+    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lz"]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     res = subprocess.run(cmd, capture_output=True, text=True)
@@ -84,6 +86,8 @@ EXPORTED_SYMBOLS = (
     "mv3d_pytwin_encode_batch_dev", "mv3d_pytwin_encode_batch_host", "mv3d_debug_atan2f",
     "mv3d_ctx_set_anchors", "mv3d_remove_empty_anchor_dev", "mv3d_remove_empty_anchor_host",
     "mv3d_encode_filter_batch_dev", "mv3d_pytwin_encode_filter_batch_dev",
+    "mv3d_io_stat_sweeps", "mv3d_io_read_sweeps", "mv3d_io_write_npy", "mv3d_io_write_npy_batch", "mv3d_io_npy_info",
+    "mv3d_io_read_npy", "mv3d_io_write_npz_compressed", "mv3d_io_write_npz_compressed_batch",
 )
 ANCHORS_AUTO, ANCHORS_EXACT = 0, 1
 ANCHOR_MAX_LINES = 50
@@ -138,6 +142,16 @@ def load_library() -> ctypes.CDLL:
                                                  ctypes.POINTER(FrontParamsC), ci, ci, cf, ci, vp, vp, vp]
     lib.mv3d_pytwin_encode_filter_batch_dev.argtypes = [vp, vp, ctypes.POINTER(ci), ci, vp, vp,
                                                         ctypes.POINTER(PyTwinParamsC), cf, ci, vp, vp, vp]
+    cpp, ll, sz = ctypes.POINTER(ctypes.c_char_p), ctypes.c_longlong, ctypes.c_size_t
+    llp = ctypes.POINTER(ll)
+    lib.mv3d_io_stat_sweeps.argtypes = [cpp, ci, vp]
+    lib.mv3d_io_read_sweeps.argtypes = [cpp, ci, vp, vp, ci]
+    lib.mv3d_io_write_npy.argtypes = [ctypes.c_char_p, vp, llp, ci]
+    lib.mv3d_io_write_npy_batch.argtypes = [cpp, ci, vp, sz, llp, ci, ci]
+    lib.mv3d_io_npy_info.argtypes = [ctypes.c_char_p, llp, ctypes.POINTER(ci), llp]
+    lib.mv3d_io_read_npy.argtypes = [ctypes.c_char_p, vp, sz]
+    lib.mv3d_io_write_npz_compressed.argtypes = [ctypes.c_char_p, ctypes.c_char_p, vp, llp, ci, ci]
+    lib.mv3d_io_write_npz_compressed_batch.argtypes = [cpp, ci, ctypes.c_char_p, vp, sz, llp, ci, ci, ci]
     _lib = lib
     return lib
 

@@ -93,6 +93,7 @@ __device__ __forceinline__ void store_zero16(float4 *p)
 //   keys[g] = {output cell, rank inside its tile's bin}  ({kInvalidKey, 0} when the point is rejected)
 // grid = (blocks, batch); each CTA strides over one sweep's points with coalesced 16-byte loads.
 // ------------------------------------------------------------------------------------------------
+template <bool kPy>
 __global__ void __launch_bounds__(kPointThreads)
 classify_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
                 uint2 *__restrict__ keys, unsigned *__restrict__ tile_count, unsigned *__restrict__ fv_winner)
@@ -114,10 +115,10 @@ classify_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
         uint32_t tile = kInvalidKey;
         if (i < n) {
             const float4 pt = load_point(pts + base + i);
-            const CellHit c = classify(pt, p);
+            const CellHit c = classify_as<kPy>(pt, p);
             if (c.keep) {
                 cell = c.cell;
-                if (p.want_front) {
+                if (!kPy && p.want_front) {
                     const int pix = front_pixel(pt, p);
                     if (pix >= 0) atomicMax(winners + pix, (unsigned)i + 1u);
                 }
@@ -202,6 +203,7 @@ tile_scan_kernel(unsigned *__restrict__ tile_count, unsigned *__restrict__ tile_
 //   record = { cell-in-tile | slice << 16,  h bits,  point index,  intensity bits }   (16 bytes)
 // Order inside a bin is arbitrary; every order-dependent decision uses the point index carried along.
 // ------------------------------------------------------------------------------------------------
+template <bool kPy>
 __global__ void __launch_bounds__(kPointThreads)
 bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
            const uint2 *__restrict__ keys, const unsigned *__restrict__ tile_off, uint4 *__restrict__ binned)
@@ -218,7 +220,7 @@ bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
         const uint32_t local = k.x - tile * (uint32_t)p.tile_cells;
         uint32_t zfield;
         float key;
-        if (p.py) {
+        if (kPy) {
             // Python twin: key = qz; slice field = floor(qz) (kNoSlice when it is past the last slice, such a point
             // still counts and can win the intensity), top bit = "also closes the slice below"
             const CellHit c = py_classify(pt, p);
@@ -258,7 +260,7 @@ bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
 // zero -- into a pre-zeroed per-frame bit map, and raise the frame's flag when an intensity is negative, -0 or NaN
 // (the only values of a view that can be; then the filter must take exact sums). The bits of a tile are gathered
 // in shared memory; the first and last word of a tile may be shared with its neighbours and go out as atomics.
-template <bool kCompact, bool kOccupancy = false>
+template <bool kCompact, bool kOccupancy, bool kPy>
 __device__ __forceinline__ void
 tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
           ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
@@ -342,7 +344,7 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 unsigned *cellw = img + local * planes;
                 if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(&ndirty, 1u)] = local;
                 if ((int)q.y > 0) {  // h > 0: the reference's maps start at 0 and update on strict '>'
-                    if (p.py) {  // slice = floor(qz) if it exists, and the one below when qz is integral
+                    if (kPy) {  // slice = floor(qz) if it exists, and the one below when qz is integral
                         const unsigned zs = Z & (kLowerFlag - 1u);
                         if (zs != kNoSlice) atomicMax(cellw + zs, q.y);
                         if (Z & kLowerFlag) {
@@ -378,7 +380,7 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 for (int k = lane; k < planes; k += 32) {
                     if (k < zn) {
                         const unsigned raw = cellw[k];
-                        if (raw) cellw[k] = __float_as_uint(p.py ? __fsub_rn(__uint_as_float(raw), (float)k)  // max(qz) - z
+                        if (raw) cellw[k] = __float_as_uint(kPy ? __fsub_rn(__uint_as_float(raw), (float)k)  // max(qz) - z
                                                                  : slice_value(__uint_as_float(raw), p.z_div, k));
                     } else if (k == zn + 1) {
                         const unsigned c = cellw[k];
@@ -436,29 +438,32 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
     if (!kCompact && tid == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
 }
 
+template <bool kPy>
 __global__ void __launch_bounds__(kTileThreads)
 tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
                   ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles)
 {
-    tile_body<false>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u);
+    tile_body<false, false, kPy>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u);
 }
 
 // Same, and the occupancy bits / flag of every frame for the empty-anchor filter (see tile_body).
+template <bool kPy>
 __global__ void __launch_bounds__(kTileThreads)
 tile_build_occupancy_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
                             ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
                             OccupancySink sink)
 {
-    tile_body<false, true>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u, sink);
+    tile_body<false, true, kPy>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u, sink);
 }
 
 // Same reduction, compact output (see tile_body).
+template <bool kPy>
 __global__ void __launch_bounds__(kTileThreads)
 tile_compact_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
                     ViewParams p, const float *__restrict__ lut, int total_tiles, unsigned *__restrict__ compact,
                     unsigned compact_cap)
 {
-    tile_body<true>(binned, tile_off, offs, p, lut, nullptr, total_tiles, compact, compact_cap);
+    tile_body<true, false, kPy>(binned, tile_off, offs, p, lut, nullptr, total_tiles, compact, compact_cap);
 }
 
 
@@ -842,16 +847,18 @@ size_t tile_smem_bytes(const ViewParams &p)
 cudaError_t tile_build_configure(const ViewParams &p, int *blocks_per_sm)
 {
     const size_t smem = tile_smem_bytes(p);
-    cudaError_t e = cudaFuncSetAttribute(tile_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    auto kernel = p.py ? tile_build_kernel<true> : tile_build_kernel<false>;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, tile_build_kernel, kTileThreads, smem);
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, kernel, kTileThreads, smem);
 }
 
 int launch_classify(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
                     uint2 *keys, unsigned *tile_count, unsigned *fv_winner, cudaStream_t s)
 {
     dim3 grid(point_blocks(max_points), batch);
-    classify_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_count, fv_winner);
+    auto kernel = p.py ? classify_kernel<true> : classify_kernel<false>;
+    kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_count, fv_winner);
     return 1;
 }
 
@@ -868,7 +875,8 @@ int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p,
                const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s)
 {
     dim3 grid(point_blocks(max_points), batch);
-    bin_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_off, binned);
+    auto kernel = p.py ? bin_kernel<true> : bin_kernel<false>;
+    kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_off, binned);
     return 1;
 }
 
@@ -878,12 +886,12 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
     const int total = batch * p.tiles_per_frame;
     const int grid = grid_blocks < total ? grid_blocks : total;
     if (sink && sink->words) {
-        cudaFuncSetAttribute(tile_build_occupancy_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             (int)tile_smem_bytes(p));
-        tile_build_occupancy_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top,
-                                                                                   total, *sink);
+        auto kernel = p.py ? tile_build_occupancy_kernel<true> : tile_build_occupancy_kernel<false>;
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(p));
+        kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total, *sink);
     } else {
-        tile_build_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
+        auto kernel = p.py ? tile_build_kernel<true> : tile_build_kernel<false>;
+        kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
     }
     return 1;
 }
@@ -894,9 +902,9 @@ int launch_tile_compact(const uint4 *binned, const unsigned *tile_off, const Fra
 {
     const int total = batch * p.tiles_per_frame;
     const int grid = grid_blocks < total ? grid_blocks : total;
-    cudaFuncSetAttribute(tile_compact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(p));
-    tile_compact_kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, total, compact,
-                                                                       compact_cap);
+    auto kernel = p.py ? tile_compact_kernel<true> : tile_compact_kernel<false>;
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(p));
+    kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, total, compact, compact_cap);
     return 1;
 }
 

@@ -130,9 +130,12 @@ __device__ __forceinline__ CellHit py_classify(const float4 &pt, const ViewParam
     return c;
 }
 
-__device__ __forceinline__ CellHit classify(const float4 &pt, const ViewParams &p)
+// kPy selects the Python encoder's semantics at compile time: the kernels of the tile strategy are instantiated for
+// both, so the C-routine path carries none of the other's branches or registers.
+template <bool kPy>
+__device__ __forceinline__ CellHit classify_as(const float4 &pt, const ViewParams &p)
 {
-    if (p.py) return py_classify(pt, p);
+    if (kPy) return py_classify(pt, p);
     CellHit c;
     c.lower = false;
     if (p.center_car && !(fabsf(pt.x) > 2.35f || fabsf(pt.y) > 1.05f)) {  // removed before the C routine is called
@@ -151,6 +154,11 @@ __device__ __forceinline__ CellHit classify(const float4 &pt, const ViewParams &
     c.slice = Z;
     c.h = __fsub_rn(pt.z, p.z_min);
     return c;
+}
+
+__device__ __forceinline__ CellHit classify(const float4 &pt, const ViewParams &p)
+{
+    return p.py ? classify_as<true>(pt, p) : classify_as<false>(pt, p);
 }
 
 // Height-slice output value: h / z_DIV - k  [T:205; TF:143 then :258].

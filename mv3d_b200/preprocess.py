@@ -1,0 +1,119 @@
+"""The preprocessing run of `src/preprocess_for_mv3d.py`, batched on the GPU.
+
+The reference maps one handler per `.bin` file over a process pool (`:62-75`): `np.fromfile`, `data.lidar_to_top`,
+`Preprocess.lidar_to_front_fast`, two `np.save` calls (`:28-38`, 8 s of numpy per frame). Here the same files are
+read `batch` at a time by native reader threads into page-locked memory, encoded in one Python-twin GPU call per
+batch, and written back as the same `top_view/<tag>.npy` / `front_view/<tag>.npy` files by native writer threads,
+while a background thread reads the next batch. Output files are byte-identical to what `np.save` writes for the
+same arrays.
+
+    python -m mv3d_b200.preprocess ~/data/kitti/training            # velodyne/*.bin -> top_view/, front_view/
+"""
+from __future__ import annotations
+
+import argparse
+import glob
+import os
+import threading
+import time
+from typing import Optional, Sequence
+
+from . import sweep_io
+from .params import PYTWIN_PRESETS, PyTwinParams
+
+__all__ = ["preprocess_files", "preprocess_directory"]
+
+
+def _tag(fname: str) -> str:
+    return fname.split("/")[-1].split(".")[-2]          # src/preprocess_for_mv3d.py:32
+
+
+def preprocess_files(files: Sequence[str], top_dir: Optional[str], front_dir: Optional[str],
+                     params: PyTwinParams, batch: int = 16, device: int = 0, io_threads: int = 0,
+                     compressed_top: bool = False, encoder=None) -> dict:
+    """Encode `files` and write `<top_dir>/<tag>.npy`, `<front_dir>/<tag>.npy` (either directory may be None).
+    `compressed_top`: write the bird's-eye views as `np.savez_compressed(path, top_view=top)` archives
+    (`<tag>.npy.npz`, the format of `src/data.py:521`) instead. Returns counters and timings."""
+    from .pytwin import PyTwinEncoder
+    own = encoder is None
+    enc = encoder or PyTwinEncoder(device)
+    for d in (top_dir, front_dir):
+        if d:
+            os.makedirs(d, exist_ok=True)                # `:34-35`
+    groups = [list(files[i:i + batch]) for i in range(0, len(files), batch)]
+    stats = {"frames": 0, "points": 0, "read_s": 0.0, "encode_s": 0.0, "write_s": 0.0}
+    nxt = {}
+
+    def read(group, slot):
+        t0 = time.perf_counter()
+        try:
+            slot["data"] = sweep_io.read_sweeps(group, threads=io_threads)
+        except Exception as e:
+            slot["error"] = e
+        slot["s"] = time.perf_counter() - t0
+
+    def start(i):
+        if i < len(groups):
+            slot = {}
+            th = threading.Thread(target=read, args=(groups[i], slot), daemon=True)
+            th.start()
+            nxt[i] = (th, slot)
+
+    t_all = time.perf_counter()
+    start(0)
+    for i, group in enumerate(groups):
+        th, slot = nxt.pop(i)
+        th.join()
+        start(i + 1)                                      # read the next batch while this one is encoded and written
+        if "error" in slot:
+            raise slot["error"]
+        points, offsets = slot["data"]
+        stats["read_s"] += slot["s"]
+        t0 = time.perf_counter()
+        top, front = enc.encode_host(points, offsets, params, want_top=top_dir is not None,
+                                     want_front=front_dir is not None)
+        t1 = time.perf_counter()
+        tags = [_tag(f) for f in group]
+        if top_dir:
+            paths = [os.path.join(top_dir, t + ".npy") for t in tags]
+            if compressed_top:
+                sweep_io.savez_compressed_batch(paths, top, member="top_view", threads=io_threads)
+            else:
+                sweep_io.save_batch(paths, top, threads=io_threads)
+        if front_dir:
+            sweep_io.save_batch([os.path.join(front_dir, t + ".npy") for t in tags], front, threads=io_threads)
+        t2 = time.perf_counter()
+        stats["encode_s"] += t1 - t0
+        stats["write_s"] += t2 - t1
+        stats["frames"] += len(group)
+        stats["points"] += int(offsets[-1])
+    stats["total_s"] = time.perf_counter() - t_all
+    if own:
+        enc.close()
+    return stats
+
+
+def preprocess_directory(split_dir: str, params: PyTwinParams, **kw) -> dict:
+    """`main_train` / `main_test` of the reference (`:62-70`): `<split_dir>/velodyne/*.bin` ->
+    `<split_dir>/top_view/`, `<split_dir>/front_view/`."""
+    files = sorted(glob.glob(os.path.join(split_dir, "velodyne", "*.bin")))
+    return preprocess_files(files, os.path.join(split_dir, "top_view"), os.path.join(split_dir, "front_view"),
+                            params, **kw)
+
+
+def main(argv=None) -> int:
+    ap = argparse.ArgumentParser(description=__doc__.split("\n")[0])
+    ap.add_argument("split_dir", help="directory holding velodyne/*.bin (e.g. ~/data/kitti/training)")
+    ap.add_argument("--preset", default="kitti", choices=sorted(PYTWIN_PRESETS))
+    ap.add_argument("--batch", type=int, default=16)
+    ap.add_argument("--device", type=int, default=0)
+    ap.add_argument("--io-threads", type=int, default=0)
+    args = ap.parse_args(argv)
+    stats = preprocess_directory(os.path.expanduser(args.split_dir), PYTWIN_PRESETS[args.preset], batch=args.batch,
+                                 device=args.device, io_threads=args.io_threads)
+    print(stats)
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())
