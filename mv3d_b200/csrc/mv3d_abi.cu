@@ -609,8 +609,14 @@ extern "C" int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int
 // rebuild the dense tensor in the caller's buffer (zero-fill + scatter of the finished values) while the GPU works
 // on the next sweeps. PCIe carries ~3 MB per sweep instead of 60.8 MB; the caller's buffer may be pageable.
 // ------------------------------------------------------------------------------------------------
+static int py_encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
+                                float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp,
+                                cudaStream_t s, const OccupancySink *sink, const CompactOut *compact);
+
+// pyfp: non-NULL for the Python-twin mode (its own front view and encode call; everything else is shared).
 static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const int *offsets_host, int batch,
-                               float *top_host, float *front_host, const ViewParams &p)
+                               float *top_host, float *front_host, const ViewParams &p,
+                               const PyFrontParams *pyfp = nullptr)
 {
     if (!ctx->pool) {
         int threads = ctx->host_threads;
@@ -627,7 +633,8 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         if (!ctx->pool) return fail("cannot create the host thread pool");
     }
     const size_t cells = (size_t)p.xn * p.yn;
-    const size_t front_bytes = (size_t)p.front_frame_floats * 4;
+    const size_t front_floats = pyfp ? (size_t)pyfp->pixels * 3 : (size_t)p.front_frame_floats;
+    const size_t front_bytes = front_floats * 4;
     const size_t toff_words = (size_t)p.tiles_per_frame + 1;
 
     // Layout of the list on both sides: cell indices [cap], then values [cap][planes], cap = points of the sweep.
@@ -658,8 +665,10 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         out.cap = (unsigned)cap;
         float *front_d = front_host ? static_cast<float *>(slot.front.ptr) : nullptr;
         // `top` only has to be non-NULL here: the compact kernel never dereferences it
-        if (encode_dev_locked(ctx, slot.ws, static_cast<const float *>(slot.points.ptr), local_off, 1,
-                              reinterpret_cast<float *>(slot.compact.ptr), front_d, p, MV3D_STRATEGY_TILE, s, &out))
+        const float *pts_d = static_cast<const float *>(slot.points.ptr);
+        float *top_stub = reinterpret_cast<float *>(slot.compact.ptr);
+        if (pyfp ? py_encode_dev_locked(ctx, slot.ws, pts_d, local_off, 1, top_stub, front_d, p, *pyfp, s, nullptr, &out)
+                 : encode_dev_locked(ctx, slot.ws, pts_d, local_off, 1, top_stub, front_d, p, MV3D_STRATEGY_TILE, s, &out))
             return -1;
         CUDA_TRY(cudaMemcpyAsync(slot.toff_stage.ptr, slot.ws.tile_off.ptr, toff_words * 4, cudaMemcpyDeviceToHost, s));
         // Speculative copy sized from the previous sweep (first sweep: every slot); topped up later if short.
@@ -712,7 +721,7 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         const std::function<void()> errand = [&] {
             double t1 = now();
             if (front_host && front_bytes)
-                memcpy(front_host + (size_t)i * (size_t)p.front_frame_floats, slot.front_stage.ptr, front_bytes);
+                memcpy(front_host + (size_t)i * front_floats, slot.front_stage.ptr, front_bytes);
             t_front += now() - t1;
             t1 = now();
             if (i >= 1 && i - 1 + kSlots < batch) enq_rc = enqueue(i - 1 + kSlots);
@@ -832,7 +841,7 @@ static int make_py_params(const mv3d_ctx *ctx, const mv3d_pytwin_params *pp, boo
 
 static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
                             float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp, cudaStream_t s,
-                            const OccupancySink *sink = nullptr)
+                            const OccupancySink *sink = nullptr, const CompactOut *compact = nullptr)
 {
     FrameOffsets offs;
     memset(&offs, 0, sizeof(offs));
@@ -862,9 +871,15 @@ static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_de
         timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, nullptr, s); });
         timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
         timed_launch(ctx, K_BIN, s, [&] { return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s); });
-        timed_launch(ctx, K_TILE_BUILD, s, [&] {
-            return launch_tile_build(binned, toff, offs, p, ctx->lut_py, top_dev, batch, blocks_per_sm * ctx->sm_count, s, sink);
-        });
+        if (compact)  // host read-back: report the touched cells only (single sweep per call)
+            timed_launch(ctx, K_TILE_COMPACT, s, [&] {
+                return launch_tile_compact(binned, toff, offs, p, ctx->lut_py, batch, blocks_per_sm * ctx->sm_count,
+                                           compact->entries, compact->cap, s);
+            });
+        else
+            timed_launch(ctx, K_TILE_BUILD, s, [&] {
+                return launch_tile_build(binned, toff, offs, p, ctx->lut_py, top_dev, batch, blocks_per_sm * ctx->sm_count, s, sink);
+            });
     }
     if (front_dev && fp.pixels > 0) {
         // list heads per pixel (self-cleaning, zero between calls) and one link per point (reuses the key scratch)
@@ -880,7 +895,7 @@ static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_de
 
 static int py_encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
                                 float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp, cudaStream_t s,
-                                const OccupancySink *sink = nullptr)
+                                const OccupancySink *sink = nullptr, const CompactOut *compact = nullptr)
 {
     if (offsets[batch] > offsets[0] && (reinterpret_cast<uintptr_t>(points_dev) & 15u))
         return fail("points_dev must be 16-byte aligned");
@@ -894,7 +909,8 @@ static int py_encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *point
             sink_c.words += (size_t)c0 * sink->words_per_frame;
             sink_c.flags += c0;
         }
-        if (enqueue_py_chunk(ctx, ws, points_dev, offsets + c0, nb, top_c, front_c, p, fp, s, sink ? &sink_c : nullptr))
+        if (enqueue_py_chunk(ctx, ws, points_dev, offsets + c0, nb, top_c, front_c, p, fp, s, sink ? &sink_c : nullptr,
+                             compact))
             return -1;
     }
     return 0;
@@ -988,7 +1004,7 @@ extern "C" int mv3d_pytwin_encode_filter_batch_dev(mv3d_ctx *ctx, const float *p
     return anchor_run_locked(ctx, plan, top_dev, limit, keep_dev, count_dev, nullptr, s, have);
 }
 
-// Host buffers: sweep by sweep over the slot streams (H2D, encode, dense D2H).
+// Host buffers: sweep by sweep over the slot streams (H2D, encode, compact read-back; MV3D_HOST_READBACK=dense: dense D2H).
 extern "C" int mv3d_pytwin_encode_batch_host(mv3d_ctx *ctx, const float *points_host, const int *offsets_host, int batch,
                                              float *top_host, float *front_host, const mv3d_pytwin_params *pp)
 {
@@ -1002,6 +1018,13 @@ extern "C" int mv3d_pytwin_encode_batch_host(mv3d_ctx *ctx, const float *points_
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
     const size_t top_bytes = (size_t)p.top_frame_floats * 4, front_bytes = (size_t)fp.pixels * 3 * 4;
+    if (ctx->host_compact && top_host && top_bytes) {  // compact read-back, as for the C routine's views
+        int rcc = encode_host_compact(ctx, points_host, offsets_host, batch, top_host, front_host, p, &fp);
+        if (rcc)
+            for (auto &slot : ctx->slots)
+                if (slot.stream) cudaStreamSynchronize(slot.stream);
+        return rcc;
+    }
     int rc = 0;
     for (int i = 0; i < batch && rc == 0; i++) {
         HostSlot &slot = ctx->slots[i % kSlots];

@@ -101,3 +101,34 @@ def test_batch16_every_frame(pytwin):
         same(top[i], pytwin.lidar_to_top(s, PYTWIN_KITTI), f"frame {i} top")
         same(front[i], pytwin.lidar_to_front_fast(s, PYTWIN_KITTI), f"frame {i} front")
     enc.close()
+
+
+@pytest.mark.parametrize("readback", ["compact", "dense"])
+def test_host_batch_readback(pytwin, readback, monkeypatch):
+    """numpy in / numpy out for a ragged batch, through both ways of bringing the bird's-eye view back: the compact
+    list of touched cells rebuilt by host threads (default) and the dense device-to-host copy."""
+    from mv3d_b200.pytwin import PyTwinEncoder
+    monkeypatch.setenv("MV3D_HOST_READBACK", readback)
+    enc = PyTwinEncoder(0)
+    qc = {c[0]: c[1] for c in pytwin_cases.quirk_cases()}
+    sweeps = [hdl64_sweep(6), np.zeros((0, 4), np.float32), qc["integral_qz"], hdl64_sweep(7)[:30001], hdl64_sweep(8)[:1],
+              qc["ties_density"], hdl64_sweep(9)[::3]]
+    pts, offs = pack_sweeps(sweeps)
+    for p in (PYTWIN_KITTI, PYTWIN_DIDI2):
+        top, front = enc.encode_host(pts, offs, p)
+        for i, s in enumerate(sweeps):
+            same(top[i], pytwin.lidar_to_top(s, p), f"{readback} sweep {i} top")
+            same(front[i], pytwin.lidar_to_front_fast(s, p), f"{readback} sweep {i} front")
+    top, front = enc.encode_host(pts, offs, PYTWIN_KITTI, want_front=False)
+    assert front is None
+    same(top[0], pytwin.lidar_to_top(sweeps[0], PYTWIN_KITTI), "top only")
+    h2d, d2h = ctypes_transfer(enc)
+    assert h2d > 0 and d2h > 0
+    enc.close()
+
+
+def ctypes_transfer(enc):
+    import ctypes
+    h2d, d2h = ctypes.c_ulonglong(), ctypes.c_ulonglong()
+    assert enc._lib.mv3d_ctx_transfer_bytes(enc._ctx, ctypes.byref(h2d), ctypes.byref(d2h), 0) == 0
+    return h2d.value, d2h.value
