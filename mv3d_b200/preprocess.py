@@ -59,8 +59,32 @@ def preprocess_files(files: Sequence[str], top_dir: Optional[str], front_dir: Op
             th.start()
             nxt[i] = (th, slot)
 
+    # Two sets of output buffers: while the writer threads drain one, the GPU fills the other.
+    import numpy as np
+    bufs = [{"top": np.empty((batch, *params.top_shape), np.float32) if top_dir else None,
+             "front": np.empty((batch, *params.front_shape), np.float32) if front_dir else None} for _ in range(2)]
+    writers = [None, None]
+    write_error = []
+
+    def write(group, top, front, slot):
+        t0 = time.perf_counter()
+        try:
+            tags = [_tag(f) for f in group]
+            if top_dir:
+                paths = [os.path.join(top_dir, t + ".npy") for t in tags]
+                if compressed_top:
+                    sweep_io.savez_compressed_batch(paths, top, member="top_view", threads=io_threads)
+                else:
+                    sweep_io.save_batch(paths, top, threads=io_threads)
+            if front_dir:
+                sweep_io.save_batch([os.path.join(front_dir, t + ".npy") for t in tags], front, threads=io_threads)
+        except Exception as e:
+            write_error.append(e)
+        slot["s"] = time.perf_counter() - t0
+
     t_all = time.perf_counter()
     start(0)
+    write_slots = []
     for i, group in enumerate(groups):
         th, slot = nxt.pop(i)
         th.join()
@@ -69,24 +93,27 @@ def preprocess_files(files: Sequence[str], top_dir: Optional[str], front_dir: Op
             raise slot["error"]
         points, offsets = slot["data"]
         stats["read_s"] += slot["s"]
+        b = bufs[i % 2]
+        if writers[i % 2] is not None:                    # this buffer set is still being written out
+            writers[i % 2].join()
+        if write_error:
+            raise write_error[0]
         t0 = time.perf_counter()
         top, front = enc.encode_host(points, offsets, params, want_top=top_dir is not None,
-                                     want_front=front_dir is not None)
-        t1 = time.perf_counter()
-        tags = [_tag(f) for f in group]
-        if top_dir:
-            paths = [os.path.join(top_dir, t + ".npy") for t in tags]
-            if compressed_top:
-                sweep_io.savez_compressed_batch(paths, top, member="top_view", threads=io_threads)
-            else:
-                sweep_io.save_batch(paths, top, threads=io_threads)
-        if front_dir:
-            sweep_io.save_batch([os.path.join(front_dir, t + ".npy") for t in tags], front, threads=io_threads)
-        t2 = time.perf_counter()
-        stats["encode_s"] += t1 - t0
-        stats["write_s"] += t2 - t1
+                                     want_front=front_dir is not None, top_out=b["top"], front_out=b["front"])
+        stats["encode_s"] += time.perf_counter() - t0
+        wslot = {}
+        write_slots.append(wslot)
+        writers[i % 2] = threading.Thread(target=write, args=(group, top, front, wslot), daemon=True)
+        writers[i % 2].start()
         stats["frames"] += len(group)
         stats["points"] += int(offsets[-1])
+    for w in writers:
+        if w is not None:
+            w.join()
+    if write_error:
+        raise write_error[0]
+    stats["write_s"] = sum(w.get("s", 0.0) for w in write_slots)
     stats["total_s"] = time.perf_counter() - t_all
     if own:
         enc.close()

@@ -81,13 +81,22 @@ class PyTwinEncoder:
         return (top_out if want_top else None), (front_out if want_front else None)
 
     def encode_host(self, points: np.ndarray, offsets, params: PyTwinParams = PYTWIN_KITTI, want_top=True,
-                    want_front=True):
-        """numpy in, numpy out (H2D, encode, D2H pipelined inside the library)."""
+                    want_front=True, top_out=None, front_out=None):
+        """numpy in, numpy out (H2D, encode, read-back pipelined inside the library). `top_out` / `front_out`:
+        C-contiguous float32 arrays with room for the batch, to reuse buffers between calls."""
         points = np.ascontiguousarray(points, dtype=np.float32)
         offs = np.ascontiguousarray(offsets, dtype=np.int32)
         batch = len(offs) - 1
-        top = np.empty((batch, *params.top_shape), np.float32) if want_top else None
-        front = np.empty((batch, *params.front_shape), np.float32) if want_front else None
+
+        def buffer(out, shape):
+            if out is None:
+                return np.empty((batch, *shape), np.float32)
+            need = batch * int(np.prod(shape, dtype=np.int64))
+            assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"] and out.size >= need, "output buffer"
+            return out.reshape(-1)[:need].reshape((batch, *shape))
+
+        top = buffer(top_out, params.top_shape) if want_top else None
+        front = buffer(front_out, params.front_shape) if want_front else None
         pc = _params_c(params)
         rc = self._lib.mv3d_pytwin_encode_batch_host(
             self._ctx, points.ctypes.data, offs.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), batch,
