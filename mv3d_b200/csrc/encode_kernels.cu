@@ -83,6 +83,22 @@ __device__ __forceinline__ void bulk_wait_read_all()
 {
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
+// How the tile kernel writes a finished tile (ViewParams::store_mode; MV3D_TILE_STORE=tma|tma_hint|tma_split|lsu|lsu_cs).
+// Default: bulk stores with an L2 evict-first policy -- the output is written once and never read back here, so it
+// should not push the bin records (read by this same kernel) out of L2. Measured in profiles/strategy_experiments_r1.md.
+enum TileStore { kStoreTma = 0, kStoreTmaHint = 1, kStoreTmaSplit = 2, kStoreLsu = 3, kStoreLsuStream = 4 };
+__device__ __forceinline__ void tile_bulk_store(void *gdst, const void *ssrc, uint32_t bytes, int mode)
+{
+    if (mode == kStoreTmaHint) {
+        bulk_store_hint(gdst, ssrc, bytes, l2_policy_evict_first());
+    } else if (mode == kStoreTmaSplit) {  // four bulk operations per tile instead of one
+        const uint32_t quarter = ((bytes >> 2) + 15u) & ~15u;
+        for (uint32_t off = 0; off < bytes; off += quarter)
+            bulk_store(static_cast<char *>(gdst) + off, static_cast<const char *>(ssrc) + off, min(quarter, bytes - off));
+    } else {
+        bulk_store(gdst, ssrc, bytes);
+    }
+}
 __device__ __forceinline__ void store_zero16(float4 *p)
 {
     asm volatile("st.global.cs.v4.f32 [%0], {%1,%1,%1,%1};" :: "l"(p), "f"(0.0f) : "memory");
@@ -260,10 +276,10 @@ bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
 // zero -- into a pre-zeroed per-frame bit map, and raise the frame's flag when an intensity is negative, -0 or NaN
 // (the only values of a view that can be; then the filter must take exact sums). The bits of a tile are gathered
 // in shared memory; the first and last word of a tile may be shared with its neighbours and go out as atomics.
-template <bool kCompact, bool kOccupancy, bool kPy>
+template <bool kCompact, bool kOccupancy, bool kPy, int kStore = kStoreTmaHint>
 __device__ __forceinline__ void
-tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
-          ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
+tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, const FrameOffsets &offs,
+          const ViewParams &p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
           unsigned *__restrict__ compact, unsigned compact_cap, OccupancySink sink = OccupancySink())
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -325,14 +341,20 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
             // nothing to report for an empty tile
         } else if (n0 == 0) {
             // Empty tile: stream the all-zero image; nothing is modified, so no barrier.
-            if (bulk) {
-                if (tid == 0) { bulk_store(dst, img, bytes); bulk_commit(); }
+            if (bulk && kStore == kStoreLsu) {
+                float4 *d4 = reinterpret_cast<float4 *>(dst);
+                for (int w = tid; w < (int)(bytes >> 4); w += kTileThreads) d4[w] = make_float4(0.f, 0.f, 0.f, 0.f);
+            } else if (bulk && kStore == kStoreLsuStream) {
+                float4 *d4 = reinterpret_cast<float4 *>(dst);
+                for (int w = tid; w < (int)(bytes >> 4); w += kTileThreads) store_zero16(d4 + w);
+            } else if (bulk) {
+                if (tid == 0) { tile_bulk_store(dst, img, bytes, kStore); bulk_commit(); }
             } else {
                 for (int w = tid; w < ncell * planes; w += kTileThreads) dst[w] = 0.0f;
             }
         } else {
             // Earlier (empty-tile) bulk stores may still be reading the image: wait before touching it.
-            if (!kCompact) {
+            if (!kCompact && kStore < kStoreLsu) {
                 if (tid == 0) bulk_wait_read_all();
                 __syncthreads();
             }
@@ -405,8 +427,16 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 }
                 for (int d = nd + tid; d < n0; d += kTileThreads)
                     if (beg + (unsigned)d < compact_cap) out_idx[beg + (unsigned)d] = kNoCell;
+            } else if (bulk && kStore >= kStoreLsu) {
+                const uint4 *s4 = reinterpret_cast<const uint4 *>(img);
+                uint4 *d4 = reinterpret_cast<uint4 *>(dst);
+                if (kStore == kStoreLsu) {
+                    for (int w = tid; w < (int)(bytes >> 4); w += kTileThreads) d4[w] = s4[w];
+                } else {
+                    for (int w = tid; w < (int)(bytes >> 4); w += kTileThreads) __stcs(d4 + w, s4[w]);
+                }
             } else if (bulk) {
-                if (tid == 0) { bulk_store(dst, img, bytes); bulk_commit(); bulk_wait_read_all(); }
+                if (tid == 0) { tile_bulk_store(dst, img, bytes, kStore); bulk_commit(); bulk_wait_read_all(); }
             } else {
                 for (int w = tid; w < ncell * planes; w += kTileThreads) dst[w] = __uint_as_float(img[w]);
             }
@@ -438,20 +468,23 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
     if (!kCompact && tid == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
 }
 
-template <bool kPy>
+template <bool kPy, int kStore = kStoreTmaHint>
 __global__ void __launch_bounds__(kTileThreads)
-tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
-                  ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles)
+tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
+                  const __grid_constant__ FrameOffsets offs,
+                  const __grid_constant__ ViewParams p, const float *__restrict__ lut, float *__restrict__ top,
+                  int total_tiles)
 {
-    tile_body<false, false, kPy>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u);
+    tile_body<false, false, kPy, kStore>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u);
 }
 
 // Same, and the occupancy bits / flag of every frame for the empty-anchor filter (see tile_body).
 template <bool kPy>
 __global__ void __launch_bounds__(kTileThreads)
-tile_build_occupancy_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
-                            ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
-                            OccupancySink sink)
+tile_build_occupancy_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
+                  const __grid_constant__ FrameOffsets offs,
+                            const __grid_constant__ ViewParams p, const float *__restrict__ lut,
+                            float *__restrict__ top, int total_tiles, OccupancySink sink)
 {
     tile_body<false, true, kPy>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u, sink);
 }
@@ -459,9 +492,10 @@ tile_build_occupancy_kernel(const uint4 *__restrict__ binned, const unsigned *__
 // Same reduction, compact output (see tile_body).
 template <bool kPy>
 __global__ void __launch_bounds__(kTileThreads)
-tile_compact_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
-                    ViewParams p, const float *__restrict__ lut, int total_tiles, unsigned *__restrict__ compact,
-                    unsigned compact_cap)
+tile_compact_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
+                  const __grid_constant__ FrameOffsets offs,
+                    const __grid_constant__ ViewParams p, const float *__restrict__ lut, int total_tiles,
+                    unsigned *__restrict__ compact, unsigned compact_cap)
 {
     tile_body<true, false, kPy>(binned, tile_off, offs, p, lut, nullptr, total_tiles, compact, compact_cap);
 }
@@ -891,6 +925,13 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
         kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total, *sink);
     } else {
         auto kernel = p.py ? tile_build_kernel<true> : tile_build_kernel<false>;
+        if (!p.py && p.store_mode != kStoreTmaHint) {  // experiment knob (MV3D_TILE_STORE), C-routine semantics only
+            kernel = p.store_mode == kStoreTma ? tile_build_kernel<false, kStoreTma>
+                   : p.store_mode == kStoreTmaSplit ? tile_build_kernel<false, kStoreTmaSplit>
+                   : p.store_mode == kStoreLsu ? tile_build_kernel<false, kStoreLsu>
+                                               : tile_build_kernel<false, kStoreLsuStream>;
+            cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(p));
+        }
         kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
     }
     return 1;

@@ -87,6 +87,11 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     const char *fa = getenv("MV3D_FILL_CTAS");
     ctx->fill_ctas = fa ? atoi(fa) : 2;
     if (ctx->fill_ctas < 1) ctx->fill_ctas = 1;
+    if (const char *ts = getenv("MV3D_TILE_STORE")) {
+        const char *names[] = {"tma", "tma_hint", "tma_split", "lsu", "lsu_cs"};
+        for (int i = 0; i < 5; i++)
+            if (strcmp(ts, names[i]) == 0) ctx->tile_store = i;
+    }
     const char *fs = getenv("MV3D_FRONT_ASIDE");
     ctx->front_aside = fs ? atoi(fs) : 1;
     const char *ao = getenv("MV3D_ATOMIC_OVERLAP");
@@ -298,6 +303,7 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
     p.tile_cells = pick_tile_cells(strategy == MV3D_STRATEGY_PATCH ? ctx->patch_tile_bytes : ctx->tile_bytes_target,
                                    p.planes, cells);
     p.tiles_per_frame = (int)((cells + p.tile_cells - 1) / p.tile_cells);
+    p.store_mode = ctx->tile_store;
     p.z_span = tp->z_max - tp->z_min;  // float subtraction, LidarTopAndFrontPreprocess.c:185
     if (want_front) {
         if (!fp) return fail("front parameters are required when a front view is requested");
@@ -825,6 +831,7 @@ static int make_py_params(const mv3d_ctx *ctx, const mv3d_pytwin_params *pp, boo
     p.top_frame_floats = cells * p.planes;
     p.tile_cells = pick_tile_cells(ctx->tile_bytes_target, p.planes, cells);
     p.tiles_per_frame = cells ? (int)((cells + p.tile_cells - 1) / p.tile_cells) : 0;
+    p.store_mode = ctx->tile_store;
     PyFrontParams f;
     memset(&f, 0, sizeof(f));
     f.ang_res = pp->ang_res; f.vert_res = pp->vert_res; f.velodyne_height = pp->velodyne_height;

@@ -26,6 +26,7 @@ struct ViewParams {
     long long top_frame_floats;   // xn*yn*planes
     // output tiling (tile strategy): a tile is tile_cells consecutive output cells = one contiguous chunk
     int tile_cells, tiles_per_frame;
+    int store_mode;               // how the tile kernel writes a tile: see TileStore in encode_kernels.cu
     // front view
     float z_span;                 // z_MAX - z_MIN, rounded to float [TF:185]
     float rad_to_deg;             // (float)(180/3.141596) [TF:36]
