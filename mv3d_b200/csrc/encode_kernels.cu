@@ -86,11 +86,20 @@ __device__ __forceinline__ void bulk_wait_read_all()
 // How the tile kernel writes a finished tile (ViewParams::store_mode; MV3D_TILE_STORE=tma|tma_hint|tma_split|lsu|lsu_cs).
 // Default: bulk stores with an L2 evict-first policy -- the output is written once and never read back here, so it
 // should not push the bin records (read by this same kernel) out of L2. Measured in profiles/strategy_experiments_r1.md.
-enum TileStore { kStoreTma = 0, kStoreTmaHint = 1, kStoreTmaSplit = 2, kStoreLsu = 3, kStoreLsuStream = 4 };
+enum TileStore { kStoreTma = 0, kStoreTmaHint = 1, kStoreTmaSplit = 2, kStoreLsu = 3, kStoreLsuStream = 4, kStoreTmaPaced = 5 };
 __device__ __forceinline__ void tile_bulk_store(void *gdst, const void *ssrc, uint32_t bytes, int mode)
 {
     if (mode == kStoreTmaHint) {
         bulk_store_hint(gdst, ssrc, bytes, l2_policy_evict_first());
+    } else if (mode == kStoreTmaPaced) {  // four bulk operations, each waited for: at most a quarter tile in flight
+        const uint32_t quarter = ((bytes >> 2) + 15u) & ~15u;
+        const uint64_t pol = l2_policy_evict_first();
+        for (uint32_t off = 0; off < bytes; off += quarter) {
+            bulk_store_hint(static_cast<char *>(gdst) + off, static_cast<const char *>(ssrc) + off,
+                            min(quarter, bytes - off), pol);
+            bulk_commit();
+            bulk_wait_read_all();
+        }
     } else if (mode == kStoreTmaSplit) {  // four bulk operations per tile instead of one
         const uint32_t quarter = ((bytes >> 2) + 15u) & ~15u;
         for (uint32_t off = 0; off < bytes; off += quarter)
@@ -109,10 +118,12 @@ __device__ __forceinline__ void store_zero16(float4 *p)
 //   keys[g] = {output cell, rank inside its tile's bin}  ({kInvalidKey, 0} when the point is rejected)
 // grid = (blocks, batch); each CTA strides over one sweep's points with coalesced 16-byte loads.
 // ------------------------------------------------------------------------------------------------
+constexpr int kPointItems = 4;  // points per thread and round: their loads and atomics are in flight together
 template <bool kPy>
 __global__ void __launch_bounds__(kPointThreads)
-classify_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
-                uint2 *__restrict__ keys, unsigned *__restrict__ tile_count, unsigned *__restrict__ fv_winner)
+classify_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets offs,
+                const __grid_constant__ ViewParams p, uint2 *__restrict__ keys, unsigned *__restrict__ tile_count,
+                unsigned *__restrict__ fv_winner)
 {
     const int f = blockIdx.y;
     const int base = offs.off[f];
@@ -121,35 +132,57 @@ classify_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
     unsigned *counts = tile_count + (size_t)f * (p.tiles_per_frame + 1);
     unsigned *winners = fv_winner + (size_t)f * p.front_pixels;
 
-    // warp-uniform trip count so the match/shuffle below is convergent
+    // warp-uniform trip count so the match/shuffle below is convergent; a round covers kPointItems consecutive
+    // chunks of gridDim.x * blockDim.x points, so every load stays coalesced
     const int stride = gridDim.x * blockDim.x;
     const int first = blockIdx.x * blockDim.x + threadIdx.x;
     const int warp_first = first - (int)lane;
-    for (int i0 = warp_first; i0 < n; i0 += stride) {
-        const int i = i0 + (int)lane;
-        uint32_t cell = kInvalidKey;
-        uint32_t tile = kInvalidKey;
-        if (i < n) {
-            const float4 pt = load_point(pts + base + i);
-            const CellHit c = classify_as<kPy>(pt, p);
-            if (c.keep) {
-                cell = c.cell;
-                if (!kPy && p.want_front) {
-                    const int pix = front_pixel(pt, p);
-                    if (pix >= 0) atomicMax(winners + pix, (unsigned)i + 1u);
+    for (int i0 = warp_first; i0 < n; i0 += stride * kPointItems) {
+        float4 pt[kPointItems];
+        int idx[kPointItems];
+#pragma unroll
+        for (int k = 0; k < kPointItems; k++) {
+            idx[k] = i0 + k * stride + (int)lane;
+            if (idx[k] < n) pt[k] = load_point(pts + base + idx[k]);
+        }
+        uint32_t cell[kPointItems], tile[kPointItems];
+#pragma unroll
+        for (int k = 0; k < kPointItems; k++) {
+            cell[k] = kInvalidKey;
+            tile[k] = kInvalidKey;
+            if (idx[k] < n) {
+                const CellHit c = classify_as<kPy>(pt[k], p);
+                if (c.keep) {
+                    cell[k] = c.cell;
+                    if (!kPy && p.want_front) {
+                        const int pix = front_pixel(pt[k], p);
+                        if (pix >= 0) atomicMax(winners + pix, (unsigned)idx[k] + 1u);
+                    }
                 }
             }
+            if (cell[k] != kInvalidKey) tile[k] = cell[k] / (uint32_t)p.tile_cells;
         }
         if (p.want_top) {
-            if (cell != kInvalidKey) tile = cell / (uint32_t)p.tile_cells;
-            // Warp-aggregated histogram: lanes that hit the same tile share one atomicAdd.
-            const unsigned peers = __match_any_sync(0xFFFFFFFFu, tile);
-            const int leader = __ffs(peers) - 1;
-            unsigned rank = 0;
-            if (tile != kInvalidKey && (int)lane == leader) rank = atomicAdd(counts + tile, (unsigned)__popc(peers));
-            rank = __shfl_sync(0xFFFFFFFFu, rank, leader);
-            rank += (unsigned)__popc(peers & ((1u << lane) - 1u));
-            if (i < n) keys[base + i] = make_uint2(cell, rank);
+            // Warp-aggregated histogram: lanes that hit the same tile share one atomicAdd. All the atomics of a round
+            // are issued before the first result is consumed.
+            unsigned peers[kPointItems], rank[kPointItems];
+            int leader[kPointItems];
+#pragma unroll
+            for (int k = 0; k < kPointItems; k++) {
+                if (i0 + k * stride >= n) { peers[k] = 0u; leader[k] = 0; rank[k] = 0u; continue; }  // warp-uniform
+                peers[k] = __match_any_sync(0xFFFFFFFFu, tile[k]);
+                leader[k] = __ffs(peers[k]) - 1;
+                rank[k] = 0;
+                if (tile[k] != kInvalidKey && (int)lane == leader[k])
+                    rank[k] = atomicAdd(counts + tile[k], (unsigned)__popc(peers[k]));
+            }
+#pragma unroll
+            for (int k = 0; k < kPointItems; k++) {
+                if (i0 + k * stride >= n) continue;
+                unsigned r = __shfl_sync(0xFFFFFFFFu, rank[k], leader[k]);
+                r += (unsigned)__popc(peers[k] & ((1u << lane) - 1u));
+                if (idx[k] < n) keys[base + idx[k]] = make_uint2(cell[k], r);
+            }
         }
     }
 }
@@ -221,33 +254,52 @@ tile_scan_kernel(unsigned *__restrict__ tile_count, unsigned *__restrict__ tile_
 // ------------------------------------------------------------------------------------------------
 template <bool kPy>
 __global__ void __launch_bounds__(kPointThreads)
-bin_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
-           const uint2 *__restrict__ keys, const unsigned *__restrict__ tile_off, uint4 *__restrict__ binned)
+bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets offs,
+           const __grid_constant__ ViewParams p, const uint2 *__restrict__ keys,
+           const unsigned *__restrict__ tile_off, uint4 *__restrict__ binned)
 {
     const int f = blockIdx.y;
     const int base = offs.off[f];
     const int n = offs.off[f + 1] - base;
     const unsigned *off = tile_off + (size_t)f * (p.tiles_per_frame + 1);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint2 k = keys[base + i];
-        if (k.x == kInvalidKey) continue;
-        const float4 pt = load_point(pts + base + i);
-        const uint32_t tile = k.x / (uint32_t)p.tile_cells;
-        const uint32_t local = k.x - tile * (uint32_t)p.tile_cells;
-        uint32_t zfield;
-        float key;
-        if (kPy) {
-            // Python twin: key = qz; slice field = floor(qz) (kNoSlice when it is past the last slice, such a point
-            // still counts and can win the intensity), top bit = "also closes the slice below"
-            const CellHit c = py_classify(pt, p);
-            key = c.h;
-            zfield = (c.slice < p.zn ? (uint32_t)c.slice : kNoSlice) | ((c.lower && c.slice <= p.zn) ? kLowerFlag : 0u);
-        } else {
-            zfield = (uint32_t)quantise(pt.z, p.z_min, p.z_div, p.quant_floor);
-            key = __fsub_rn(pt.z, p.z_min);
+    const int stride = gridDim.x * blockDim.x;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * kPointItems) {
+        uint2 k[kPointItems];
+        float4 pt[kPointItems];
+        unsigned start[kPointItems];
+#pragma unroll
+        for (int j = 0; j < kPointItems; j++) {  // key and point of every item first: independent loads
+            const int i = i0 + j * stride;
+            k[j] = make_uint2(kInvalidKey, 0u);
+            if (i < n) {
+                k[j] = keys[base + i];
+                pt[j] = load_point(pts + base + i);
+            }
         }
-        binned[(size_t)base + off[tile] + k.y] =
-            make_uint4(local | (zfield << 16), __float_as_uint(key), (uint32_t)i, __float_as_uint(pt.w));
+#pragma unroll
+        for (int j = 0; j < kPointItems; j++)
+            start[j] = k[j].x != kInvalidKey ? __ldg(off + k[j].x / (uint32_t)p.tile_cells) : 0u;
+#pragma unroll
+        for (int j = 0; j < kPointItems; j++) {
+            if (k[j].x == kInvalidKey) continue;
+            const int i = i0 + j * stride;
+            const uint32_t tile = k[j].x / (uint32_t)p.tile_cells;
+            const uint32_t local = k[j].x - tile * (uint32_t)p.tile_cells;
+            uint32_t zfield;
+            float key;
+            if (kPy) {
+                // Python twin: key = qz; slice field = floor(qz) (kNoSlice when it is past the last slice, such a
+                // point still counts and can win the intensity), top bit = "also closes the slice below"
+                const CellHit c = py_classify(pt[j], p);
+                key = c.h;
+                zfield = (c.slice < p.zn ? (uint32_t)c.slice : kNoSlice) | ((c.lower && c.slice <= p.zn) ? kLowerFlag : 0u);
+            } else {
+                zfield = (uint32_t)quantise(pt[j].z, p.z_min, p.z_div, p.quant_floor);
+                key = __fsub_rn(pt[j].z, p.z_min);
+            }
+            binned[(size_t)base + start[j] + k[j].y] =
+                make_uint4(local | (zfield << 16), __float_as_uint(key), (uint32_t)i, __float_as_uint(pt[j].w));
+        }
     }
 }
 
@@ -866,9 +918,9 @@ point_keys_kernel(const float4 *__restrict__ pts, int n, ViewParams p, int *__re
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
-static inline int point_blocks(int max_points)
+static inline int point_blocks(int max_points, int items = 1)
 {
-    int b = (max_points + kPointThreads - 1) / kPointThreads;
+    int b = (max_points + kPointThreads * items - 1) / (kPointThreads * items);
     return b < 1 ? 1 : (b > 4096 ? 4096 : b);
 }
 
@@ -890,7 +942,7 @@ cudaError_t tile_build_configure(const ViewParams &p, int *blocks_per_sm)
 int launch_classify(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
                     uint2 *keys, unsigned *tile_count, unsigned *fv_winner, cudaStream_t s)
 {
-    dim3 grid(point_blocks(max_points), batch);
+    dim3 grid(point_blocks(max_points, kPointItems), batch);
     auto kernel = p.py ? classify_kernel<true> : classify_kernel<false>;
     kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_count, fv_winner);
     return 1;
@@ -908,7 +960,7 @@ int launch_tile_scan(unsigned *tile_count, unsigned *tile_off, int tiles_per_fra
 int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
                const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s)
 {
-    dim3 grid(point_blocks(max_points), batch);
+    dim3 grid(point_blocks(max_points, kPointItems), batch);
     auto kernel = p.py ? bin_kernel<true> : bin_kernel<false>;
     kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_off, binned);
     return 1;
@@ -928,6 +980,7 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
         if (!p.py && p.store_mode != kStoreTmaHint) {  // experiment knob (MV3D_TILE_STORE), C-routine semantics only
             kernel = p.store_mode == kStoreTma ? tile_build_kernel<false, kStoreTma>
                    : p.store_mode == kStoreTmaSplit ? tile_build_kernel<false, kStoreTmaSplit>
+                   : p.store_mode == kStoreTmaPaced ? tile_build_kernel<false, kStoreTmaPaced>
                    : p.store_mode == kStoreLsu ? tile_build_kernel<false, kStoreLsu>
                                                : tile_build_kernel<false, kStoreLsuStream>;
             cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(p));

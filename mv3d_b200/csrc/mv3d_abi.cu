@@ -88,8 +88,8 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     ctx->fill_ctas = fa ? atoi(fa) : 2;
     if (ctx->fill_ctas < 1) ctx->fill_ctas = 1;
     if (const char *ts = getenv("MV3D_TILE_STORE")) {
-        const char *names[] = {"tma", "tma_hint", "tma_split", "lsu", "lsu_cs"};
-        for (int i = 0; i < 5; i++)
+        const char *names[] = {"tma", "tma_hint", "tma_split", "lsu", "lsu_cs", "tma_paced"};
+        for (int i = 0; i < 6; i++)
             if (strcmp(ts, names[i]) == 0) ctx->tile_store = i;
     }
     const char *fs = getenv("MV3D_FRONT_ASIDE");
