@@ -45,6 +45,7 @@ def parse_args():
     ap.add_argument("--strategy", default="auto", choices=["auto", "tile", "patch", "atomic"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
+    ap.add_argument("--no-also", action="store_true", help="skip the short legs for the widened rows (profiling runs)")
     return ap.parse_args()
 
 
@@ -178,6 +179,47 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------------
+# short legs for the rows built around the path (not the headline metric; device-resident, same 64 sweeps)
+# ------------------------------------------------------------------------------------------------------
+def widened_rows(d_pts, offs, device, steps):
+    import torch
+    from mv3d_b200.anchors import AnchorFilter, make_anchors
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.params import PYTWIN_KITTI, REFERENCE_KITTI_TOP
+    from mv3d_b200.pytwin import PyTwinEncoder
+
+    def rate(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return BATCH * steps / (e0.elapsed_time(e1) * 1e-3)
+
+    out = {"unit": "sweeps/s", "steps": steps, "batch": BATCH}
+    py = PyTwinEncoder(device)
+    top = torch.empty((BATCH, *PYTWIN_KITTI.top_shape), dtype=torch.float32, device=d_pts.device)
+    front = torch.empty((BATCH, *PYTWIN_KITTI.front_shape), dtype=torch.float32, device=d_pts.device)
+    out["python_twin_encode"] = {"value": rate(lambda: py.encode_device(d_pts, offs, PYTWIN_KITTI, top_out=top, front_out=front)),
+                                 "what": "lidar_to_top + lidar_to_front_fast semantics, BEV 800x600x27 + FV 1500x100x3"}
+    py.close()
+    del front
+    enc = ViewEncoder(device, semantics="top")
+    filt = AnchorFilter(enc, anchors=make_anchors(REFERENCE_KITTI_TOP.shape[:2], stride=8))
+    out["encode_and_filter_fused"] = {
+        "value": rate(lambda: filt.encode_and_filter(d_pts, offs, REFERENCE_KITTI_TOP, top_out=top)),
+        "what": "createTopMaps (BEV 800x600x27) + remove_empty_anchor over 30000 anchors, one call, nothing leaves the device"}
+    out["filter_resident_views"] = {"value": rate(lambda: filt.filter_device(top)), "unit": "frames/s",
+                                    "what": "remove_empty_anchor alone on 64 resident views"}
+    enc.close()
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------
 # our arm
 # ------------------------------------------------------------------------------------------------------
 def run_ours(args):
@@ -282,6 +324,11 @@ def run_ours(args):
                "ms_per_step": e2e_s / args.steps * 1e3, "api": "mv3d_encode_batch_host (pinned host buffers)",
                "result_checksum": checksum}
 
+    # ---- also (N=1 only, outside the timed region above): the rows built around the path, SURVEY.md 8(f) -------
+    also = None
+    if world == 1 and not args.no_also:
+        also = widened_rows(d_pts, offs, local_rank, max(3, min(args.steps, 10)))
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -321,6 +368,8 @@ def run_ours(args):
     }
     if cpu is not None:
         line["cpu_baseline"] = cpu
+    if also is not None:
+        line["also"] = also
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
