@@ -25,7 +25,9 @@ KEYS = [
 
 
 def short(name):
-    return name.split("(")[0]
+    """'void tile_build_kernel<0, 1>(const uint4 *, ...)' -> 'tile_build_kernel' (the name mv3d_kernel_name reports)."""
+    name = name.split("(")[0].split("<")[0].strip()
+    return name[5:] if name.startswith("void ") else name
 
 
 def launches(path, out):
