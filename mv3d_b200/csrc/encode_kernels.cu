@@ -498,7 +498,9 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 for (unsigned w = tid; w <= w_last - w_first; w += kTileThreads) {
                     const unsigned bits = occ_tile[w];
                     if (bits) {
-                        if (w == 0 || w == w_last - w_first) atomicOr(out + w, bits);
+                        // a tile of a multiple of 32 cells owns all its words; otherwise its first and last word
+                        // are shared with the neighbouring tiles
+                        if ((T & 31) != 0 && (w == 0 || w == w_last - w_first)) atomicOr(out + w, bits);
                         else out[w] = bits;
                         occ_tile[w] = 0u;
                     }

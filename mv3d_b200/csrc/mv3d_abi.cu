@@ -943,6 +943,27 @@ extern "C" int mv3d_pytwin_encode_batch_dev(mv3d_ctx *ctx, const float *points_d
 // builds the view, so the filter never reads the view. Falls back to encode, then the stand-alone filter, whenever
 // the occupancy map cannot decide (limit != 0, exact mode) or the strategy in use is not the tile strategy.
 // ------------------------------------------------------------------------------------------------
+// The fused encode + filter reports occupancy bits per tile: with a tile of a multiple of 32 cells every word of the
+// bit map belongs to exactly one tile (plain stores, no atomics into a map the store stream keeps evicting from L2).
+static void align_tiles_to_words(const mv3d_ctx *ctx, ViewParams *p)
+{
+    const long long cells = (long long)p->xn * p->yn;
+    const int t = p->tile_cells;
+    if (cells <= 0 || (t & 31) == 0) return;
+    auto resident = [&](int tile_cells) {  // CTAs of the tile kernel an SM can hold with this tile size
+        ViewParams q = *p;
+        q.tile_cells = tile_cells;
+        const size_t bytes = tile_smem_bytes(q);
+        return bytes <= ctx->smem_optin ? (int)(ctx->smem_per_sm / (bytes + 1024)) : 0;
+    };
+    const int up = (t + 31) & ~31, down = t & ~31;
+    int pick = t;
+    if (up <= 65504 && resident(up) > 0 && resident(up) >= resident(t)) pick = up;  // same residency: take the larger
+    else if (down >= 32) pick = down;
+    p->tile_cells = pick;
+    p->tiles_per_frame = (int)((cells + pick - 1) / pick);
+}
+
 static int check_filter_args(const char *who, mv3d_ctx *ctx, int batch, float *top_dev, int mode, int *keep_dev,
                              int *count_dev)
 {
@@ -973,6 +994,7 @@ extern "C" int mv3d_encode_filter_batch_dev(mv3d_ctx *ctx, const float *points_d
     AnchorPlan plan;
     OccupancySink sink;
     const bool fused = strat == MV3D_STRATEGY_TILE && ctx->anchors.n > 0;
+    if (fused && !(limit != 0.0f) && mode == MV3D_ANCHORS_AUTO) align_tiles_to_words(ctx, &p);
     if (anchor_plan_locked(ctx, batch, p.xn, p.yn, p.planes, limit, mode, false, s, &plan, fused ? &sink : nullptr))
         return -1;
     const bool have = fused && sink.words != nullptr;
@@ -1002,6 +1024,7 @@ extern "C" int mv3d_pytwin_encode_filter_batch_dev(mv3d_ctx *ctx, const float *p
     AnchorPlan plan;
     OccupancySink sink;
     const bool fused = ctx->anchors.n > 0;  // the Python-twin mode always runs the tile strategy
+    if (fused && !(limit != 0.0f) && mode == MV3D_ANCHORS_AUTO) align_tiles_to_words(ctx, &p);
     if (anchor_plan_locked(ctx, batch, p.xn, p.yn, p.planes, limit, mode, false, s, &plan, fused ? &sink : nullptr))
         return -1;
     const bool have = fused && sink.words != nullptr;
