@@ -41,7 +41,8 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
     """Compile csrc/*.cu into mv3d_b200/libmv3d_encode.so for sm_100a (nvcc cross-compiles without a GPU)."""
     if not force and not _stale():
         return LIB_PATH
-    cmd = [_nvcc(), *NVCC_FLAGS, "-o", LIB_PATH] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lz"]
+    extra = os.environ.get("MV3D_NVCC_EXTRA", "").split()  # tuning experiments, e.g. -DMV3D_POINT_ITEMS=2
+    cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-o", LIB_PATH] + [os.path.join(CSRC, s) for s in SOURCES] + ["-lz"]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
     res = subprocess.run(cmd, capture_output=True, text=True)

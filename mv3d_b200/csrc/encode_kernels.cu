@@ -118,7 +118,10 @@ __device__ __forceinline__ void store_zero16(float4 *p)
 //   keys[g] = {output cell, rank inside its tile's bin}  ({kInvalidKey, 0} when the point is rejected)
 // grid = (blocks, batch); each CTA strides over one sweep's points with coalesced 16-byte loads.
 // ------------------------------------------------------------------------------------------------
-constexpr int kPointItems = 4;  // points per thread and round: their loads and atomics are in flight together
+#ifndef MV3D_POINT_ITEMS
+#define MV3D_POINT_ITEMS 2
+#endif
+constexpr int kPointItems = MV3D_POINT_ITEMS;  // points per thread and round: their loads and atomics are in flight together
 template <bool kPy>
 __global__ void __launch_bounds__(kPointThreads)
 classify_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets offs,
@@ -160,7 +163,7 @@ classify_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOff
                     }
                 }
             }
-            if (cell[k] != kInvalidKey) tile[k] = cell[k] / (uint32_t)p.tile_cells;
+            if (cell[k] != kInvalidKey) tile[k] = tile_of(cell[k], p);
         }
         if (p.want_top) {
             // Warp-aggregated histogram: lanes that hit the same tile share one atomicAdd. All the atomics of a round
@@ -278,12 +281,12 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
         }
 #pragma unroll
         for (int j = 0; j < kPointItems; j++)
-            start[j] = k[j].x != kInvalidKey ? __ldg(off + k[j].x / (uint32_t)p.tile_cells) : 0u;
+            start[j] = k[j].x != kInvalidKey ? __ldg(off + tile_of(k[j].x, p)) : 0u;
 #pragma unroll
         for (int j = 0; j < kPointItems; j++) {
             if (k[j].x == kInvalidKey) continue;
             const int i = i0 + j * stride;
-            const uint32_t tile = k[j].x / (uint32_t)p.tile_cells;
+            const uint32_t tile = tile_of(k[j].x, p);
             const uint32_t local = k[j].x - tile * (uint32_t)p.tile_cells;
             uint32_t zfield;
             float key;

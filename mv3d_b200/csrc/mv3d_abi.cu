@@ -304,6 +304,7 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
                                    p.planes, cells);
     p.tiles_per_frame = (int)((cells + p.tile_cells - 1) / p.tile_cells);
     p.store_mode = ctx->tile_store;
+    p.tile_magic = tile_magic_for(p.tile_cells);
     p.z_span = tp->z_max - tp->z_min;  // float subtraction, LidarTopAndFrontPreprocess.c:185
     if (want_front) {
         if (!fp) return fail("front parameters are required when a front view is requested");
@@ -832,6 +833,7 @@ static int make_py_params(const mv3d_ctx *ctx, const mv3d_pytwin_params *pp, boo
     p.tile_cells = pick_tile_cells(ctx->tile_bytes_target, p.planes, cells);
     p.tiles_per_frame = cells ? (int)((cells + p.tile_cells - 1) / p.tile_cells) : 0;
     p.store_mode = ctx->tile_store;
+    p.tile_magic = tile_magic_for(p.tile_cells);
     PyFrontParams f;
     memset(&f, 0, sizeof(f));
     f.ang_res = pp->ang_res; f.vert_res = pp->vert_res; f.velodyne_height = pp->velodyne_height;
@@ -961,6 +963,7 @@ static void align_tiles_to_words(const mv3d_ctx *ctx, ViewParams *p)
     if (up <= 65504 && resident(up) > 0 && resident(up) >= resident(t)) pick = up;  // same residency: take the larger
     else if (down >= 32) pick = down;
     p->tile_cells = pick;
+    p->tile_magic = tile_magic_for(pick);
     p->tiles_per_frame = (int)((cells + pick - 1) / pick);
 }
 

@@ -26,6 +26,7 @@ struct ViewParams {
     long long top_frame_floats;   // xn*yn*planes
     // output tiling (tile strategy): a tile is tile_cells consecutive output cells = one contiguous chunk
     int tile_cells, tiles_per_frame;
+    unsigned long long tile_magic; // ceil(2^48 / tile_cells) << 16: cell / tile_cells == umul64hi(cell, tile_magic), see tile_of()
     int store_mode;               // how the tile kernel writes a tile: see TileStore in encode_kernels.cu
     // front view
     float z_span;                 // z_MAX - z_MIN, rounded to float [TF:185]
@@ -37,6 +38,18 @@ struct ViewParams {
     int front_pixels;             // rn*cn
     long long front_frame_floats; // rn*cn*fn
 };
+
+// Tile of an output cell without an integer division: for cell < 2^31 and tile_cells < 2^16,
+// floor(cell * ceil(2^48 / d) / 2^48) == cell / d (the error term cell * d / 2^48 stays below 1 / d).
+__host__ __device__ inline unsigned long long tile_magic_for(int tile_cells)
+{
+    const unsigned long long d = (unsigned long long)(tile_cells > 0 ? tile_cells : 1);
+    return (((1ull << 48) + d - 1) / d) << 16;
+}
+__device__ __forceinline__ uint32_t tile_of(uint32_t cell, const ViewParams &p)
+{
+    return (uint32_t)__umul64hi((unsigned long long)cell, p.tile_magic);
+}
 
 constexpr int kMaxBatchPerLaunch = 64;
 struct FrameOffsets {            // first point of each sweep in the packed point array
