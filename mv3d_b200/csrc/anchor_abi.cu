@@ -51,6 +51,7 @@ int anchor_plan_locked(mv3d_ctx *ctx, int frames, int xn, int yn, int planes, fl
     g.planes = planes;
     g.cells = (unsigned)xn * (unsigned)yn;
     g.words = (g.cells + 31u) / 32u;
+    g.wpr = ((unsigned)yn + 31u) / 32u;
     g.n = st.n;
     g.chunks = (unsigned)((st.n + kAnchorChunk - 1) / kAnchorChunk);
     g.max_lines = MV3D_ANCHOR_MAX_LINES;
@@ -71,6 +72,10 @@ int anchor_plan_locked(mv3d_ctx *ctx, int frames, int xn, int yn, int planes, fl
     if (!plan->exact_all) {
         if (ensure(st.occupancy, (size_t)frames * g.words * sizeof(unsigned), false, s)) return -1;
         plan->occupancy = static_cast<unsigned *>(st.occupancy.ptr);
+        const size_t row_words = (size_t)frames * xn * g.wpr, group_words = (size_t)frames * ((xn + 7) / 8) * g.wpr;
+        if (ensure(st.rows, (row_words + group_words) * sizeof(unsigned), false, s)) return -1;
+        plan->rows = static_cast<unsigned *>(st.rows.ptr);
+        plan->groups = plan->rows + row_words;
         if (sink) {
             CUDA_TRY(cudaMemsetAsync(plan->occupancy, 0, (size_t)frames * g.words * sizeof(unsigned), s));
             sink->words = plan->occupancy;
@@ -101,7 +106,8 @@ int anchor_run_locked(mv3d_ctx *ctx, const AnchorPlan &plan, const float *views_
                 return launch_anchor_occupancy(views_dev, g, frames, plan.occupancy, plan.flags, ctx->sm_count, s);
             });
         timed_launch(ctx, K_ANCHOR_TEST, s, [&] {
-            return launch_anchor_test(boxes, g, frames, plan.occupancy, plan.flags, plan.keep, plan.chunk_count, s);
+            return launch_anchor_test(boxes, g, frames, plan.occupancy, plan.flags, plan.rows, plan.groups, plan.keep,
+                                      plan.chunk_count, s);
         });
     }
     // In AUTO mode this launch exits at once for every frame the occupancy map could decide (the usual case).

@@ -9,7 +9,9 @@
 //                            one bit per cell "holds a non-zero value", and a per-frame flag "holds a negative
 //                            value, a -0 or a NaN". Without the flag every value is >= +0, float32 sums of such
 //                            values are monotone, and "total > 0" is exactly "some cell of the box has its bit set".
-//   anchor_test_kernel       thread per anchor: ORs the bit ranges of the box's rows (<= 50 rows, 1-3 words each).
+//   anchor_rows_kernel       the bit map re-laid row by row (word-aligned rows) plus its OR over groups of 8 rows
+//   anchor_test_kernel       thread per anchor: ORs the column range of the box over its rows, 8 rows at a time where
+//                            a whole group lies inside (<= 50 rows -> <= 20 probes of 1-3 words).
 //   anchor_sum_kernel        frames with the flag, limit != 0, or totals requested: warp per anchor, lane per
 //                            channel, the float32 sums in the reference's order (row left to right, rows ascending,
 //                            numpy's pairwise sum over the channels), read through L2 (a 52 MB view fits it).
@@ -109,8 +111,38 @@ __device__ __forceinline__ Box clamp_box(int4 b, int xn, int yn, int max_lines)
     return r;
 }
 
+// Row-aligned copy of the occupancy map, and its OR over groups of 8 rows. The map is laid out over the flattened
+// cell index (that is how the view is stored and how tiles cut it), so a row of the view starts at an arbitrary bit;
+// here row x starts at word x * wpr, which makes the column masks of a box the same for all of its rows and lets the
+// test take 8 rows at a time.  thread = (group of 8 rows, word column).
+__global__ void __launch_bounds__(256) anchor_rows_kernel(AnchorGeometry g, const unsigned *__restrict__ occupancy,
+                                                          const unsigned *__restrict__ flags,
+                                                          unsigned *__restrict__ rows, unsigned *__restrict__ groups)
+{
+    const unsigned frame = blockIdx.y;
+    if (flags[frame] != 0u) return;
+    const unsigned wpr = g.wpr, ngroups = (unsigned)(g.xn + 7) >> 3;
+    const unsigned item = blockIdx.x * blockDim.x + threadIdx.x;
+    if (item >= ngroups * wpr) return;
+    const unsigned grp = item / wpr, w = item - grp * wpr;
+    const unsigned *occ = occupancy + (size_t)frame * g.words;
+    const unsigned nbits = min(32u, (unsigned)g.yn - 32u * w);
+    const unsigned keep = nbits == 32u ? kFull : ((1u << nbits) - 1u);
+    unsigned any = 0;
+    for (unsigned x = grp * 8u; x < min(grp * 8u + 8u, (unsigned)g.xn); x++) {
+        const unsigned b = x * (unsigned)g.yn + 32u * w;
+        const unsigned i = b >> 5;
+        const unsigned lo = __ldg(occ + i), hi = (i + 1 < g.words) ? __ldg(occ + i + 1) : 0u;
+        const unsigned word = __funnelshift_r(lo, hi, b & 31u) & keep;
+        rows[((size_t)frame * g.xn + x) * wpr + w] = word;
+        any |= word;
+    }
+    groups[((size_t)frame * ngroups + grp) * wpr + w] = any;
+}
+
 __global__ void __launch_bounds__(kAnchorChunk) anchor_test_kernel(const int4 *__restrict__ boxes, AnchorGeometry g,
-                                                                   const unsigned *__restrict__ occupancy,
+                                                                   const unsigned *__restrict__ rows,
+                                                                   const unsigned *__restrict__ groups,
                                                                    const unsigned *__restrict__ flags,
                                                                    unsigned char *__restrict__ keep,
                                                                    unsigned *__restrict__ chunk_count)
@@ -122,21 +154,27 @@ __global__ void __launch_bounds__(kAnchorChunk) anchor_test_kernel(const int4 *_
     if (a < g.n) {
         const Box b = clamp_box(boxes[a], g.xn, g.yn, g.max_lines);
         if (b.lines > 0 && b.len > 0) {
-            const unsigned *occ = occupancy + (size_t)frame * g.words;
-            for (int line = 0; line < b.lines && !hit; line++) {
-                const unsigned b0 = (unsigned)(b.x1 + line) * (unsigned)g.yn + (unsigned)b.y1;
-                const unsigned b1 = b0 + (unsigned)b.len - 1u;  // last bit of the row
-                const unsigned w0 = b0 >> 5, w1 = b1 >> 5;
-                const unsigned m0 = kFull << (b0 & 31u), m1 = kFull >> (31u - (b1 & 31u));
+            const unsigned wpr = g.wpr;
+            const unsigned y_last = (unsigned)(b.y1 + b.len - 1);
+            const unsigned w0 = (unsigned)b.y1 >> 5, w1 = y_last >> 5;
+            const unsigned m0 = kFull << ((unsigned)b.y1 & 31u), m1 = kFull >> (31u - (y_last & 31u));
+            auto probe = [&](const unsigned *row) {  // any bit of columns [y1, y1 + len) in this row (or 8-row group)?
                 unsigned any;
                 if (w0 == w1) {
-                    any = __ldg(occ + w0) & m0 & m1;
+                    any = __ldg(row + w0) & m0 & m1;
                 } else {
-                    any = (__ldg(occ + w0) & m0) | (__ldg(occ + w1) & m1);
-                    for (unsigned w = w0 + 1; w < w1; w++) any |= __ldg(occ + w);
+                    any = (__ldg(row + w0) & m0) | (__ldg(row + w1) & m1);
+                    for (unsigned w = w0 + 1; w < w1; w++) any |= __ldg(row + w);
                 }
-                hit = any != 0u;
-            }
+                return any != 0u;
+            };
+            const unsigned *frame_rows = rows + (size_t)frame * g.xn * wpr;
+            const unsigned *frame_groups = groups + (size_t)frame * ((unsigned)(g.xn + 7) >> 3) * wpr;
+            int x = b.x1;
+            const int xend = b.x1 + b.lines;
+            while (!hit && x < xend && (x & 7)) hit = probe(frame_rows + (size_t)x++ * wpr);        // up to a group boundary
+            while (!hit && x + 8 <= xend) { hit = probe(frame_groups + (size_t)(x >> 3) * wpr); x += 8; }  // whole groups
+            while (!hit && x < xend) hit = probe(frame_rows + (size_t)x++ * wpr);                    // the rest
         }
         keep[(size_t)frame * g.n + a] = hit ? 1 : 0;
     }
@@ -292,10 +330,13 @@ int launch_anchor_occupancy(const float *views, const AnchorGeometry &g, int fra
 }
 
 int launch_anchor_test(const int4 *boxes, const AnchorGeometry &g, int frames, const unsigned *occupancy,
-                       const unsigned *flags, unsigned char *keep, unsigned *chunk_count, cudaStream_t s)
+                       const unsigned *flags, unsigned *rows, unsigned *groups, unsigned char *keep,
+                       unsigned *chunk_count, cudaStream_t s)
 {
-    anchor_test_kernel<<<dim3(g.chunks, frames), kAnchorChunk, 0, s>>>(boxes, g, occupancy, flags, keep, chunk_count);
-    return 1;
+    const unsigned items = ((unsigned)(g.xn + 7) >> 3) * g.wpr;
+    anchor_rows_kernel<<<dim3((items + 255u) / 256u, frames), 256, 0, s>>>(g, occupancy, flags, rows, groups);
+    anchor_test_kernel<<<dim3(g.chunks, frames), kAnchorChunk, 0, s>>>(boxes, g, rows, groups, flags, keep, chunk_count);
+    return 2;
 }
 
 int launch_anchor_sum(const float *views, const int4 *boxes, const AnchorGeometry &g, int frames, float limit,

@@ -14,6 +14,7 @@ struct AnchorGeometry {
     int xn, yn, planes;
     unsigned cells;            // xn * yn
     unsigned words;            // ceil(cells / 32): occupancy words per frame
+    unsigned wpr;              // ceil(yn / 32): words per row of the row-aligned copy
     unsigned chunks;           // ceil(n / kAnchorChunk)
     int n;                     // anchors
     int max_lines;             // rows of a box that count (50 in the reference)
@@ -23,7 +24,8 @@ struct AnchorGeometry {
 int launch_anchor_occupancy(const float *views, const AnchorGeometry &g, int frames, unsigned *occupancy,
                             unsigned *flags, int sm_count, cudaStream_t s);
 int launch_anchor_test(const int4 *boxes, const AnchorGeometry &g, int frames, const unsigned *occupancy,
-                       const unsigned *flags, unsigned char *keep, unsigned *chunk_count, cudaStream_t s);
+                       const unsigned *flags, unsigned *rows, unsigned *groups, unsigned char *keep,
+                       unsigned *chunk_count, cudaStream_t s);
 int launch_anchor_sum(const float *views, const int4 *boxes, const AnchorGeometry &g, int frames, float limit,
                       const unsigned *flags, bool always, unsigned char *keep, unsigned *chunk_count, float *totals,
                       int sm_count, cudaStream_t s);

@@ -60,6 +60,7 @@ struct AnchorState {
     DeviceBuffer occupancy;   // uint32 [frames][ceil(cells/32)]: bit = cell holds a positive value
     DeviceBuffer flags;       // uint32 [frames]: view holds a negative value, a -0 or a NaN (exact sums needed),
                               // followed by the kept-anchor counts uint32 [frames][ceil(n/1024)]
+    DeviceBuffer rows;        // uint32 [frames][xn][ceil(yn/32)] row-aligned copy of the map, then its 8-row ORs
     DeviceBuffer keep;        // uint8  [frames][n]
     DeviceBuffer view, idx, count;  // staging of the host entry point
 };
@@ -210,7 +211,7 @@ struct AnchorPlan {
     AnchorGeometry g;
     int frames = 0;
     bool exact_all = false;
-    unsigned *flags = nullptr, *chunk_count = nullptr, *occupancy = nullptr;
+    unsigned *flags = nullptr, *chunk_count = nullptr, *occupancy = nullptr, *rows = nullptr, *groups = nullptr;
     unsigned char *keep = nullptr;
 };
 int anchor_check_view(const char *who, int frames, int xn, int yn, int planes);

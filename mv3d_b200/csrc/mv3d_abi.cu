@@ -149,7 +149,7 @@ extern "C" void mv3d_ctx_destroy(mv3d_ctx *ctx)
     release(ctx->ws);
     {
         AnchorState &a = ctx->anchors;
-        release(a.boxes); release(a.occupancy); release(a.flags); release(a.keep);
+        release(a.boxes); release(a.occupancy); release(a.flags); release(a.keep); release(a.rows);
         release(a.view); release(a.idx); release(a.count);
     }
     for (auto &s : ctx->slots) {
