@@ -120,6 +120,10 @@ struct mv3d_ctx {
     int fill_ctas = 0;                    // fill CTAs per SM (one issuing thread each)
     int fill_pending = 0;                 // bulk stores each fill CTA keeps in flight (> 16: unbounded)
     int tile_store = 1;                   // MV3D_TILE_STORE: how the tile kernel writes a tile (1 = bulk stores, evict-first)
+    int pipe_groups = 0;                  // MV3D_TILE_PIPE=G[,threads[,chunk[,pending]]]: pipelined tile kernel (0 = off)
+    int pipe_group_threads = 192;
+    int pipe_chunk = 8640;
+    int pipe_pending = 0;
     int front_aside = 1;                  // TILE: finish the front view on the side stream (MV3D_FRONT_ASIDE=0: in line)
     int atomic_overlap = 0;               // ATOMIC: TMA zero-fill on the side stream, chunked (MV3D_ATOMIC_OVERLAP=1)
     size_t smem_per_sm = 0;

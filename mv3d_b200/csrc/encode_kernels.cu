@@ -559,6 +559,318 @@ tile_compact_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict
 
 
 // ------------------------------------------------------------------------------------------------
+// TILE strategy, pass 4, pipelined form: ONE CTA per SM, G tile images in shared memory, G builder groups and one
+// store warp (MV3D_TILE_PIPE).
+//
+// Why: the bulk-store stream runs fastest when each SM keeps only ~9 KB of it in flight (6.8 TB/s, against 6.2-6.4
+// with whole 36 KB tiles of five independent CTAs in flight: profiles/tma_store_bench_r1.txt). Pacing the store inside
+// tile_build_kernel stalls the CTA that should be building the next tile, so here the two are decoupled: builder
+// group g owns image g and reduces tile (k*G + g)*grid + cta into it; the store warp walks the images in that same
+// order, writes each finished tile in chunks of pipe_chunk bytes with at most pipe_pending chunks unread, and hands
+// the image back. full[g] / empty[g] are mbarriers; a builder re-zeroes the cells its previous tile touched once
+// empty[g] says the store has read them. Same arithmetic, same order-preserving atomics as tile_body.
+// ------------------------------------------------------------------------------------------------
+constexpr int kPipeMaxGroups = 5;  // hardware barriers: 0 = whole CTA, then per group: its own and "empty"
+__device__ __forceinline__ void named_sync(int id, int threads)
+{
+    asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void named_arrive(int id, int threads)
+{
+    asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(threads) : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_addr(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_addr(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_test(uint64_t *bar, unsigned parity)
+{
+    unsigned ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+    return ok != 0u;
+}
+__device__ __forceinline__ void bulk_wait_read_pending(int n)
+{
+    switch (n) {
+    case 0: asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); break;
+    case 1: asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); break;
+    case 2: asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory"); break;
+    case 3: asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory"); break;
+    case 4: asm volatile("cp.async.bulk.wait_group.read 4;" ::: "memory"); break;
+    case 5: asm volatile("cp.async.bulk.wait_group.read 5;" ::: "memory"); break;
+    case 6: asm volatile("cp.async.bulk.wait_group.read 6;" ::: "memory"); break;
+    default: asm volatile("cp.async.bulk.wait_group.read 7;" ::: "memory"); break;
+    }
+}
+
+struct PipeLayout {
+    size_t img_bytes, key_off, dirty_off, occ_off, stride, header;
+};
+__host__ __device__ inline PipeLayout pipe_layout(int tile_cells, int planes)
+{
+    PipeLayout l;
+    l.img_bytes = ((size_t)tile_cells * planes * 4 + 15) & ~(size_t)15;
+    l.key_off = (l.img_bytes + 7) & ~(size_t)7;
+    l.dirty_off = l.key_off + (size_t)tile_cells * 8;
+    l.occ_off = l.dirty_off + (size_t)tile_cells * 4;
+    l.stride = (l.occ_off + ((size_t)tile_cells / 32 + 2) * 4 + 127) & ~(size_t)127;
+    l.header = 256;  // density table (32 floats), cnt[5][2], full[5] mbarriers
+    return l;
+}
+
+template <bool kOccupancy, bool kPy>
+__global__ void __launch_bounds__(1024, 1)
+tile_pipe_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
+                 const __grid_constant__ FrameOffsets offs, const __grid_constant__ ViewParams p,
+                 const float *__restrict__ lut, float *__restrict__ top, int total_tiles, OccupancySink sink)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int T = p.tile_cells, planes = p.planes, zn = p.zn;
+    const int G = p.pipe_groups, gthreads = p.pipe_group_threads;
+    const PipeLayout L = pipe_layout(T, planes);
+    float *slut = reinterpret_cast<float *>(smem_raw);
+    unsigned *cnt = reinterpret_cast<unsigned *>(smem_raw + 128);  // [G][2] touched cells of the current / previous tile
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + 192);  // full[g]: builder group g has finished its tile
+    unsigned char *bufs = smem_raw + L.header;
+    const int tid = threadIdx.x;
+    const int nbuild = G * gthreads;
+    const int hand = gthreads + 32;  // a builder group and the store warp meet on the "full" / "empty" barriers
+
+    {   // all images and keys start all-zero
+        uint4 *z = reinterpret_cast<uint4 *>(bufs);
+        const int n16 = (int)((L.stride * (size_t)G) >> 4);
+        for (int w = tid; w < n16; w += blockDim.x) z[w] = make_uint4(0u, 0u, 0u, 0u);
+        if (tid < 2 * kPipeMaxGroups) cnt[tid] = 0u;
+        if (tid < kDensityLutSize) slut[tid] = __ldg(lut + tid);
+        if (tid < G) mbar_init(full + tid, (unsigned)gthreads);
+    }
+    fence_proxy_async_smem();
+    __syncthreads();
+
+    const int grid = gridDim.x, b = blockIdx.x;
+    const int tpf = p.tiles_per_frame;
+    const long long cells_total = (long long)p.xn * p.yn;
+    const int tstep = G * grid;  // total_tiles + 2 * tstep stays far below 2^31 (checked by the launcher)
+
+    if (tid >= nbuild) {
+        // ---------------- store warp ----------------
+        // Stores whichever image is finished (build times are skewed: tiles near the sensor hold hundreds of records),
+        // polling the groups' mbarriers round-robin. The bulk stores of consecutive tiles form one stream of chunks:
+        // before a chunk is issued at most pipe_pending older chunks may still be unread, and an image goes back to
+        // its builders (the "empty" barrier) as soon as the stream has moved past its last chunk -- so the next
+        // tile is found and addressed while the previous one is still being read.
+        const int lane = tid - nbuild;
+        const uint64_t pol = l2_policy_evict_first();
+        const uint32_t chunk = (uint32_t)p.pipe_chunk;
+        const int pending = p.pipe_pending;
+        int kq[kPipeMaxGroups];  // next round of each group
+#pragma unroll
+        for (int g = 0; g < kPipeMaxGroups; g++) kq[g] = 0;
+        int left = 0;  // tiles of this CTA
+        for (int g = 0; g < G; g++) {
+            const int first = g * grid + b;
+            if (first < total_tiles) left += (total_tiles - 1 - first) / tstep + 1;
+        }
+        int prev_g = -1;  // image whose store has been issued but which has not been handed back yet
+        auto release = [&](int g) {  // all lanes
+            __syncwarp();
+            named_arrive(1 + kPipeMaxGroups + g, hand);
+        };
+        while (left > 0) {
+            int idle = 1;
+#pragma unroll
+            for (int g = 0; g < kPipeMaxGroups; g++) {
+                if (g >= G) continue;
+                const int k = kq[g];
+                const int t = (k * G + g) * grid + b;
+                if (t >= total_tiles) continue;
+                int ready = (lane == 0) ? (int)mbar_test(full + g, (unsigned)(k & 1)) : 0;
+                ready = __shfl_sync(0xffffffffu, ready, 0);
+                if (!ready) continue;
+                idle = 0;
+                kq[g] = k + 1;
+                left--;
+                const int f = t / tpf, tl = t - f * tpf;
+                const long long cell0 = (long long)tl * T;
+                const int ncell = (int)min((long long)T, cells_total - cell0);
+                const uint32_t bytes = (uint32_t)ncell * (uint32_t)planes * 4u;
+                float *dst = top + (size_t)f * p.top_frame_floats + (size_t)cell0 * planes;
+                const unsigned char *img = bufs + (size_t)g * L.stride;
+                const bool bulk = ((reinterpret_cast<uintptr_t>(dst) | (uintptr_t)bytes) & 15u) == 0;
+                const bool again = t + tstep < total_tiles;  // the builders will want this image back
+                if (bulk) {
+                    int j = 0;
+                    for (uint32_t off = 0; off < bytes; off += chunk, j++) {
+                        if (lane == 0) bulk_wait_read_pending(pending);
+                        if (prev_g >= 0 && j == pending) { release(prev_g); prev_g = -1; }
+                        if (lane == 0) {
+                            bulk_store_hint(reinterpret_cast<char *>(dst) + off, img + off, min(chunk, bytes - off), pol);
+                            bulk_commit();
+                        }
+                    }
+                    if (prev_g >= 0) {  // fewer chunks than the stream may leave unread: wait for all but this tile's
+                        if (lane == 0) bulk_wait_read_pending(j);
+                        release(prev_g);
+                    }
+                    prev_g = again ? g : -1;
+                } else {
+                    if (lane == 0) bulk_wait_read_all();
+                    if (prev_g >= 0) { release(prev_g); prev_g = -1; }
+                    const unsigned *s = reinterpret_cast<const unsigned *>(img);
+                    for (int w = lane; w < ncell * planes; w += 32) dst[w] = __uint_as_float(s[w]);
+                    if (again) release(g);
+                }
+            }
+            if (idle && prev_g >= 0) {  // nothing to issue: do not sit on the last image
+                if (lane == 0) bulk_wait_read_all();
+                release(prev_g);
+                prev_g = -1;
+            }
+        }
+        if (lane == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
+        return;
+    }
+
+    // ---------------- builder group g ----------------
+    const int g = tid / gthreads, gt = tid - g * gthreads;
+    const int lane = gt & 31, gwarp = gt >> 5, gwarps = gthreads >> 5;
+    const int bar_own = 1 + g, bar_empty = 1 + kPipeMaxGroups + g;
+    unsigned char *buf = bufs + (size_t)g * L.stride;
+    unsigned *img = reinterpret_cast<unsigned *>(buf);
+    unsigned long long *key = reinterpret_cast<unsigned long long *>(buf + L.key_off);
+    unsigned *dirty = reinterpret_cast<unsigned *>(buf + L.dirty_off);
+    unsigned *occ_tile = reinterpret_cast<unsigned *>(buf + L.occ_off);
+    unsigned *mycnt = cnt + 2 * g;
+
+    auto bin_range = [&](int t, const uint4 *&rec, int &n) {
+        n = 0;
+        rec = binned;
+        if (t < total_tiles) {
+            const int f = t / tpf, tl = t - f * tpf;
+            const unsigned *off = tile_off + (size_t)f * (tpf + 1) + tl;
+            const unsigned beg = __ldg(off);
+            n = (int)(__ldg(off + 1) - beg);
+            rec = binned + (size_t)offs.off[f] + beg;
+        }
+    };
+    const int t_first = g * grid + b;
+    const uint4 *rec0, *rec1, *rec2;
+    int n0, n1, n2;
+    bin_range(t_first, rec0, n0);
+    bin_range(t_first + tstep, rec1, n1);
+    uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
+    if (gt < n0) q0 = __ldg(rec0 + gt);
+
+    int k = 0;
+    for (int t = t_first; t < total_tiles; t += tstep, k++) {
+        bin_range(t + 2 * tstep, rec2, n2);
+        if (gt < n1) q1 = __ldg(rec1 + gt);
+        const int f = t / tpf, tl = t - f * tpf;
+        const long long cell0 = (long long)tl * T;
+        unsigned *cur = mycnt + (k & 1), *prev = mycnt + ((k & 1) ^ 1);
+
+        if (k > 0) named_sync(bar_empty, hand);  // the store warp has read the previous tile of this image
+        const int nd_prev = (int)*prev;
+        if (n0 > 0 || nd_prev > 0) {
+            // re-zero what the previous tile touched
+            for (int d = gwarp; d < nd_prev; d += gwarps) {
+                const unsigned local = dirty[d];
+                for (int kk = lane; kk < planes; kk += 32) img[local * planes + kk] = 0u;
+                if (lane == 0) key[local] = 0ull;
+            }
+            if (gt == 0) *cur = 0u;
+            named_sync(bar_own, gthreads);
+
+            // accumulate
+            for (int r = gt; r < n0; r += gthreads) {
+                const uint4 q = (r == gt) ? q0 : __ldg(rec0 + r);
+                const unsigned local = q.x & 0xFFFFu, Z = q.x >> 16;
+                unsigned *cellw = img + local * planes;
+                if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(cur, 1u)] = local;
+                if ((int)q.y > 0) {
+                    if (kPy) {
+                        const unsigned zs = Z & (kLowerFlag - 1u);
+                        if (zs != kNoSlice) atomicMax(cellw + zs, q.y);
+                        if (Z & kLowerFlag) {
+                            const unsigned below = (zs == kNoSlice) ? (unsigned)zn - 1u : zs - 1u;
+                            if (below < (unsigned)zn) atomicMax(cellw + below, q.y);
+                        }
+                    } else {
+                        atomicMax(cellw + Z, q.y);
+                    }
+                    atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
+                }
+            }
+            named_sync(bar_own, gthreads);
+
+            // finalise the touched cells in place
+            const int nd = (int)*cur;
+            for (int r = gt; r < n0; r += gthreads) {
+                const uint4 q = (r == gt) ? q0 : __ldg(rec0 + r);
+                const unsigned local = q.x & 0xFFFFu;
+                if ((int)q.y > 0 &&
+                    key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z))) {
+                    img[local * planes + zn] = q.w;
+                    if (kOccupancy && ((q.w >> 31) != 0u || (q.w & 0x7fffffffu) > 0x7f800000u))
+                        atomicOr(sink.flags + f, 1u);
+                }
+            }
+            for (int d = gwarp; d < nd; d += gwarps) {
+                unsigned *cellw = img + dirty[d] * planes;
+                if (kOccupancy && lane == 0) {
+                    const unsigned gc = (unsigned)cell0 + dirty[d];
+                    atomicOr(occ_tile + ((gc >> 5) - ((unsigned)cell0 >> 5)), 1u << (gc & 31u));
+                }
+                for (int kk = lane; kk < planes; kk += 32) {
+                    if (kk < zn) {
+                        const unsigned raw = cellw[kk];
+                        if (raw) cellw[kk] = __float_as_uint(kPy ? __fsub_rn(__uint_as_float(raw), (float)kk)
+                                                                  : slice_value(__uint_as_float(raw), p.z_div, kk));
+                    } else if (kk == zn + 1) {
+                        const unsigned c = cellw[kk];
+                        cellw[kk] = __float_as_uint(slut[c < 31u ? c : 31u]);
+                    }
+                }
+            }
+            if (kOccupancy) {
+                named_sync(bar_own, gthreads);
+                const int ncell = (int)min((long long)T, cells_total - cell0);
+                const unsigned w_first = (unsigned)cell0 >> 5, w_last = ((unsigned)cell0 + (unsigned)ncell - 1u) >> 5;
+                unsigned *out = sink.words + (size_t)f * sink.words_per_frame + w_first;
+                for (unsigned w = gt; w <= w_last - w_first; w += gthreads) {
+                    const unsigned bits = occ_tile[w];
+                    if (bits) {
+                        if ((T & 31) != 0 && (w == 0 || w == w_last - w_first)) atomicOr(out + w, bits);
+                        else out[w] = bits;
+                        occ_tile[w] = 0u;
+                    }
+                }
+            }
+        } else if (gt == 0) {
+            *cur = 0u;
+        }
+        fence_proxy_async_smem();
+        mbar_arrive(full + g);  // gthreads arrivals complete the phase: the image is ready for the store warp
+        rec0 = rec1; n0 = n1; q0 = q1;
+        rec1 = rec2; n1 = n2;
+    }
+}
+
+size_t tile_pipe_smem_bytes(const ViewParams &p)
+{
+    const PipeLayout l = pipe_layout(p.tile_cells, p.planes);
+    return l.header + l.stride * (size_t)p.pipe_groups;
+}
+
+// ------------------------------------------------------------------------------------------------
 // PATCH strategy, zero-fill: bulk async (TMA) stores from one all-zero shared-memory buffer. One elected thread
 // per CTA issues the stores, so the kernel holds one warp and 16 KB of shared memory per CTA and leaves the SMs
 // to the point passes running beside it on another stream.
@@ -975,6 +1287,17 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s, const OccupancySink *sink)
 {
     const int total = batch * p.tiles_per_frame;
+    if (p.pipe_groups > 0 && (long long)total + 2LL * p.pipe_groups * p.pipe_grid < 2147483647LL) {  // one CTA per SM
+        const int grid = p.pipe_grid < total ? p.pipe_grid : total;
+        const bool occ = sink && sink->words;
+        auto kernel = occ ? (p.py ? tile_pipe_kernel<true, true> : tile_pipe_kernel<true, false>)
+                          : (p.py ? tile_pipe_kernel<false, true> : tile_pipe_kernel<false, false>);
+        const size_t smem = tile_pipe_smem_bytes(p);
+        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        const int threads = p.pipe_groups * p.pipe_group_threads + 32;
+        kernel<<<grid, threads, smem, s>>>(binned, tile_off, offs, p, lut, top, total, occ ? *sink : OccupancySink());
+        return 1;
+    }
     const int grid = grid_blocks < total ? grid_blocks : total;
     if (sink && sink->words) {
         auto kernel = p.py ? tile_build_occupancy_kernel<true> : tile_build_occupancy_kernel<false>;

@@ -21,6 +21,7 @@ struct OccupancySink {
 // Each launcher enqueues on `s` and returns the number of kernels it launched.
 size_t tile_smem_bytes(const ViewParams &p);
 cudaError_t tile_build_configure(const ViewParams &p, int *blocks_per_sm);
+size_t tile_pipe_smem_bytes(const ViewParams &p);
 
 int launch_classify(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
                     uint2 *keys, unsigned *tile_count, unsigned *fv_winner, cudaStream_t s);

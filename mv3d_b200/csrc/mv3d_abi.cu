@@ -92,6 +92,14 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
         for (int i = 0; i < 6; i++)
             if (strcmp(ts, names[i]) == 0) ctx->tile_store = i;
     }
+    if (const char *tp = getenv("MV3D_TILE_PIPE")) {
+        int v[4] = {0, ctx->pipe_group_threads, ctx->pipe_chunk, ctx->pipe_pending};
+        sscanf(tp, "%d,%d,%d,%d", &v[0], &v[1], &v[2], &v[3]);
+        ctx->pipe_groups = v[0] < 0 ? 0 : (v[0] > 5 ? 5 : v[0]);
+        ctx->pipe_group_threads = v[1] < 32 ? 32 : (v[1] & ~31);
+        ctx->pipe_chunk = v[2] < 16 ? 16 : (v[2] & ~15);
+        ctx->pipe_pending = v[3] < 0 ? 0 : v[3];
+    }
     const char *fs = getenv("MV3D_FRONT_ASIDE");
     ctx->front_aside = fs ? atoi(fs) : 1;
     const char *ao = getenv("MV3D_ATOMIC_OVERLAP");
@@ -251,6 +259,27 @@ static int pick_tile_cells(size_t bytes_target, int planes, long long cells)
     return (int)t;
 }
 
+// Pipelined tile kernel: as many tile images per CTA as the context asks for and shared memory holds; below two the
+// one-tile-per-CTA kernel is used.
+static void apply_pipe(const mv3d_ctx *ctx, ViewParams *p)
+{
+    p->pipe_groups = 0;
+    int g = ctx->pipe_groups;
+    if (g <= 0 || p->tile_cells <= 0) return;
+    while (g * ctx->pipe_group_threads + 32 > 1024) g--;
+    ViewParams q = *p;
+    for (; g >= 2; g--) {
+        q.pipe_groups = g;
+        if (tile_pipe_smem_bytes(q) <= ctx->smem_optin) break;
+    }
+    if (g < 2) return;
+    p->pipe_groups = g;
+    p->pipe_group_threads = ctx->pipe_group_threads;
+    p->pipe_chunk = ctx->pipe_chunk;
+    p->pipe_pending = ctx->pipe_pending;
+    p->pipe_grid = ctx->sm_count;
+}
+
 static bool tile_feasible(const mv3d_ctx *ctx, const mv3d_top_params *tp, bool patch)
 {
     if (!tp || tp->zn > 65535) return false;
@@ -305,6 +334,7 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
     p.tiles_per_frame = (int)((cells + p.tile_cells - 1) / p.tile_cells);
     p.store_mode = ctx->tile_store;
     p.tile_magic = tile_magic_for(p.tile_cells);
+    if (strategy != MV3D_STRATEGY_PATCH) apply_pipe(ctx, &p);
     p.z_span = tp->z_max - tp->z_min;  // float subtraction, LidarTopAndFrontPreprocess.c:185
     if (want_front) {
         if (!fp) return fail("front parameters are required when a front view is requested");
@@ -834,6 +864,7 @@ static int make_py_params(const mv3d_ctx *ctx, const mv3d_pytwin_params *pp, boo
     p.tiles_per_frame = cells ? (int)((cells + p.tile_cells - 1) / p.tile_cells) : 0;
     p.store_mode = ctx->tile_store;
     p.tile_magic = tile_magic_for(p.tile_cells);
+    apply_pipe(ctx, &p);
     PyFrontParams f;
     memset(&f, 0, sizeof(f));
     f.ang_res = pp->ang_res; f.vert_res = pp->vert_res; f.velodyne_height = pp->velodyne_height;
@@ -965,6 +996,7 @@ static void align_tiles_to_words(const mv3d_ctx *ctx, ViewParams *p)
     p->tile_cells = pick;
     p->tile_magic = tile_magic_for(pick);
     p->tiles_per_frame = (int)((cells + pick - 1) / pick);
+    apply_pipe(ctx, p);
 }
 
 static int check_filter_args(const char *who, mv3d_ctx *ctx, int batch, float *top_dev, int mode, int *keep_dev,
