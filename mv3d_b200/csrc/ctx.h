@@ -80,14 +80,16 @@ struct HostSlot {
 // Kernel classes, in the order mv3d_kernel_name() reports them.
 enum KernelId { K_CLASSIFY = 0, K_TILE_SCAN, K_BIN, K_TILE_BUILD, K_FRONT_FINALIZE, K_FILL_ZERO, K_ATOMIC_SCATTER,
                 K_ATOMIC_FINALIZE, K_FILL_TMA, K_WARP_PATCH, K_TILE_COMPACT, K_PYFRONT_LINK,
-                K_PYFRONT_REDUCE, K_ANCHOR_OCCUPANCY, K_ANCHOR_TEST, K_ANCHOR_SUM, K_ANCHOR_COMPACT, K_COUNT };
+                K_PYFRONT_REDUCE, K_ANCHOR_OCCUPANCY, K_ANCHOR_TEST, K_ANCHOR_SUM, K_ANCHOR_COMPACT, K_FILL_CE,
+                K_TILE_PATCH, K_COUNT };
 static const char *const kKernelNames[K_COUNT] = {"classify_kernel", "tile_scan_kernel", "bin_kernel",
                                                   "tile_build_kernel", "front_finalize_kernel", "fill_zero_kernel",
                                                   "atomic_scatter_kernel", "atomic_finalize_kernel",
                                                   "fill_tma_kernel", "warp_patch_kernel", "tile_compact_kernel",
                                                   "pyfront_link_kernel", "pyfront_reduce_kernel",
                                                   "anchor_occupancy_kernel", "anchor_test_kernel",
-                                                  "anchor_sum_kernel", "anchor_compact_kernel"};
+                                                  "anchor_sum_kernel", "anchor_compact_kernel",
+                                                  "ce_zero_fill", "tile_patch_kernel"};
 
 struct TimedLaunch {
     cudaEvent_t start, stop;
@@ -120,6 +122,9 @@ struct mv3d_ctx {
     int fill_ctas = 0;                    // fill CTAs per SM (one issuing thread each)
     int fill_pending = 0;                 // bulk stores each fill CTA keeps in flight (> 16: unbounded)
     int tile_store = 1;                   // MV3D_TILE_STORE: how the tile kernel writes a tile (1 = bulk stores, evict-first)
+    int auto_atomic_batch = 3;            // AUTO: up to this many sweeps per device call go to the atomic strategy
+    double auto_atomic_ratio = 0.07;      // AUTO: ... and so do calls whose points weigh more than this share of the output bytes
+    int patch_mode = 1;                   // MV3D_PATCH_MODE: 1 = copy-engine zero-fill + tile_patch_kernel, 0 = TMA fill kernel + warp_patch_kernel
     int pipe_groups = 0;                  // MV3D_TILE_PIPE=G[,threads[,chunk[,pending]]]: pipelined tile kernel (0 = off)
     int pipe_group_threads = 192;
     int pipe_chunk = 8640;

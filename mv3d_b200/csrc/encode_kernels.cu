@@ -86,7 +86,8 @@ __device__ __forceinline__ void bulk_wait_read_all()
 // How the tile kernel writes a finished tile (ViewParams::store_mode; MV3D_TILE_STORE=tma|tma_hint|tma_split|lsu|lsu_cs).
 // Default: bulk stores with an L2 evict-first policy -- the output is written once and never read back here, so it
 // should not push the bin records (read by this same kernel) out of L2. Measured in profiles/strategy_experiments_r1.md.
-enum TileStore { kStoreTma = 0, kStoreTmaHint = 1, kStoreTmaSplit = 2, kStoreLsu = 3, kStoreLsuStream = 4, kStoreTmaPaced = 5 };
+// kStorePatch: the output has been zero-filled already (copy engine); write the touched cells only.
+enum TileStore { kStoreTma = 0, kStoreTmaHint = 1, kStoreTmaSplit = 2, kStoreLsu = 3, kStoreLsuStream = 4, kStoreTmaPaced = 5, kStorePatch = 6 };
 __device__ __forceinline__ void tile_bulk_store(void *gdst, const void *ssrc, uint32_t bytes, int mode)
 {
     if (mode == kStoreTmaHint) {
@@ -331,6 +332,10 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
 // zero -- into a pre-zeroed per-frame bit map, and raise the frame's flag when an intensity is negative, -0 or NaN
 // (the only values of a view that can be; then the filter must take exact sums). The bits of a tile are gathered
 // in shared memory; the first and last word of a tile may be shared with its neighbours and go out as atomics.
+#ifndef MV3D_RECORDS_IN_FLIGHT
+#define MV3D_RECORDS_IN_FLIGHT 2
+#endif
+constexpr int kRecordsInFlight = MV3D_RECORDS_IN_FLIGHT;  // records of a heavy tile each thread fetches before reducing them
 template <bool kCompact, bool kOccupancy, bool kPy, int kStore = kStoreTmaHint>
 __device__ __forceinline__ void
 tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, const FrameOffsets &offs,
@@ -396,7 +401,9 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
             // nothing to report for an empty tile
         } else if (n0 == 0) {
             // Empty tile: stream the all-zero image; nothing is modified, so no barrier.
-            if (bulk && kStore == kStoreLsu) {
+            if (kStore == kStorePatch) {
+                // the output is zero already
+            } else if (bulk && kStore == kStoreLsu) {
                 float4 *d4 = reinterpret_cast<float4 *>(dst);
                 for (int w = tid; w < (int)(bytes >> 4); w += kTileThreads) d4[w] = make_float4(0.f, 0.f, 0.f, 0.f);
             } else if (bulk && kStore == kStoreLsuStream) {
@@ -414,9 +421,10 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 __syncthreads();
             }
 
-            // accumulate
-            for (int r = tid; r < n0; r += kTileThreads) {
-                const uint4 q = (r == tid) ? q0 : __ldg(rec0 + r);
+            // accumulate: the first kTileThreads records are in registers already (prefetched); the rest of a heavy
+            // tile (tiles next to the sensor hold hundreds to thousands of records) are fetched four per thread at
+            // a time, so that their L2 latency overlaps
+            auto accumulate = [&](const uint4 &q) {
                 const unsigned local = q.x & 0xFFFFu, Z = q.x >> 16;
                 unsigned *cellw = img + local * planes;
                 if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(&ndirty, 1u)] = local;
@@ -433,13 +441,22 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                     }
                     atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
                 }
+            };
+            if (tid < n0) accumulate(q0);
+            for (int r = tid + kTileThreads; r < n0; r += kRecordsInFlight * kTileThreads) {
+                uint4 q[kRecordsInFlight];
+#pragma unroll
+                for (int j = 0; j < kRecordsInFlight; j++)
+                    if (r + j * kTileThreads < n0) q[j] = __ldg(rec0 + r + j * kTileThreads);
+#pragma unroll
+                for (int j = 0; j < kRecordsInFlight; j++)
+                    if (r + j * kTileThreads < n0) accumulate(q[j]);
             }
             __syncthreads();
 
             // finalise the touched cells in place
             const int nd = (int)ndirty;
-            for (int r = tid; r < n0; r += kTileThreads) {  // intensity of each cell's winner
-                const uint4 q = (r == tid) ? q0 : __ldg(rec0 + r);
+            auto claim = [&](const uint4 &q) {  // intensity of each cell's winner
                 const unsigned local = q.x & 0xFFFFu;
                 if ((int)q.y > 0 &&
                     key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z))) {
@@ -447,6 +464,16 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                     if (kOccupancy && ((q.w >> 31) != 0u || (q.w & 0x7fffffffu) > 0x7f800000u))
                         atomicOr(sink.flags + f, 1u);
                 }
+            };
+            if (tid < n0) claim(q0);
+            for (int r = tid + kTileThreads; r < n0; r += kRecordsInFlight * kTileThreads) {
+                uint4 q[kRecordsInFlight];
+#pragma unroll
+                for (int j = 0; j < kRecordsInFlight; j++)
+                    if (r + j * kTileThreads < n0) q[j] = __ldg(rec0 + r + j * kTileThreads);
+#pragma unroll
+                for (int j = 0; j < kRecordsInFlight; j++)
+                    if (r + j * kTileThreads < n0) claim(q[j]);
             }
             for (int d = warp; d < nd; d += kWarps) {  // one warp per touched cell, lanes over planes
                 unsigned *cellw = img + dirty[d] * planes;
@@ -482,6 +509,11 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 }
                 for (int d = nd + tid; d < n0; d += kTileThreads)
                     if (beg + (unsigned)d < compact_cap) out_idx[beg + (unsigned)d] = kNoCell;
+            } else if (kStore == kStorePatch) {
+                for (int d = warp; d < nd; d += kWarps) {  // one warp per touched cell: its planes are contiguous
+                    const unsigned local = dirty[d];
+                    for (int k = lane; k < planes; k += 32) dst[local * planes + k] = __uint_as_float(img[local * planes + k]);
+                }
             } else if (bulk && kStore >= kStoreLsu) {
                 const uint4 *s4 = reinterpret_cast<const uint4 *>(img);
                 uint4 *d4 = reinterpret_cast<uint4 *>(dst);
@@ -526,7 +558,7 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
 }
 
 template <bool kPy, int kStore = kStoreTmaHint>
-__global__ void __launch_bounds__(kTileThreads)
+__global__ void __launch_bounds__(kTileThreads, 5)
 tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
                   const __grid_constant__ FrameOffsets offs,
                   const __grid_constant__ ViewParams p, const float *__restrict__ lut, float *__restrict__ top,
@@ -537,7 +569,7 @@ tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
 
 // Same, and the occupancy bits / flag of every frame for the empty-anchor filter (see tile_body).
 template <bool kPy>
-__global__ void __launch_bounds__(kTileThreads)
+__global__ void __launch_bounds__(kTileThreads, 5)
 tile_build_occupancy_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
                   const __grid_constant__ FrameOffsets offs,
                             const __grid_constant__ ViewParams p, const float *__restrict__ lut,
@@ -546,9 +578,20 @@ tile_build_occupancy_kernel(const uint4 *__restrict__ binned, const unsigned *__
     tile_body<false, true, kPy>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u, sink);
 }
 
+// Same reduction for an output the copy engine has zero-filled: only the touched cells are written (PATCH strategy).
+template <bool kPy>
+__global__ void __launch_bounds__(kTileThreads, 5)
+tile_patch_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
+                  const __grid_constant__ FrameOffsets offs,
+                  const __grid_constant__ ViewParams p, const float *__restrict__ lut, float *__restrict__ top,
+                  int total_tiles)
+{
+    tile_body<false, false, kPy, kStorePatch>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u);
+}
+
 // Same reduction, compact output (see tile_body).
 template <bool kPy>
-__global__ void __launch_bounds__(kTileThreads)
+__global__ void __launch_bounds__(kTileThreads, 5)
 tile_compact_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
                   const __grid_constant__ FrameOffsets offs,
                     const __grid_constant__ ViewParams p, const float *__restrict__ lut, int total_tiles,
@@ -1315,6 +1358,25 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
         }
         kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
     }
+    return 1;
+}
+
+cudaError_t tile_patch_configure(const ViewParams &p, int *blocks_per_sm)
+{
+    const size_t smem = tile_smem_bytes(p);
+    auto kernel = p.py ? tile_patch_kernel<true> : tile_patch_kernel<false>;
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, kernel, kTileThreads, smem);
+}
+
+int launch_tile_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
+                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s)
+{
+    const int total = batch * p.tiles_per_frame;
+    const int grid = grid_blocks < total ? grid_blocks : total;
+    auto kernel = p.py ? tile_patch_kernel<true> : tile_patch_kernel<false>;
+    kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
     return 1;
 }
 

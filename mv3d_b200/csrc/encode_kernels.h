@@ -34,6 +34,9 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
 int launch_tile_compact(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                         const float *lut, int batch, int grid_blocks, unsigned *compact, unsigned compact_cap,
                         cudaStream_t s);
+cudaError_t tile_patch_configure(const ViewParams &p, int *blocks_per_sm);
+int launch_tile_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
+                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
 size_t patch_smem_bytes(const ViewParams &p);
 cudaError_t warp_patch_configure(const ViewParams &p, int *blocks_per_sm);
 size_t fill_tma_smem_bytes();

@@ -82,8 +82,9 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     ctx->smem_optin = prop.sharedMemPerBlockOptin;
     const char *tb = getenv("MV3D_TILE_BYTES");
     ctx->tile_bytes_target = tb ? (size_t)strtoull(tb, nullptr, 10) : (size_t)(36 * 1024);
+    if (const char *pm = getenv("MV3D_PATCH_MODE")) ctx->patch_mode = (strcmp(pm, "warp") == 0 || strcmp(pm, "0") == 0) ? 0 : 1;
     const char *pb = getenv("MV3D_PATCH_TILE_BYTES");
-    ctx->patch_tile_bytes = pb ? (size_t)strtoull(pb, nullptr, 10) : (size_t)6912;
+    ctx->patch_tile_bytes = pb ? (size_t)strtoull(pb, nullptr, 10) : (size_t)(ctx->patch_mode ? 36 * 1024 : 6912);
     const char *fa = getenv("MV3D_FILL_CTAS");
     ctx->fill_ctas = fa ? atoi(fa) : 2;
     if (ctx->fill_ctas < 1) ctx->fill_ctas = 1;
@@ -116,6 +117,8 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     ctx->host_threads = ht ? atoi(ht) : 0;
     const char *hr = getenv("MV3D_HOST_READBACK");
     ctx->host_compact = (hr && strcmp(hr, "dense") == 0) ? 0 : 1;
+    if (const char *ab = getenv("MV3D_AUTO_ATOMIC_BATCH")) ctx->auto_atomic_batch = atoi(ab);
+    if (const char *ar = getenv("MV3D_AUTO_ATOMIC_RATIO")) ctx->auto_atomic_ratio = atof(ar);
     const char *sb = getenv("MV3D_SUB_BATCH");
     ctx->sub_batch = sb ? atoi(sb) : 0;  // measured on B200: two-stream pipelining loses to one stream (profiles/)
     int prio_lo = 0, prio_hi = 0;
@@ -286,7 +289,7 @@ static bool tile_feasible(const mv3d_ctx *ctx, const mv3d_top_params *tp, bool p
     const int planes = tp->zn + 2;
     const int t = pick_tile_cells(patch ? ctx->patch_tile_bytes : ctx->tile_bytes_target, planes, (long long)tp->xn * tp->yn);
     const size_t per = (((size_t)t * planes * 4 + 15) & ~(size_t)15) + (size_t)t * 12 + 64;
-    return (patch ? per * 8 : per) <= ctx->smem_optin;  // PATCH: one image per warp, 8 warps per CTA
+    return ((patch && ctx->patch_mode == 0) ? per * 8 : per) <= ctx->smem_optin;  // warp patch: one image per warp, 8 warps per CTA
 }
 
 extern "C" int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy)
@@ -298,14 +301,23 @@ extern "C" int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params 
     return MV3D_STRATEGY_TILE;  // AUTO is refined per call by the batch size (see resolve_for_batch)
 }
 
-// AUTO: PATCH (zero-fill on a side stream overlapped with the point passes) pays off once a call carries enough
-// sweeps to pipeline; single sweeps keep the one-pass TILE kernel.
-static int resolve_for_batch(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy, int batch)
+// AUTO, refined per call. Measured on a B200 (tools/configs_bench.py --crossover, profiles/crossover_r1j.jsonl):
+//  * the tile strategy wins when the dense write dominates (64 KITTI sweeps: 78 k vs 62 k sweeps/s);
+//  * up to three sweeps per call the three small launches of the atomic strategy finish first (one sweep: 57 vs 74 us);
+//  * once the points weigh more than ~7 % of the output bytes (the 2 M-point cloud of config 5: 36 %) the per-tile
+//    reduction chain of the hottest tiles is the long pole and the L2 atomics win (0.67 vs 0.96 ms per 8 clouds).
+// points_total < 0: the caller needs the tile strategy's by-products (compact read-back, occupancy report).
+static int resolve_for_batch(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy, int batch,
+                             long long points_total = -1)
 {
     const int r = mv3d_resolve_strategy(ctx, tp, strategy);
-    if (strategy == MV3D_STRATEGY_AUTO && r == MV3D_STRATEGY_TILE && batch >= ctx->patch_min_batch &&
-        tile_feasible(ctx, tp, true))
-        return MV3D_STRATEGY_PATCH;
+    if (strategy != MV3D_STRATEGY_AUTO || r != MV3D_STRATEGY_TILE) return r;
+    if (batch >= ctx->patch_min_batch && tile_feasible(ctx, tp, true)) return MV3D_STRATEGY_PATCH;
+    if (points_total >= 0 && batch > 0) {
+        const double out_bytes = (double)batch * tp->xn * tp->yn * (tp->zn + 2) * 4.0;
+        if (batch <= ctx->auto_atomic_batch || 16.0 * (double)points_total > ctx->auto_atomic_ratio * out_bytes)
+            return MV3D_STRATEGY_ATOMIC;
+    }
     return r;
 }
 
@@ -391,7 +403,9 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
         if (ensure(ws.tile_count, hist, true, s)) return -1;
         if (ensure(ws.tile_off, hist, false, s)) return -1;
         int blocks_per_sm = 0;
-        if (patch) {
+        if (patch && ctx->patch_mode == 1) {
+            CUDA_TRY(tile_patch_configure(p, &blocks_per_sm));
+        } else if (patch) {
             CUDA_TRY(warp_patch_configure(p, &blocks_per_sm));
             // leave shared memory for the fill CTAs that must stay resident beside the patch warps
             const size_t fill_need = (size_t)ctx->fill_ctas * (fill_tma_smem_bytes() + 1024);
@@ -418,9 +432,16 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
             for (int j0 = 0, j = 0; j0 < batch; j0 += chunk, j++) {
                 const int nb = (batch - j0 < chunk) ? batch - j0 : chunk;
                 float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
-                timed_launch(ctx, K_FILL_TMA, sf, [&] {
-                    return launch_fill_tma(top_j, (size_t)nb * (size_t)p.top_frame_floats, ctx->sm_count * ctx->fill_ctas, ctx->fill_pending, sf);
-                });
+                if (ctx->patch_mode == 1) {  // the copy engine writes zeros faster than any kernel does, and needs no SM
+                    timed_launch(ctx, K_FILL_CE, sf, [&] {
+                        cudaMemsetAsync(top_j, 0, (size_t)nb * (size_t)p.top_frame_floats * 4, sf);
+                        return 0;  // not a kernel of this library: timed, but not counted as a launch
+                    });
+                    ctx->kernel_launches[K_FILL_CE]++;
+                } else
+                    timed_launch(ctx, K_FILL_TMA, sf, [&] {
+                        return launch_fill_tma(top_j, (size_t)nb * (size_t)p.top_frame_floats, ctx->sm_count * ctx->fill_ctas, ctx->fill_pending, sf);
+                    });
                 CUDA_TRY(cudaEventRecord(ctx->ev_ready[j], sf));
             }
             timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, winners, s); });
@@ -436,9 +457,14 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
                 unsigned *to = toff + (size_t)j0 * (p.tiles_per_frame + 1);
                 float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
                 CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_ready[j], 0));
-                timed_launch(ctx, K_WARP_PATCH, s, [&] {
-                    return launch_warp_patch(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
-                });
+                if (ctx->patch_mode == 1)
+                    timed_launch(ctx, K_TILE_PATCH, s, [&] {
+                        return launch_tile_patch(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
+                    });
+                else
+                    timed_launch(ctx, K_WARP_PATCH, s, [&] {
+                        return launch_warp_patch(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
+                    });
             }
             CUDA_TRY(cudaGetLastError());
             return 0;
@@ -616,7 +642,7 @@ extern "C" int mv3d_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, con
     if (!ctx) return fail("mv3d_encode_batch_dev: ctx is NULL");
     if (check_offsets(offsets_host, batch)) return -1;
     ViewParams p;
-    const int strat = resolve_for_batch(ctx, tp, strategy, batch);
+    const int strat = resolve_for_batch(ctx, tp, strategy, batch, (long long)offsets_host[batch] - offsets_host[0]);
     if (make_params(ctx, tp, fp, top_dev != nullptr, front_dev != nullptr, semantics, strat, &p)) return -1;
     if (batch == 0 || (!top_dev && !front_dev)) return 0;
     std::lock_guard<std::mutex> lock(ctx->mu);
