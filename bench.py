@@ -42,7 +42,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--strategy", default="auto", choices=["auto", "tile", "patch", "atomic"])
+    ap.add_argument("--strategy", default="auto", choices=["auto", "tile", "patch", "atomic", "sort"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
     ap.add_argument("--no-also", action="store_true", help="skip the short legs for the widened rows (profiling runs)")
@@ -342,7 +342,8 @@ def run_ours(args):
     step_kernel_ms = sum(v[0] for v in ktimes.values())
     # bytes the dominant kernel is responsible for, per launch
     # (a step may launch it several times: one launch per pipelined sub-batch)
-    per_step = {"tile_build_kernel": ab["bev"] * BATCH, "fill_tma_kernel": ab["bev"] * BATCH}.get(dominant, ab["total"] * BATCH)
+    per_step = {"tile_build_kernel": ab["bev"] * BATCH, "fill_tma_kernel": ab["bev"] * BATCH, "fill_zero_kernel": ab["bev"] * BATCH,
+                "ce_zero_fill": ab["bev"] * BATCH}.get(dominant, ab["total"] * BATCH)
     per_launch = per_step * args.steps / max(dom_launches, 1)
     achieved = per_launch / (dom_ms / max(dom_launches, 1) * 1e-3) / 1e9 if dom_ms > 0 else 0.0
     step_achieved = ab["total"] * BATCH * args.steps / (elapsed_ms * 1e-3) / 1e9

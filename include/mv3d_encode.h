@@ -86,8 +86,11 @@ enum {
     MV3D_STRATEGY_AUTO = 0,
     MV3D_STRATEGY_ATOMIC = 1, /* zero-fill, then order-preserving integer atomics straight into the output in HBM/L2 */
     MV3D_STRATEGY_TILE = 2,   /* bin points by output tile, reduce in shared memory, one bulk (TMA) store per tile */
-    MV3D_STRATEGY_PATCH = 3   /* zero-fill by TMA on a side stream while points are binned; then reduce per tile in
-                                 shared memory and overwrite only the sectors that hold touched cells */
+    MV3D_STRATEGY_PATCH = 3,  /* zero-fill on a side stream (copy engine) while points are binned; then reduce per tile
+                                 in shared memory and overwrite only the touched cells */
+    MV3D_STRATEGY_SORT = 4    /* radix sort of the kept points by (frame, cell, slice) key, then one walk per cell run:
+                                 the measured alternative to the tile strategy (C-routine semantics, keys must fit 32
+                                 bits: batch * Xn * Yn * Zn < 2^32; the sort itself is CUB's, a library kernel) */
 };
 
 typedef struct mv3d_ctx mv3d_ctx;

@@ -13,7 +13,7 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libmv3d_encode.so")
-SOURCES = ["encode_kernels.cu", "mv3d_abi.cu", "host_expand.cu", "anchor_kernels.cu", "anchor_abi.cu",
+SOURCES = ["encode_kernels.cu", "sort_strategy.cu", "mv3d_abi.cu", "host_expand.cu", "anchor_kernels.cu", "anchor_abi.cu",
            "sweep_io.cu"]
 HEADERS = ["encode_kernels.h", "view_math.cuh", "host_expand.h", "ctx.h", "anchor_kernels.h",
            os.path.join("..", "..", "include", "mv3d_encode.h"), os.path.join("..", "..", "include", "mv3d_anchors.h"),
@@ -75,7 +75,9 @@ class PyTwinParamsC(ctypes.Structure):
 
 SEM_TOP, SEM_TOPFRONT = 0, 1
 STRATEGY_AUTO, STRATEGY_ATOMIC, STRATEGY_TILE, STRATEGY_PATCH = 0, 1, 2, 3
-STRATEGIES = {"auto": STRATEGY_AUTO, "atomic": STRATEGY_ATOMIC, "tile": STRATEGY_TILE, "patch": STRATEGY_PATCH}
+STRATEGY_SORT = 4
+STRATEGIES = {"auto": STRATEGY_AUTO, "atomic": STRATEGY_ATOMIC, "tile": STRATEGY_TILE, "patch": STRATEGY_PATCH,
+              "sort": STRATEGY_SORT}
 
 # Every symbol include/mv3d_encode.h declares (tests check the built library exports exactly these).
 EXPORTED_SYMBOLS = (

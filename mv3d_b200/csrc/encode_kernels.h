@@ -37,6 +37,16 @@ int launch_tile_compact(const uint4 *binned, const unsigned *tile_off, const Fra
 cudaError_t tile_patch_configure(const ViewParams &p, int *blocks_per_sm);
 int launch_tile_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
+// SORT strategy (sort_strategy.cu)
+unsigned sort_invalid_key(const ViewParams &p, int batch);
+size_t sort_temp_bytes(size_t n, unsigned invalid_key);
+int launch_sort_keys(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
+                     unsigned *keys, unsigned *vals, unsigned *fv_winner, unsigned invalid_key, cudaStream_t s);
+int launch_sort_pairs(void *temp, size_t temp_bytes, const unsigned *keys_in, unsigned *keys_out, const unsigned *vals_in,
+                      unsigned *vals_out, size_t n, unsigned invalid_key, cudaStream_t s);
+int launch_sort_reduce(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const float *lut,
+                       const unsigned *skeys, const unsigned *svals, size_t n, unsigned invalid_key, float *top,
+                       cudaStream_t s);
 size_t patch_smem_bytes(const ViewParams &p);
 cudaError_t warp_patch_configure(const ViewParams &p, int *blocks_per_sm);
 size_t fill_tma_smem_bytes();

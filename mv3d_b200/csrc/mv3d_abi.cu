@@ -296,6 +296,7 @@ extern "C" int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params 
 {
     if (strategy == MV3D_STRATEGY_ATOMIC) return MV3D_STRATEGY_ATOMIC;
     if (!ctx || !tp) return MV3D_STRATEGY_ATOMIC;
+    if (strategy == MV3D_STRATEGY_SORT) return MV3D_STRATEGY_SORT;  // checked per call: the keys must fit 32 bits
     if (strategy == MV3D_STRATEGY_PATCH && tile_feasible(ctx, tp, true)) return MV3D_STRATEGY_PATCH;
     if (!tile_feasible(ctx, tp, false)) return MV3D_STRATEGY_ATOMIC;
     return MV3D_STRATEGY_TILE;  // AUTO is refined per call by the batch size (see resolve_for_batch)
@@ -537,6 +538,29 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
             CUDA_TRY(cudaGetLastError());
             return 0;
         }
+    } else if (p.want_top && cells > 0 && strategy == MV3D_STRATEGY_SORT) {
+        const unsigned invalid_key = sort_invalid_key(p, batch);
+        if (p.py || invalid_key == 0u)
+            return fail("sort strategy: %d x %d x %d cells x %d sweeps do not fit a 32-bit key", p.xn, p.yn, p.zn, batch);
+        if (ensure(ws.keys, total * 8 + 16, false, s)) return -1;
+        if (ensure(ws.binned, total * 8 + 16, false, s)) return -1;
+        const size_t temp_bytes = sort_temp_bytes(total, invalid_key);
+        if (ensure(ws.sort_temp, temp_bytes + 16, false, s)) return -1;
+        unsigned *keys_in = static_cast<unsigned *>(ws.keys.ptr), *vals_in = keys_in + total;
+        unsigned *keys_out = static_cast<unsigned *>(ws.binned.ptr), *vals_out = keys_out + total;
+        timed_launch(ctx, K_SORT_KEYS, s, [&] {
+            return launch_sort_keys(pts, offs, p, batch, max_points, keys_in, vals_in, winners, invalid_key, s);
+        });
+        timed_launch(ctx, K_RADIX_SORT, s, [&] {
+            return launch_sort_pairs(ws.sort_temp.ptr, temp_bytes, keys_in, keys_out, vals_in, vals_out, total, invalid_key, s);
+        });
+        ctx->kernel_launches[K_RADIX_SORT]++;
+        timed_launch(ctx, K_FILL_ZERO, s, [&] {
+            return launch_fill_zero(top_dev, (size_t)batch * (size_t)p.top_frame_floats, ctx->sm_count, s);
+        });
+        timed_launch(ctx, K_SORT_REDUCE, s, [&] {
+            return launch_sort_reduce(pts, offs, p, ctx->lut, keys_out, vals_out, total, invalid_key, top_dev, s);
+        });
     } else if (p.want_top && cells > 0) {
         if (ensure(ws.cellkey, (size_t)batch * cells * 8, false, s)) return -1;
         unsigned long long *cellkey = static_cast<unsigned long long *>(ws.cellkey.ptr);

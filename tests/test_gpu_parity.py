@@ -60,7 +60,7 @@ def test_clidar_to_top_flip(oracle_mod):
 
 
 # ---- the batched device entry point ----------------------------------------------------------------------
-@pytest.mark.parametrize("strategy", ["tile", "patch", "atomic"])
+@pytest.mark.parametrize("strategy", ["tile", "patch", "atomic", "sort"])
 @pytest.mark.parametrize("semantics", ["top", "topfront"])
 def test_batched_device_ragged(torch_cuda, oracle_mod, strategy, semantics):
     """Ragged batch on the real grid: full sweeps, an empty sweep, a single point, a hot cell."""
@@ -88,7 +88,7 @@ def test_batched_device_ragged(torch_cuda, oracle_mod, strategy, semantics):
     enc.close()
 
 
-@pytest.mark.parametrize("strategy", ["tile", "patch", "atomic"])
+@pytest.mark.parametrize("strategy", ["tile", "patch", "atomic", "sort"])
 @pytest.mark.parametrize("name,pts,top,front", cases.small_cases(), ids=[c[0] for c in cases.small_cases()])
 def test_batched_device_small_grids(torch_cuda, oracle_mod, strategy, name, pts, top, front):
     torch = torch_cuda
@@ -147,7 +147,7 @@ def test_config2_batch64_bit_exact(torch_cuda, oracle_mod):
     enc.close()
 
 
-@pytest.mark.parametrize("strategy", ["tile", "patch", "atomic"])
+@pytest.mark.parametrize("strategy", ["tile", "patch", "atomic", "sort"])
 def test_config5_dense_cloud(torch_cuda, oracle_mod, strategy):
     """BASELINE config 5: 2 M points, 1408x1600x(8+2) at 0.05 m -- the high-contention case."""
     torch = torch_cuda

@@ -148,7 +148,7 @@ def main():
     d = torch.from_numpy(pts).cuda()
     top = torch.empty((B, *DENSE_TOP.shape), dtype=torch.float32, device="cuda")
     by = 16 * len(pts) + B * 4 * int(np.prod(DENSE_TOP.shape))
-    for strategy in ("tile", "atomic", "patch"):
+    for strategy in ("tile", "atomic", "patch", "sort"):
         enc = ViewEncoder(0, semantics="top", strategy=strategy)
         ms, k = timed(enc, lambda: enc.encode_device(d, offs, DENSE_TOP, top_out=top), args.steps)
         print(json.dumps({"config": 5, "what": "2 M-point cloud, BEV 1408x1600x(8+2) at 0.05 m, 8 clouds per launch",
