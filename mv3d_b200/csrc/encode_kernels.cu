@@ -336,7 +336,10 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
 #define MV3D_RECORDS_IN_FLIGHT 2
 #endif
 constexpr int kRecordsInFlight = MV3D_RECORDS_IN_FLIGHT;  // records of a heavy tile each thread fetches before reducing them
-template <bool kCompact, bool kOccupancy, bool kPy, int kStore = kStoreTmaHint>
+// kInFlight: records of a heavy tile each thread fetches before reducing them. Two pay for the plain C-routine kernel
+// (+1.6 %); the occupancy-reporting and Python-twin variants are faster with one (measured: -6.5 % / -0.5 % with two).
+template <bool kCompact, bool kOccupancy, bool kPy, int kStore = kStoreTmaHint,
+          int kInFlight = (kCompact || kOccupancy || kPy) ? 1 : kRecordsInFlight>
 __device__ __forceinline__ void
 tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, const FrameOffsets &offs,
           const ViewParams &p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
@@ -443,13 +446,13 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 }
             };
             if (tid < n0) accumulate(q0);
-            for (int r = tid + kTileThreads; r < n0; r += kRecordsInFlight * kTileThreads) {
-                uint4 q[kRecordsInFlight];
+            for (int r = tid + kTileThreads; r < n0; r += kInFlight * kTileThreads) {
+                uint4 q[kInFlight];
 #pragma unroll
-                for (int j = 0; j < kRecordsInFlight; j++)
+                for (int j = 0; j < kInFlight; j++)
                     if (r + j * kTileThreads < n0) q[j] = __ldg(rec0 + r + j * kTileThreads);
 #pragma unroll
-                for (int j = 0; j < kRecordsInFlight; j++)
+                for (int j = 0; j < kInFlight; j++)
                     if (r + j * kTileThreads < n0) accumulate(q[j]);
             }
             __syncthreads();
@@ -466,13 +469,13 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 }
             };
             if (tid < n0) claim(q0);
-            for (int r = tid + kTileThreads; r < n0; r += kRecordsInFlight * kTileThreads) {
-                uint4 q[kRecordsInFlight];
+            for (int r = tid + kTileThreads; r < n0; r += kInFlight * kTileThreads) {
+                uint4 q[kInFlight];
 #pragma unroll
-                for (int j = 0; j < kRecordsInFlight; j++)
+                for (int j = 0; j < kInFlight; j++)
                     if (r + j * kTileThreads < n0) q[j] = __ldg(rec0 + r + j * kTileThreads);
 #pragma unroll
-                for (int j = 0; j < kRecordsInFlight; j++)
+                for (int j = 0; j < kInFlight; j++)
                     if (r + j * kTileThreads < n0) claim(q[j]);
             }
             for (int d = warp; d < nd; d += kWarps) {  // one warp per touched cell, lanes over planes
