@@ -188,6 +188,9 @@ int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int num, const
  * dst[cells][planes] is zero-filled by `threads` host threads, then every entry {cell, planes values}
  * (planes + 1 words each) is copied to dst[cell]; entries with cell >= cells are ignored. */
 int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n, int threads);
+/* Same result in the two steps the first sweep of a host call takes (zero-fill while the GPU encodes, then a scatter
+ * of the finished values). */
+int mv3d_debug_expand_split(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n, int threads);
 
 /* The strategy a request resolves to for a parameter set (tile strategies fall back to _ATOMIC when a tile
  * cannot fit shared memory). AUTO additionally switches _TILE to _PATCH per call for large batches. */

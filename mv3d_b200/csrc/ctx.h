@@ -113,6 +113,7 @@ struct mv3d_ctx {
     HostSlot slots[kSlots];  // used by mv3d_encode_batch_host
     std::unique_ptr<mv3d::HostPool> pool;  // host threads of the compact read-back (created on first use)
     int host_threads = 0;
+    int host_split_first = 1; // first sweep of a host call: zero-fill while the GPU encodes, scatter afterwards (MV3D_HOST_SPLIT_FIRST=0: one pass)
     int host_compact = 1;    // MV3D_HOST_READBACK=dense switches the host entry points back to a dense D2H copy
     unsigned long long h2d_bytes = 0, d2h_bytes = 0;  // moved by the host entry points since the last reset
     unsigned compact_est = 0;  // entries the previous sweep produced: sizes the speculative copy of the next one

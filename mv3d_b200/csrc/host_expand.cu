@@ -173,6 +173,41 @@ static void store_fence()
 #endif
 }
 
+void zero_fill(HostPool &pool, float *dst, size_t floats)
+{
+    if (!dst || floats == 0) return;
+    const int parts = pool.size() * 2;
+    const size_t bytes = floats * 4;
+    const size_t per = ((bytes + parts - 1) / parts + 63) & ~(size_t)63;
+    const std::function<void(int)> body = [&](int part) {
+        const size_t b0 = (size_t)part * per;
+        if (b0 >= bytes) return;
+        zero_stream(reinterpret_cast<char *>(dst) + b0, (b0 + per < bytes) ? per : bytes - b0);
+        store_fence();
+    };
+    pool.parallel_for(parts, body);
+}
+
+void scatter_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
+                     unsigned n, const std::function<void()> *caller_first)
+{
+    if (!dst || cells == 0 || planes <= 0 || n == 0) {
+        if (caller_first) (*caller_first)();
+        return;
+    }
+    const int parts = pool.size() * 2;
+    const unsigned per = (n + parts - 1) / parts;
+    const size_t cell_bytes = (size_t)planes * 4;
+    const std::function<void(int)> body = [&](int part) {  // a cell appears at most once: no two threads share bytes
+        const unsigned i0 = (unsigned)part * per, i1 = (i0 + per < n) ? i0 + per : n;
+        for (unsigned i = i0; i < i1; i++) {
+            const size_t cell = idx[i];
+            if (cell < cells) memcpy(reinterpret_cast<char *>(dst) + cell * cell_bytes, vals + (size_t)i * planes, cell_bytes);
+        }
+    };
+    pool.parallel_for(parts, body, caller_first);
+}
+
 void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
                     unsigned n, const unsigned *tile_off, int tiles, int tile_cells,
                     const std::function<void()> *caller_first)

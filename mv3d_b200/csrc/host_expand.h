@@ -48,4 +48,10 @@ void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const 
                     unsigned n, const unsigned *tile_off = nullptr, int tiles = 0, int tile_cells = 0,
                     const std::function<void()> *caller_first = nullptr);
 
+// The same result in two steps, for a call that has nothing else to overlap with (one sweep per call, the reference
+// symbols): zero_fill runs while the GPU is still encoding, scatter_compact places the finished values afterwards.
+void zero_fill(HostPool &pool, float *dst, size_t floats);
+void scatter_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
+                     unsigned n, const std::function<void()> *caller_first = nullptr);
+
 } // namespace mv3d

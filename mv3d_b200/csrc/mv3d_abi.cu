@@ -115,6 +115,7 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     ctx->patch_min_batch = pm ? atoi(pm) : 1 << 30;
     const char *ht = getenv("MV3D_HOST_THREADS");
     ctx->host_threads = ht ? atoi(ht) : 0;
+    if (const char *hs = getenv("MV3D_HOST_SPLIT_FIRST")) ctx->host_split_first = atoi(hs);
     const char *hr = getenv("MV3D_HOST_READBACK");
     ctx->host_compact = (hr && strcmp(hr, "dense") == 0) ? 0 : 1;
     if (const char *ab = getenv("MV3D_AUTO_ATOMIC_BATCH")) ctx->auto_atomic_batch = atoi(ab);
@@ -785,6 +786,14 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
     t_enq += now() - t0;
     for (int i = 0; i < batch; i++) {
         HostSlot &slot = ctx->slots[i % kSlots];
+        // The first sweep of a call has no earlier sweep to rebuild while the GPU works (for the reference symbols,
+        // one sweep per call, that is the whole call): zero-fill its view meanwhile, scatter the values afterwards.
+        const bool split = i == 0 && ctx->host_split_first;
+        if (split) {
+            t0 = now();
+            zero_fill(*ctx->pool, top_host, (size_t)p.top_frame_floats);
+            t_expand += now() - t0;
+        }
         t0 = now();
         CUDA_TRY(cudaEventSynchronize(slot.done));
         t_wait += now() - t0;
@@ -815,8 +824,11 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
             t_enq += now() - t1;
         };
         t0 = now();
-        expand_compact(*ctx->pool, top_host + (size_t)i * (size_t)p.top_frame_floats, cells, p.planes, stage,
-                       stage + cap, used, toff, p.tiles_per_frame, p.tile_cells, &errand);
+        if (split)
+            scatter_compact(*ctx->pool, top_host, cells, p.planes, stage, stage + cap, used, &errand);
+        else
+            expand_compact(*ctx->pool, top_host + (size_t)i * (size_t)p.top_frame_floats, cells, p.planes, stage,
+                           stage + cap, used, toff, p.tiles_per_frame, p.tile_cells, &errand);
         t_expand += now() - t0;
         if (enq_rc) return -1;
     }
@@ -1205,6 +1217,21 @@ extern "C" int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, c
     }
     HostPool pool(threads);
     expand_compact(pool, dst, cells, planes, idx.data(), vals.data(), n, nullptr, 0, 0, nullptr);
+    return 0;
+}
+
+extern "C" int mv3d_debug_expand_split(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n,
+                                       int threads)
+{
+    if (!dst || planes <= 0 || (n && !entries)) return fail("mv3d_debug_expand_split: bad arguments");
+    std::vector<unsigned> idx(n), vals((size_t)n * planes);
+    for (unsigned i = 0; i < n; i++) {
+        idx[i] = entries[(size_t)i * (planes + 1)];
+        memcpy(vals.data() + (size_t)i * planes, entries + (size_t)i * (planes + 1) + 1, (size_t)planes * 4);
+    }
+    HostPool pool(threads);
+    zero_fill(pool, dst, cells * (size_t)planes);
+    scatter_compact(pool, dst, cells, planes, idx.data(), vals.data(), n, nullptr);
     return 0;
 }
 

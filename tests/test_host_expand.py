@@ -4,14 +4,14 @@ import numpy as np
 import pytest
 
 
-def _expand(lib, cells, planes, idx, vals, threads, offset_floats=0, garbage=7.0):
+def _expand(lib, cells, planes, idx, vals, threads, offset_floats=0, garbage=7.0, split=False):
     buf = np.full(cells * planes + offset_floats + 8, garbage, dtype=np.float32)
     dst = buf[offset_floats:offset_floats + cells * planes]
     entries = np.empty((len(idx), planes + 1), dtype=np.uint32)
     entries[:, 0] = idx
     entries[:, 1:] = vals.view(np.uint32)
-    rc = lib.mv3d_debug_expand_compact(dst.ctypes.data, cells, planes, entries.ctypes.data if len(idx) else None,
-                                       len(idx), threads)
+    fn = lib.mv3d_debug_expand_split if split else lib.mv3d_debug_expand_compact
+    rc = fn(dst.ctypes.data, cells, planes, entries.ctypes.data if len(idx) else None, len(idx), threads)
     assert rc == 0
     # nothing outside the tensor is touched
     assert (buf[:offset_floats] == garbage).all() and (buf[offset_floats + cells * planes:] == garbage).all()
@@ -30,6 +30,9 @@ def test_expand_matches_numpy_scatter(encoder_lib, threads, cells, planes):
     for offset in (0, 1, 3):  # 16-byte aligned and misaligned destinations
         got = _expand(encoder_lib, cells, planes, idx, vals, threads, offset_floats=offset)
         assert np.array_equal(got, expect)
+        # the two-step form the first sweep of a host call takes (zero-fill during the GPU's work, then scatter)
+        got = _expand(encoder_lib, cells, planes, idx, vals, threads, offset_floats=offset, split=True)
+        assert np.array_equal(got, expect)
 
 
 def test_expand_empty_and_out_of_range(encoder_lib):
@@ -37,10 +40,11 @@ def test_expand_empty_and_out_of_range(encoder_lib):
     assert not got.any()
     idx = np.array([3, 100, 0xFFFFFFFF, 99], np.uint32)  # 100 and 0xFFFFFFFF are out of range: ignored
     vals = np.arange(20, dtype=np.float32).reshape(4, 5) + 1
-    got = _expand(encoder_lib, 100, 5, idx, vals, 4)
     expect = np.zeros((100, 5), np.float32)
     expect[3], expect[99] = vals[0], vals[3]
-    assert np.array_equal(got, expect)
+    for split in (False, True):
+        assert np.array_equal(_expand(encoder_lib, 100, 5, idx, vals, 4, split=split), expect)
+        assert not _expand(encoder_lib, 100, 5, np.zeros(0, np.uint32), np.zeros((0, 5), np.float32), 4, split=split).any()
 
 
 def test_expand_preserves_nan_and_bit_patterns(encoder_lib):
