@@ -97,10 +97,11 @@ typedef struct mv3d_ctx mv3d_ctx;
 
 /* Creates a per-GPU context (workspace grows on demand, density table, stream pool). 0 on success.
  * Concurrency: every entry point may be called from any thread (calls on one context are serialised by a mutex).
- * The asynchronous device entry points (`*_dev`, `void *stream` argument) share the context's scratch buffers: the
- * work of successive calls on ONE context must be ordered on the device -- use one stream, or make the next call's
- * stream wait for the previous one. For independent concurrent streams create one context per stream
- * (mv3d_b200/stream.py does exactly that for its ring of slots). */
+ * The asynchronous device entry points (`*_dev`, `void *stream` argument) share the context's scratch buffers, so the
+ * library orders the work of successive calls on ONE context on the device: a call on a different stream than the
+ * previous one first waits (cudaStreamWaitEvent, no host blocking) for that call to finish. Results are correct from
+ * any thread and any stream; for work that should really overlap create one context per stream (mv3d_b200/stream.py
+ * does exactly that for its ring of slots). */
 int mv3d_ctx_create(int device, mv3d_ctx **out);
 void mv3d_ctx_destroy(mv3d_ctx *ctx);
 

@@ -145,6 +145,7 @@ extern "C" int mv3d_remove_empty_anchor_dev(mv3d_ctx *ctx, const float *views_de
     if (frames > 65535) return fail("mv3d_remove_empty_anchor_dev: at most 65535 frames per call (got %d)", frames);
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
+    StreamOrder order(ctx, static_cast<cudaStream_t>(stream));
     return filter_locked(ctx, views_dev, frames, xn, yn, planes, limit, mode, keep_dev, count_dev, totals_dev,
                          static_cast<cudaStream_t>(stream));
 }
@@ -166,6 +167,7 @@ extern "C" int mv3d_remove_empty_anchor_host(mv3d_ctx *ctx, const float *view_ho
     CUDA_TRY(cudaSetDevice(ctx->device));
     AnchorState &st = ctx->anchors;
     cudaStream_t s = nullptr;  // the legacy default stream: this call returns only when its results are on the host
+    StreamOrder order(ctx, s);
     const size_t view_bytes = (size_t)xn * yn * planes * sizeof(float);
     if (ensure(st.view, view_bytes, false, s)) return -1;
     if (ensure(st.idx, (size_t)n * sizeof(int), false, s)) return -1;

@@ -138,7 +138,30 @@ struct mv3d_ctx {
     int sub_batch = 0;                    // sweeps per pipeline stage of the tile strategy (0 = no pipelining)
     cudaStream_t side_stream = nullptr;   // runs the point passes ahead of the tile kernel
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_ready[kMaxBatchPerLaunch] = {nullptr};
+    cudaEvent_t ev_order = nullptr;       // end of the latest device call on this context (see StreamOrder)
+    cudaStream_t order_stream = nullptr;
+    bool order_valid = false;
     std::mutex mu;
+};
+
+// Successive device calls on one context share its scratch buffers, so their work must not overlap on the device.
+// Calls on the same stream are ordered anyway; a call on another stream first waits (on the device, not the host) for
+// the end of the previous call. Construct under ctx->mu, after cudaSetDevice.
+struct StreamOrder {
+    mv3d_ctx *ctx;
+    cudaStream_t s;
+    StreamOrder(mv3d_ctx *c, cudaStream_t stream) : ctx(c), s(stream)
+    {
+        if (!ctx->ev_order) cudaEventCreateWithFlags(&ctx->ev_order, cudaEventDisableTiming);
+        if (ctx->ev_order && ctx->order_valid && ctx->order_stream != s) cudaStreamWaitEvent(s, ctx->ev_order, 0);
+    }
+    ~StreamOrder()
+    {
+        if (!ctx->ev_order) return;
+        cudaEventRecord(ctx->ev_order, s);
+        ctx->order_stream = s;
+        ctx->order_valid = true;
+    }
 };
 
 inline int ensure(DeviceBuffer &b, size_t bytes, bool zero, cudaStream_t s)

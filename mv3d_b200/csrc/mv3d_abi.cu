@@ -177,6 +177,7 @@ extern "C" void mv3d_ctx_destroy(mv3d_ctx *ctx)
     if (ctx->lut) cudaFree(ctx->lut);
     if (ctx->lut_py) cudaFree(ctx->lut_py);
     if (ctx->side_stream) cudaStreamDestroy(ctx->side_stream);
+    if (ctx->ev_order) cudaEventDestroy(ctx->ev_order);
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     for (auto e : ctx->ev_ready) if (e) cudaEventDestroy(e);
@@ -672,6 +673,7 @@ extern "C" int mv3d_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, con
     if (batch == 0 || (!top_dev && !front_dev)) return 0;
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
+    StreamOrder order(ctx, static_cast<cudaStream_t>(stream));
     return encode_dev_locked(ctx, ctx->ws, points_dev, offsets_host, batch, top_dev, front_dev, p, strat,
                              static_cast<cudaStream_t>(stream));
 }
@@ -1029,6 +1031,7 @@ extern "C" int mv3d_pytwin_encode_batch_dev(mv3d_ctx *ctx, const float *points_d
     if (batch == 0 || (!top_dev && !front_dev)) return 0;
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
+    StreamOrder order(ctx, static_cast<cudaStream_t>(stream));
     return py_encode_dev_locked(ctx, ctx->ws, points_dev, offsets_host, batch, top_dev, front_dev, p, fp,
                                 static_cast<cudaStream_t>(stream));
 }
@@ -1088,6 +1091,7 @@ extern "C" int mv3d_encode_filter_batch_dev(mv3d_ctx *ctx, const float *points_d
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    StreamOrder order(ctx, s);
     AnchorPlan plan;
     OccupancySink sink;
     const bool fused = strat == MV3D_STRATEGY_TILE && ctx->anchors.n > 0;
@@ -1118,6 +1122,7 @@ extern "C" int mv3d_pytwin_encode_filter_batch_dev(mv3d_ctx *ctx, const float *p
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
     cudaStream_t s = static_cast<cudaStream_t>(stream);
+    StreamOrder order(ctx, s);
     AnchorPlan plan;
     OccupancySink sink;
     const bool fused = ctx->anchors.n > 0;  // the Python-twin mode always runs the tile strategy
