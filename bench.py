@@ -136,13 +136,16 @@ def cpu_baseline(top, front):
         pool.run([f % BATCH for f in warm])
         frames = [f % BATCH for f in range(pool.cores * 8)]
         wall, per_call = pool.run(frames)
+        # SURVEY.md 8(d), CPU baseline (1): one process at a time on an otherwise idle host, median of 10 calls
+        alone = sorted(pool.run([f])[1][0] for f in range(10))
     finally:
         pool.close()
     per_call.sort()
     return {"value": len(frames) / wall, "unit": "sweeps/s", "cores": pool.cores, "kind": pool.kind,
             "sample": f"{len(frames)} sweeps (8 per core) of the config-1 sweep set, BEV+FV via "
                       f"createTopAndFrontMaps, multiprocessing.Pool({pool.cores}); median {per_call[len(per_call) // 2] * 1e3:.1f} ms/call/core",
-            "ms_per_call_median": per_call[len(per_call) // 2] * 1e3}
+            "ms_per_call_median": per_call[len(per_call) // 2] * 1e3,
+            "single_process_ms_per_call_median": alone[len(alone) // 2] * 1e3}
 
 
 def run_reference(args):
@@ -279,12 +282,20 @@ def run_ours(args):
     torch.cuda.synchronize()
     if rank == 0:
         sampler.start()
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps - 1)]  # between steps: no synchronisation
     ev0.record()
-    for _ in range(args.steps):
+    for k in range(args.steps):
         step()
+        if k < args.steps - 1:
+            marks[k].record()
     ev1.record()
     torch.cuda.synchronize()
     barrier()
+    edges = [ev0] + marks + [ev1]
+    per_step = sorted(edges[k].elapsed_time(edges[k + 1]) for k in range(args.steps))
+
+    def pct(q):
+        return per_step[min(len(per_step) - 1, max(0, int(round(q * (len(per_step) - 1)))))]
     clocks = sampler.stop() if rank == 0 else None
     elapsed_ms = ev0.elapsed_time(ev1)
     launches = enc.launch_count - launches0
@@ -366,6 +377,8 @@ def run_ours(args):
                    "strategy": strategy, "sharding": f"frame i -> rank i mod {world}, no collective",
                    "l2": "each step writes 3.9 GB of output per GPU (>> 126 MB L2), so no step starts with a warm L2"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
+        "step_ms": {"median": pct(0.5), "p5": pct(0.05), "p95": pct(0.95), "min": per_step[0], "max": per_step[-1],
+                    "what": "rank 0, CUDA events between the steps of the timed region"},
     }
     if cpu is not None:
         line["cpu_baseline"] = cpu

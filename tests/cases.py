@@ -96,3 +96,34 @@ def sweep_cases(frames=(0, 1)):
     cases.append(("hdl64_0_didi", s0, REFERENCE_DIDI_TOP, FrontParams(-20.0, 20.0, -45.0, 45.0, 0.1, 0.2)))
     cases.append(("uniform_in_box", uniform_in_box(120000, KITTI_PAPER_TOP, seed=5), KITTI_PAPER_TOP, KITTI_FRONT_64x512))
     return cases
+
+
+def fuzz_cases(count=40, seed=2024):
+    """Random parameter sets and clouds: odd plane counts (tiles that are not a multiple of 16 bytes), one-cell and
+    no-slice grids, negative origins, coordinates sitting on cell and bin boundaries, ties, non-finite rows."""
+    rng = np.random.default_rng(seed)
+    divs = [0.05, 0.1, 0.2, 0.25, 0.3, 0.37, 0.5, 1.0]
+    out = []
+    for k in range(count):
+        xn, yn, zn = int(rng.integers(1, 48)), int(rng.integers(1, 56)), int(rng.integers(0, 34))
+        xd, yd, zd = (float(np.float32(rng.choice(divs))) for _ in range(3))
+        x0, y0, z0 = (float(np.float32(rng.uniform(-20.0, 5.0))) for _ in range(3))
+        top = TopParams(x0, x0 + xn * xd, y0, y0 + yn * yd, z0, z0 + max(zn, 1) * zd, xd, yd, zd, xn, yn, zn)
+        rn, cn = int(rng.integers(1, 40)), int(rng.integers(1, 64))
+        front = FrontParams(-20.0, 20.0, -45.0, 45.0, float(np.float32(rng.uniform(0.3, 6.0))),
+                            float(np.float32(rng.uniform(0.3, 6.0))), rn, cn, 3)
+        n = int(rng.choice([0, 1, 17, 300, 5000]))
+        pts = np.empty((n, 4), np.float32)
+        for a, (lo, d, cnt) in enumerate(((x0, xd, xn), (y0, yd, yn), (z0, zd, max(zn, 1)))):
+            pts[:, a] = rng.uniform(lo - 2 * d, lo + (cnt + 2) * d, n)
+        pts[:, 3] = rng.random(n)
+        if n >= 17:
+            snap = rng.random(n) < 0.3  # on cell boundaries: lo + j * div evaluated in float32
+            for a, (lo, d) in enumerate(((x0, xd), (y0, yd), (z0, zd))):
+                j = np.round((pts[snap, a] - np.float32(lo)) / np.float32(d))
+                pts[snap, a] = np.float32(lo) + j.astype(np.float32) * np.float32(d)
+            dup = rng.integers(0, n, n // 8)  # ties: copies of earlier points with another intensity
+            pts[dup[: len(dup) // 2], :3] = pts[dup[len(dup) // 2: 2 * (len(dup) // 2)], :3]
+            pts[rng.integers(0, n, 3), rng.integers(0, 4, 3)] = [np.nan, np.inf, -np.inf]
+        out.append((f"fuzz{k}_{xn}x{yn}x{zn}_n{n}", pts, top, front))
+    return out

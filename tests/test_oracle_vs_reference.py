@@ -8,7 +8,7 @@ import pytest
 import cases
 from mv3d_b200.params import KITTI_FRONT_64x512, KITTI_PAPER_TOP
 
-ALL_CASES = cases.quirk_cases() + cases.small_cases() + cases.sweep_cases()
+ALL_CASES = cases.quirk_cases() + cases.small_cases() + cases.sweep_cases() + cases.fuzz_cases()
 
 
 def _needs_ref(oracle_mod):
