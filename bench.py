@@ -292,10 +292,10 @@ def run_ours(args):
     torch.cuda.synchronize()
     barrier()
     edges = [ev0] + marks + [ev1]
-    per_step = sorted(edges[k].elapsed_time(edges[k + 1]) for k in range(args.steps))
+    step_times = sorted(edges[k].elapsed_time(edges[k + 1]) for k in range(args.steps))
 
     def pct(q):
-        return per_step[min(len(per_step) - 1, max(0, int(round(q * (len(per_step) - 1)))))]
+        return step_times[min(len(step_times) - 1, max(0, int(round(q * (len(step_times) - 1)))))]
     clocks = sampler.stop() if rank == 0 else None
     elapsed_ms = ev0.elapsed_time(ev1)
     launches = enc.launch_count - launches0
@@ -377,7 +377,7 @@ def run_ours(args):
                    "strategy": strategy, "sharding": f"frame i -> rank i mod {world}, no collective",
                    "l2": "each step writes 3.9 GB of output per GPU (>> 126 MB L2), so no step starts with a warm L2"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-        "step_ms": {"median": pct(0.5), "p5": pct(0.05), "p95": pct(0.95), "min": per_step[0], "max": per_step[-1],
+        "step_ms": {"median": pct(0.5), "p5": pct(0.05), "p95": pct(0.95), "min": step_times[0], "max": step_times[-1],
                     "what": "rank 0, CUDA events between the steps of the timed region"},
     }
     if cpu is not None:

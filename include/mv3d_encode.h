@@ -185,6 +185,13 @@ int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int num, const
                           const mv3d_front_params *fp, int semantics, int *cell_dev, int *pix_dev,
                           int *pix_exact_dev, void *stream);
 
+/* Per-frame checksum of device-resident views -- the consumer of a streamed run whose encoded tensors never leave the
+ * GPU (BASELINE config 4: 4096 x 60.8 MB through a ring of output slots). sums_dev[f] = sum of the 32-bit words of
+ * frame f modulo 2^64: exact and order-independent, so equal views give equal sums on any rank; compare with
+ * numpy: view.view(np.uint32).astype(np.uint64).sum(). Enqueues on `stream` (one streaming read of the views). */
+int mv3d_frame_checksums_dev(mv3d_ctx *ctx, const float *views_dev, int frames, long long floats_per_frame,
+                             unsigned long long *sums_dev, void *stream);
+
 /* Test hook (no GPU needed): the host half of the compact read-back used by the host-buffer entry points.
  * dst[cells][planes] is zero-filled by `threads` host threads, then every entry {cell, planes values}
  * (planes + 1 words each) is copied to dst[cell]; entries with cell >= cells are ignored. */

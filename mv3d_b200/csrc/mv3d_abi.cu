@@ -1209,6 +1209,70 @@ extern "C" int mv3d_debug_atan2f(mv3d_ctx *ctx, const float *y_dev, const float 
     return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// per-frame checksum of device-resident views: the consumer of the streamed configuration (BASELINE config 4), where
+// 4096 x 60.8 MB of output are never resident at once and never leave the GPU. Sum of the 32-bit words of a frame
+// modulo 2^64: exact, independent of the order of summation, so equal views give equal sums on any rank.
+// One streaming read of the views: 16-byte loads, four in flight per thread.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+frame_checksum_kernel(const float *__restrict__ views, long long floats_per_frame, unsigned long long *__restrict__ sums)
+{
+    const unsigned *w = reinterpret_cast<const unsigned *>(views) + (size_t)blockIdx.y * (size_t)floats_per_frame;
+    unsigned long long acc = 0ull;
+    // leading words up to 16-byte alignment, then vectors, then the tail
+    const size_t mis = (size_t)((16u - ((unsigned)(reinterpret_cast<uintptr_t>(w)) & 15u)) & 15u) / 4;
+    const size_t head = mis < (size_t)floats_per_frame ? mis : (size_t)floats_per_frame;
+    const size_t nvec = ((size_t)floats_per_frame - head) / 4;
+    const uint4 *v = reinterpret_cast<const uint4 *>(w + head);
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < nvec; i += 4 * stride) {
+        const uint4 a = __ldcs(v + i), b = __ldcs(v + i + stride), c = __ldcs(v + i + 2 * stride), d = __ldcs(v + i + 3 * stride);
+        acc += (unsigned long long)a.x + a.y + a.z + a.w;
+        acc += (unsigned long long)b.x + b.y + b.z + b.w;
+        acc += (unsigned long long)c.x + c.y + c.z + c.w;
+        acc += (unsigned long long)d.x + d.y + d.z + d.w;
+    }
+    for (; i < nvec; i += stride) {
+        const uint4 a = __ldcs(v + i);
+        acc += (unsigned long long)a.x + a.y + a.z + a.w;
+    }
+    if (blockIdx.x == 0) {
+        for (size_t k = threadIdx.x; k < head; k += blockDim.x) acc += w[k];
+        for (size_t k = head + nvec * 4 + threadIdx.x; k < (size_t)floats_per_frame; k += blockDim.x) acc += w[k];
+    }
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_down_sync(0xFFFFFFFFu, acc, o);
+    if ((threadIdx.x & 31) == 0 && acc) atomicAdd(sums + blockIdx.y, acc);
+}
+
+extern "C" int mv3d_frame_checksums_dev(mv3d_ctx *ctx, const float *views_dev, int frames, long long floats_per_frame,
+                                        unsigned long long *sums_dev, void *stream)
+{
+    if (!ctx) return fail("mv3d_frame_checksums_dev: ctx is NULL");
+    if (frames < 0 || floats_per_frame < 0) return fail("mv3d_frame_checksums_dev: negative size");
+    if (frames == 0) return 0;
+    if (!sums_dev || (floats_per_frame > 0 && !views_dev)) return fail("mv3d_frame_checksums_dev: NULL buffer");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    CUDA_TRY(cudaMemsetAsync(sums_dev, 0, (size_t)frames * sizeof(unsigned long long), s));
+    if (floats_per_frame > 0) {
+        for (int f0 = 0; f0 < frames; f0 += 32768) {
+            const int nf = frames - f0 < 32768 ? frames - f0 : 32768;
+            long long want = (floats_per_frame / 4 + 256 * 16 - 1) / (256 * 16);  // ~16 vectors per thread
+            const long long cap = ((long long)ctx->sm_count * 8 + nf - 1) / nf;  // about eight CTAs per SM over all frames
+            int bx = (int)(want < 1 ? 1 : (want > cap ? cap : want));
+            if (bx < 1) bx = 1;
+            frame_checksum_kernel<<<dim3(bx, nf), 256, 0, s>>>(views_dev + (size_t)f0 * (size_t)floats_per_frame,
+                                                                floats_per_frame, sums_dev + f0);
+            ctx->launches++;
+        }
+    }
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
 // Test hook for the host half of the compact read-back (needs no GPU).
 extern "C" int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n,
                                          int threads)

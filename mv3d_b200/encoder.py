@@ -102,6 +102,23 @@ class ViewEncoder:
             raise RuntimeError("mv3d_encode_batch_dev: " + _lib.last_error())
         return (top_out if want_top else None), front_out
 
+    def frame_checksums(self, views, out=None, stream=None):
+        """Sum of the 32-bit words of every frame of a CUDA float32 tensor `[frames, ...]`, modulo 2^64, as an int64
+        CUDA tensor (the bit pattern of the unsigned sum): the on-device consumer of a streamed run."""
+        import torch
+        assert views.is_cuda and views.dtype == torch.float32 and views.is_contiguous()
+        frames = views.shape[0]
+        if out is None:
+            out = torch.empty(frames, dtype=torch.int64, device=views.device)
+        if stream is None:
+            stream = torch.cuda.current_stream(views.device).cuda_stream
+        per = views.numel() // frames if frames else 0
+        rc = self._lib.mv3d_frame_checksums_dev(self._ctx, views.data_ptr(), frames, per, out.data_ptr(),
+                                                ctypes.c_void_p(stream))
+        if rc != 0:
+            raise RuntimeError("mv3d_frame_checksums_dev: " + _lib.last_error())
+        return out
+
     def debug_point_keys(self, points, top: TopParams, front: FrontParams | None = None):
         """Test hook: per-point (cell, front pixel, front pixel by the all-double path) as int32 CUDA tensors."""
         import torch

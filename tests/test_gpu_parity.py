@@ -321,3 +321,20 @@ def test_stream_with_top_ragged_tail(torch_cuda, oracle_mod):
             got += 1
     assert got == len(frames)
     stream.close()
+
+
+@pytest.mark.parametrize("shape", [(3, 704, 800, 27), (5, 64, 512, 3), (4, 7, 3), (2, 1), (1, 1000003)])
+def test_frame_checksums_equal_numpy(torch_cuda, shape):
+    """The streamed configuration's consumer: per-frame sum of the 32-bit words modulo 2^64 (also on views whose
+    frames do not start on a 16-byte boundary)."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    enc = ViewEncoder(0)
+    g = torch.Generator(device="cuda").manual_seed(sum(shape))
+    x = torch.randn(shape, device="cuda", generator=g)
+    x[0].view(-1)[::3] = 0.0
+    x.view(-1)[-1] = float("nan")
+    got = enc.frame_checksums(x).cpu().numpy().view(np.uint64)
+    want = x.cpu().numpy().reshape(shape[0], -1).view(np.uint32).astype(np.uint64).sum(axis=1)
+    assert np.array_equal(got, want)
+    enc.close()
