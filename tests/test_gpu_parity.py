@@ -338,3 +338,35 @@ def test_frame_checksums_equal_numpy(torch_cuda, shape):
     want = x.cpu().numpy().reshape(shape[0], -1).view(np.uint32).astype(np.uint64).sum(axis=1)
     assert np.array_equal(got, want)
     enc.close()
+
+
+@pytest.mark.parametrize("strategy", ["tile", "patch", "atomic", "sort"])
+@pytest.mark.parametrize("pad", [0, 1, 4, 7])
+def test_outputs_inside_guard_bands(torch_cuda, oracle_mod, strategy, pad):
+    """compute-sanitizer is closed on this GPU pool, so out-of-bounds stores are hunted with guard bands: the outputs
+    are slices of larger sentinel-filled buffers, at 16-byte-aligned and misaligned offsets (the misaligned ones take
+    the tile kernel's plain-store path instead of the bulk store), and nothing outside the slice may change."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    top_p, front_p = KITTI_PAPER_TOP, KITTI_FRONT_64x512
+    sweeps = [hdl64_sweep(30)[:40000], hdl64_sweep(31)[:1], hdl64_sweep(32)[:70001], np.zeros((0, 4), np.float32)]
+    pts, offs = pack_sweeps(sweeps)
+    d = torch.from_numpy(pts).cuda()
+    nb = len(sweeps)
+    guard = 4096
+    nt, nf = nb * int(np.prod(top_p.shape)), nb * int(np.prod(front_p.shape))
+    big_t = torch.full((guard + pad + nt + guard,), -777.0, device="cuda")
+    big_f = torch.full((guard + pad + nf + guard,), -777.0, device="cuda")
+    top = big_t[guard + pad: guard + pad + nt].view(nb, *top_p.shape)
+    front = big_f[guard + pad: guard + pad + nf].view(nb, *front_p.shape)
+    enc = ViewEncoder(0, strategy=strategy)
+    enc.encode_device(d, offs, top_p, front_p, top_out=top, front_out=front)
+    torch.cuda.synchronize()
+    for big, n in ((big_t, nt), (big_f, nf)):
+        assert bool((big[: guard + pad] == -777.0).all()) and bool((big[guard + pad + n:] == -777.0).all()), \
+            f"{strategy} pad {pad}: wrote outside the output"
+    for i, s in enumerate(sweeps):
+        et, ef = oracle_mod.top_and_front_maps(s, top_p, front_p)
+        assert_same(top[i].cpu().numpy(), et, f"{strategy} pad {pad} sweep {i} top")
+        assert_same(front[i].cpu().numpy(), ef, f"{strategy} pad {pad} sweep {i} front")
+    enc.close()
