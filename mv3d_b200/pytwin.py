@@ -22,7 +22,7 @@ import numpy as np
 from . import _lib
 from .params import PYTWIN_KITTI, PyTwinParams
 
-__all__ = ["lidar_to_top", "lidar_to_front_fast", "PyTwinEncoder"]
+__all__ = ["lidar_to_top", "lidar_to_front_fast", "lidar_to_top_cuda", "lidar_to_front_cuda", "Preprocess", "PyTwinEncoder"]
 
 
 def _params_c(p: PyTwinParams) -> _lib.PyTwinParamsC:
@@ -139,3 +139,31 @@ def lidar_to_front_fast(lidar, params: PyTwinParams = PYTWIN_KITTI) -> np.ndarra
     lidar = np.ascontiguousarray(lidar, dtype=np.float32)
     _, front = _encoder().encode_host(lidar, [0, lidar.shape[0]], params, want_top=False)
     return front[0]
+
+
+# The names the reference's loaders import (`from net.utility.front_top_preprocess import lidar_to_top_cuda,
+# lidar_to_front_cuda`, src/utils/batch_loading.py:35; call sites :113, :427-428, :661-665). The pycuda twins promise
+# what their self-test asserts (src/net/utility/front_top_preprocess.py:213-215, 222-223): every height slice and the
+# density channel equal to `lidar_to_top`, the whole front view equal to `lidar_to_front_fast` -- which the functions
+# above deliver on every channel, the intensity included.
+lidar_to_top_cuda = lidar_to_top
+lidar_to_front_cuda = lidar_to_front_fast
+
+
+class Preprocess:
+    """The view-encoding methods of `data.Preprocess` (src/data.py:47-54, 113-180), same names and arguments.
+    `lidar_to_top` follows `cfg.USE_CLIDAR_TO_TOP` (src/data.py:49-52): False (the reference's default,
+    src/config.py:224) -> the Python encoder's semantics, True -> the C routine through `clidar_to_top`."""
+
+    def __init__(self, params: PyTwinParams = PYTWIN_KITTI, use_clidar_to_top: bool = False):
+        self.params = params
+        self.use_clidar_to_top = use_clidar_to_top
+
+    def lidar_to_top(self, lidar):
+        if self.use_clidar_to_top:
+            from .ver3 import clidar_to_top
+            return clidar_to_top(lidar)
+        return lidar_to_top(lidar, self.params)
+
+    def lidar_to_front_fast(self, lidar):
+        return lidar_to_front_fast(lidar, self.params)

@@ -132,3 +132,25 @@ def ctypes_transfer(enc):
     h2d, d2h = ctypes.c_ulonglong(), ctypes.c_ulonglong()
     assert enc._lib.mv3d_ctx_transfer_bytes(enc._ctx, ctypes.byref(h2d), ctypes.byref(d2h), 0) == 0
     return h2d.value, d2h.value
+
+
+def test_loader_names_pass_the_reference_self_test(pytwin):
+    """The reference's own equality asserts for its pycuda twins (src/net/utility/front_top_preprocess.py:211-223),
+    run against the drop-in names the loaders import, with the executed-reference golden outputs as ground truth."""
+    from mv3d_b200.pytwin import Preprocess, lidar_to_front_cuda, lidar_to_top_cuda
+    g = np.load(GOLDEN)
+    name, lidar, p = next(c for c in CASES if c[2] is PYTWIN_KITTI and len(c[1]) > 1000)
+    pro = Preprocess()
+    top = lidar_to_top_cuda(lidar)
+    top_gt = unpack(g, name, "top", p.top_shape)
+    assert top.shape == top_gt.shape
+    zn = p.top_shape[2] - 2
+    assert np.sum(top[..., 0:zn] != top_gt[..., 0:zn]) == 0
+    assert np.sum(top[..., zn + 1] != top_gt[..., zn + 1]) == 0
+    assert np.sum(top[..., zn] != top_gt[..., zn]) == 0  # the intensity too, which the pycuda twin does not promise
+    front = lidar_to_front_cuda(lidar)
+    front_gt = unpack(g, name, "front", p.front_shape)
+    assert front.shape == front_gt.shape
+    assert np.sum(front != front_gt) == 0
+    same(pro.lidar_to_top(lidar), top_gt, "Preprocess.lidar_to_top")
+    same(pro.lidar_to_front_fast(lidar), front_gt, "Preprocess.lidar_to_front_fast")
