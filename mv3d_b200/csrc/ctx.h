@@ -124,7 +124,7 @@ struct mv3d_ctx {
     int fill_ctas = 0;                    // fill CTAs per SM (one issuing thread each)
     int fill_pending = 0;                 // bulk stores each fill CTA keeps in flight (> 16: unbounded)
     int tile_store = 1;                   // MV3D_TILE_STORE: how the tile kernel writes a tile (1 = bulk stores, evict-first)
-    int auto_atomic_batch = 3;            // AUTO: up to this many sweeps per device call go to the atomic strategy
+    int auto_atomic_batch = 4;            // AUTO: up to this many sweeps per device call go to the atomic strategy
     double auto_atomic_ratio = 0.07;      // AUTO: ... and so do calls whose points weigh more than this share of the output bytes
     int patch_mode = 1;                   // MV3D_PATCH_MODE: 1 = copy-engine zero-fill + tile_patch_kernel, 0 = TMA fill kernel + warp_patch_kernel
     int pipe_groups = 0;                  // MV3D_TILE_PIPE=G[,threads[,chunk[,pending]]]: pipelined tile kernel (0 = off)

@@ -1209,21 +1209,30 @@ atomic_scatter_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPar
     unsigned *out = reinterpret_cast<unsigned *>(top + (size_t)f * p.top_frame_floats);
     unsigned long long *keys = cellkey + (size_t)f * ((size_t)p.xn * p.yn);
     unsigned *winners = fv_winner + (size_t)f * p.front_pixels;
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 pt = load_point(pts + base + i);
-        const CellHit c = classify(pt, p);
-        if (!c.keep) continue;
-        if (p.want_top) {
-            unsigned *cellw = out + (size_t)c.cell * p.planes;
-            atomicAdd(cellw + p.zn + 1, 1u);
-            if (c.h > 0.0f) {
-                atomicMax(cellw + c.slice, __float_as_uint(c.h) | kRawTag);
-                atomicMax(keys + c.cell, cell_key(c.h, (uint32_t)i));
+    // two points per thread and round: both loads are issued before the first atomic
+    const int stride = gridDim.x * blockDim.x;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 2 * stride) {
+        float4 pt[2];
+        pt[0] = load_point(pts + base + i0);
+        if (i0 + stride < n) pt[1] = load_point(pts + base + i0 + stride);
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            const int i = i0 + k * stride;
+            if (i >= n) continue;
+            const CellHit c = classify(pt[k], p);
+            if (!c.keep) continue;
+            if (p.want_top) {
+                unsigned *cellw = out + (size_t)c.cell * p.planes;
+                atomicAdd(cellw + p.zn + 1, 1u);
+                if (c.h > 0.0f) {
+                    atomicMax(cellw + c.slice, __float_as_uint(c.h) | kRawTag);
+                    atomicMax(keys + c.cell, cell_key(c.h, (uint32_t)i));
+                }
             }
-        }
-        if (p.want_front) {
-            const int pix = front_pixel(pt, p);
-            if (pix >= 0) atomicMax(winners + pix, (unsigned)i + 1u);
+            if (p.want_front) {
+                const int pix = front_pixel(pt[k], p);
+                if (pix >= 0) atomicMax(winners + pix, (unsigned)i + 1u);
+            }
         }
     }
 }
@@ -1241,18 +1250,39 @@ atomic_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPa
     const int n = offs.off[f + 1] - base;
     unsigned *out = reinterpret_cast<unsigned *>(top + (size_t)f * p.top_frame_floats);
     unsigned long long *keys = cellkey + (size_t)f * ((size_t)p.xn * p.yn);
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 pt = load_point(pts + base + i);
-        const CellHit c = classify(pt, p);
-        if (!c.keep) continue;
-        unsigned *cellw = out + (size_t)c.cell * p.planes;
-        const unsigned cnt = *reinterpret_cast<volatile unsigned *>(cellw + p.zn + 1);
-        if (cnt < 0x3E000000u) cellw[p.zn + 1] = __float_as_uint(__ldg(lut + (cnt < 31u ? cnt : 31u)));
-        if (c.h > 0.0f) {
-            const unsigned mine = __float_as_uint(c.h) | kRawTag;
-            if (*reinterpret_cast<volatile unsigned *>(cellw + c.slice) == mine)
-                cellw[c.slice] = __float_as_uint(slice_value(c.h, p.z_div, c.slice));
-            if (keys[c.cell] == cell_key(c.h, (uint32_t)i)) cellw[p.zn] = __float_as_uint(pt.w);
+    const int stride = gridDim.x * blockDim.x;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 2 * stride) {
+        float4 pt[2];
+        pt[0] = load_point(pts + base + i0);
+        if (i0 + stride < n) pt[1] = load_point(pts + base + i0 + stride);
+        // both points' cell words are requested before either is examined
+        CellHit c[2];
+        unsigned cnt[2] = {0u, 0u}, slot[2] = {0u, 0u};
+        unsigned long long key[2] = {0ull, 0ull};
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            c[k].keep = false;
+            if (i0 + k * stride >= n) continue;
+            c[k] = classify(pt[k], p);
+            if (!c[k].keep) continue;
+            unsigned *cellw = out + (size_t)c[k].cell * p.planes;
+            cnt[k] = *reinterpret_cast<volatile unsigned *>(cellw + p.zn + 1);
+            if (c[k].h > 0.0f) {
+                slot[k] = *reinterpret_cast<volatile unsigned *>(cellw + c[k].slice);
+                key[k] = *reinterpret_cast<volatile unsigned long long *>(keys + c[k].cell);
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            if (!c[k].keep) continue;
+            const int i = i0 + k * stride;
+            unsigned *cellw = out + (size_t)c[k].cell * p.planes;
+            if (cnt[k] < 0x3E000000u) cellw[p.zn + 1] = __float_as_uint(__ldg(lut + (cnt[k] < 31u ? cnt[k] : 31u)));
+            if (c[k].h > 0.0f) {
+                if (slot[k] == (__float_as_uint(c[k].h) | kRawTag))
+                    cellw[c[k].slice] = __float_as_uint(slice_value(c[k].h, p.z_div, c[k].slice));
+                if (key[k] == cell_key(c[k].h, (uint32_t)i)) cellw[p.zn] = __float_as_uint(pt[k].w);
+            }
         }
     }
 }

@@ -306,9 +306,9 @@ extern "C" int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params 
 
 // AUTO, refined per call. Measured on a B200 (tools/configs_bench.py --crossover, profiles/crossover_r1j.jsonl):
 //  * the tile strategy wins when the dense write dominates (64 KITTI sweeps: 78 k vs 62 k sweeps/s);
-//  * up to three sweeps per call the three small launches of the atomic strategy finish first (one sweep: 57 vs 74 us);
+//  * up to four sweeps per call the three small launches of the atomic strategy finish first (one sweep: 53 vs 73 us);
 //  * once the points weigh more than ~7 % of the output bytes (the 2 M-point cloud of config 5: 36 %) the per-tile
-//    reduction chain of the hottest tiles is the long pole and the L2 atomics win (0.67 vs 0.96 ms per 8 clouds).
+//    reduction chain of the hottest tiles is the long pole and the L2 atomics win (0.64 vs 0.98 ms per 8 clouds).
 // points_total < 0: the caller needs the tile strategy's by-products (compact read-back, occupancy report).
 static int resolve_for_batch(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy, int batch,
                              long long points_total = -1)

@@ -55,7 +55,7 @@ def test_one_encoder_from_concurrent_threads(oracle_mod):
     from mv3d_b200.encoder import ViewEncoder
     top_p, front_p = KITTI_PAPER_TOP, KITTI_FRONT_64x512
     enc = ViewEncoder(0)
-    batches = [[hdl64_sweep(70 + 4 * i + j)[: 100000 + 5000 * j] for j in range(1 + i)] for i in range(4)]  # 1..4 sweeps: both AUTO branches
+    batches = [[hdl64_sweep(70 + 6 * i + j)[: 100000 + 4000 * j] for j in range(n)] for i, n in enumerate((1, 2, 4, 6))]  # both AUTO branches
     out, errors = [None] * 4, []
 
     def work(i):
