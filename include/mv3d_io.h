@@ -34,6 +34,10 @@ int mv3d_io_stat_sweeps(const char *const *paths, int n, long long *points_out);
  * a direct DMA. */
 int mv3d_io_read_sweeps(const char *const *paths, int n, float *dst, const long long *offsets, int threads);
 
+/* The same packing for sweeps that are already in host memory (a ROS subscriber, an earlier np.fromfile): sweep i
+ * (offsets[i+1] - offsets[i] points at sweeps[i]) is copied to dst + 4*offsets[i] by `threads` threads in parallel. */
+int mv3d_io_pack_sweeps(const float *const *sweeps, int n, float *dst, const long long *offsets, int threads);
+
 /* np.save(path, array) for a C-contiguous float32 array: byte-identical to numpy's file (format 1.0, the header
  * dictionary padded to a multiple of 64 bytes as numpy >= 1.14 pads it). `path` is used as given (numpy appends
  * ".npy" when it is missing; the Python mirror does the same before calling). */

@@ -89,7 +89,7 @@ EXPORTED_SYMBOLS = (
     "mv3d_pytwin_encode_batch_dev", "mv3d_pytwin_encode_batch_host", "mv3d_debug_atan2f", "mv3d_frame_checksums_dev",
     "mv3d_ctx_set_anchors", "mv3d_remove_empty_anchor_dev", "mv3d_remove_empty_anchor_host",
     "mv3d_encode_filter_batch_dev", "mv3d_pytwin_encode_filter_batch_dev",
-    "mv3d_io_stat_sweeps", "mv3d_io_read_sweeps", "mv3d_io_write_npy", "mv3d_io_write_npy_batch", "mv3d_io_npy_info",
+    "mv3d_io_stat_sweeps", "mv3d_io_read_sweeps", "mv3d_io_pack_sweeps", "mv3d_io_write_npy", "mv3d_io_write_npy_batch", "mv3d_io_npy_info",
     "mv3d_io_read_npy", "mv3d_io_write_npz_compressed", "mv3d_io_write_npz_compressed_batch",
 )
 ANCHORS_AUTO, ANCHORS_EXACT = 0, 1
@@ -151,6 +151,7 @@ def load_library() -> ctypes.CDLL:
     llp = ctypes.POINTER(ll)
     lib.mv3d_io_stat_sweeps.argtypes = [cpp, ci, vp]
     lib.mv3d_io_read_sweeps.argtypes = [cpp, ci, vp, vp, ci]
+    lib.mv3d_io_pack_sweeps.argtypes = [vp, ci, vp, vp, ci]
     lib.mv3d_io_write_npy.argtypes = [ctypes.c_char_p, vp, llp, ci]
     lib.mv3d_io_write_npy_batch.argtypes = [cpp, ci, vp, sz, llp, ci, ci]
     lib.mv3d_io_npy_info.argtypes = [ctypes.c_char_p, llp, ctypes.POINTER(ci), llp]

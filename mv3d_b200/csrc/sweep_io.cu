@@ -315,6 +315,22 @@ extern "C" int mv3d_io_read_sweeps(const char *const *paths, int n, float *dst, 
     return e.empty() ? 0 : fail("mv3d_io_read_sweeps: %s", e.c_str());
 }
 
+extern "C" int mv3d_io_pack_sweeps(const float *const *sweeps, int n, float *dst, const long long *offsets, int threads)
+{
+    if (n < 0 || (n > 0 && (!sweeps || !dst || !offsets))) return fail("mv3d_io_pack_sweeps: bad arguments");
+    for (int i = 0; i < n; i++) {
+        if (offsets[i + 1] < offsets[i]) return fail("mv3d_io_pack_sweeps: offsets must not decrease");
+        if (offsets[i + 1] > offsets[i] && !sweeps[i]) return fail("mv3d_io_pack_sweeps: sweep %d is NULL", i);
+    }
+    // a sweep is ~2 MB: one memcpy each, spread over the threads (a single thread copies at ~10 GB/s, the batch of a
+    // 64-sweep launch is 123 MB)
+    run_parallel(n, threads, [&](int i) -> std::string {
+        memcpy(dst + 4 * offsets[i], sweeps[i], (size_t)(offsets[i + 1] - offsets[i]) * 16);
+        return "";
+    });
+    return 0;
+}
+
 extern "C" int mv3d_io_write_npy(const char *path, const float *data, const long long *shape, int ndim)
 {
     size_t count;

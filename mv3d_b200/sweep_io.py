@@ -18,7 +18,7 @@ import numpy as np
 from . import _lib
 from .encoder import pinned_empty
 
-__all__ = ["read_sweep", "read_sweeps", "save", "save_batch", "load_view", "savez_compressed",
+__all__ = ["read_sweep", "read_sweeps", "pack_sweeps_into", "save", "save_batch", "load_view", "savez_compressed",
            "savez_compressed_batch", "npy_path", "npz_path"]
 
 
@@ -72,6 +72,23 @@ def read_sweeps(paths: Sequence[str], threads: int = 0, pinned: bool = True):
     if lib.mv3d_io_read_sweeps(arr, len(paths), points.ctypes.data, offsets.ctypes.data, int(threads)) != 0:
         raise OSError(_lib.last_error())
     return points, offsets.astype(np.int32)
+
+
+def pack_sweeps_into(sweeps: Sequence[np.ndarray], dst: np.ndarray, threads: int = 0) -> np.ndarray:
+    """Copy in-memory sweeps (`(n_i, 4)` float32 arrays) back to back into `dst` (typically a page-locked staging
+    buffer) with parallel native copies; returns the int32 offsets (`len(sweeps) + 1`)."""
+    import ctypes
+    lib = _lib.load_library()
+    sweeps = [np.ascontiguousarray(s, dtype=np.float32) for s in sweeps]
+    offsets = np.zeros(len(sweeps) + 1, dtype=np.int64)
+    for i, s in enumerate(sweeps):
+        assert s.ndim == 2 and s.shape[1] == 4, "a sweep is (n, 4) float32"
+        offsets[i + 1] = offsets[i] + s.shape[0]
+    assert dst.dtype == np.float32 and dst.flags["C_CONTIGUOUS"] and dst.size >= 4 * int(offsets[-1])
+    ptrs = (ctypes.c_void_p * max(len(sweeps), 1))(*[s.ctypes.data for s in sweeps])
+    if lib.mv3d_io_pack_sweeps(ptrs, len(sweeps), dst.ctypes.data, offsets.ctypes.data, int(threads)) != 0:
+        raise ValueError(_lib.last_error())
+    return offsets.astype(np.int32)
 
 
 def read_sweep(path: str) -> np.ndarray:

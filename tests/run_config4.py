@@ -109,6 +109,9 @@ def main():
         enc.close()
     else:
         stream = SweepStream(local, top_p, front_p, batch=args.batch, depth=2)
+        for _ in stream.run(mine[: 2 * args.batch], load):  # warm-up: page-locked staging, output slots, workspaces
+            pass
+        torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()

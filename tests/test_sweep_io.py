@@ -138,3 +138,19 @@ def test_npz_batch(tmp_path):
     # archives are reproducible: a fixed timestamp, no zip64 padding
     sweep_io.savez_compressed(str(tmp_path / "again.npy"), top_view=views[0])
     assert open(paths[0] + ".npz", "rb").read() == open(str(tmp_path / "again.npy.npz"), "rb").read()
+
+
+@pytest.mark.parametrize("threads", [0, 1, 3])
+def test_pack_sweeps_into_equals_concatenate(threads):
+    """In-memory sweeps packed by the native parallel copier == np.concatenate (ragged, empty and single-point sweeps)."""
+    from mv3d_b200.sweep_io import pack_sweeps_into
+    rng = np.random.default_rng(5)
+    sweeps = [rng.random((n, 4), dtype=np.float32) for n in (1000, 0, 1, 120000, 77, 0, 50001)]
+    dst = np.full((sum(len(s) for s in sweeps) + 8, 4), -1.0, np.float32)
+    offs = pack_sweeps_into(sweeps, dst, threads)
+    assert offs.tolist() == np.concatenate([[0], np.cumsum([len(s) for s in sweeps])]).tolist()
+    assert np.array_equal(dst[: offs[-1]], np.concatenate(sweeps))
+    assert (dst[offs[-1]:] == -1.0).all()
+    assert pack_sweeps_into([], dst).tolist() == [0]
+    sliced = rng.random((100, 8), dtype=np.float32)[:, :4]  # not contiguous: copied first
+    assert np.array_equal(dst[: pack_sweeps_into([sliced], dst)[-1]], sliced)
