@@ -272,17 +272,30 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
         float4 pt[kPointItems];
         unsigned start[kPointItems];
 #pragma unroll
-        for (int j = 0; j < kPointItems; j++) {  // key and point of every item first: independent loads
+        for (int j = 0; j < kPointItems; j++) {  // the keys of every item first: independent loads
             const int i = i0 + j * stride;
             k[j] = make_uint2(kInvalidKey, 0u);
-            if (i < n) {
-                k[j] = keys[base + i];
-                pt[j] = load_point(pts + base + i);
+            if (i < n) k[j] = keys[base + i];
+        }
+#ifndef MV3D_BIN_LOAD_ALL
+        // Rejected points come in runs (the part of every beam's turn that lies outside the box), so fetching only the
+        // kept points' 16 bytes spares about half of the point traffic of this pass.
+#pragma unroll
+        for (int j = 0; j < kPointItems; j++) {
+            start[j] = 0u;
+            if (k[j].x != kInvalidKey) {
+                pt[j] = load_point(pts + base + i0 + j * stride);
+                start[j] = __ldg(off + tile_of(k[j].x, p));
             }
         }
+#else
+#pragma unroll
+        for (int j = 0; j < kPointItems; j++)
+            if (i0 + j * stride < n) pt[j] = load_point(pts + base + i0 + j * stride);
 #pragma unroll
         for (int j = 0; j < kPointItems; j++)
             start[j] = k[j].x != kInvalidKey ? __ldg(off + tile_of(k[j].x, p)) : 0u;
+#endif
 #pragma unroll
         for (int j = 0; j < kPointItems; j++) {
             if (k[j].x == kInvalidKey) continue;
