@@ -67,3 +67,39 @@ def test_param_grid_sizes():
     assert REFERENCE_KITTI_TOP.shape == (800, 600, 27)  # src/utils/batch_loading.py:620
     assert KITTI_FRONT_64x512.shape == (64, 512, 3)
     assert KITTI_FRONT_64x512.as_front_paras()[6:] == (64, 512, 3)
+
+
+REF_VER3 = "/root/reference/src/lidar_data_preprocess/Python_to_C_Interface/ver3"
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_VER3), reason="the reference tree is not on this machine")
+def test_reference_wrappers_bind_this_library(encoder_lib, capfd):
+    """The reference's OWN ctypes wrappers (ver3/createTopMaps.py, ver3/createTopAndFrontMaps.py), imported unmodified
+    from where they lie and pointed at libmv3d_encode.so through their `c_lib_path` argument: the symbols resolve with
+    the reference's call shape (15 / 25 by-value arguments, no argtypes), nothing crashes, and on a machine without a
+    GPU the error contract holds (outputs zero-filled, the reason recorded)."""
+    import importlib.util
+    import numpy as np
+    import torch
+    from mv3d_b200 import _lib
+    from mv3d_b200.params import FrontParams, TopParams
+
+    def load(name):
+        spec = importlib.util.spec_from_file_location("ref_" + name, os.path.join(REF_VER3, name + ".py"))
+        mod = importlib.util.module_from_spec(spec)
+        spec.loader.exec_module(mod)
+        return getattr(mod, name)
+
+    top = TopParams(0.0, 4.0, -2.0, 2.0, -1.0, 1.0, 0.5, 0.5, 0.5)
+    front = FrontParams(-20.0, 20.0, -45.0, 45.0, 2.5, 5.0)
+    pts = np.array([[1.1, 0.3, 0.2, 0.5], [2.2, -0.7, -0.4, 0.9]], np.float32)
+    out = np.ones(top.shape, np.float32)
+    load("createTopMaps")(pts, 2, out, list(top.as_top_paras()), _lib.LIB_PATH)
+    fout = np.ones(front.shape, np.float32)
+    out2 = np.ones(top.shape, np.float32)
+    load("createTopAndFrontMaps")(pts, 2, out2, fout, list(top.as_top_paras()), list(front.as_front_paras()), _lib.LIB_PATH)
+    if not torch.cuda.is_available():
+        assert not out.any() and not out2.any() and not fout.any()
+        assert b"no CPU fallback" in encoder_lib.mv3d_last_error()
+    else:
+        assert out.any() and out2.any()  # a GPU is present: the views were encoded
