@@ -370,3 +370,28 @@ def test_outputs_inside_guard_bands(torch_cuda, oracle_mod, strategy, pad):
         assert_same(top[i].cpu().numpy(), et, f"{strategy} pad {pad} sweep {i} top")
         assert_same(front[i].cpu().numpy(), ef, f"{strategy} pad {pad} sweep {i} front")
     enc.close()
+
+
+@pytest.mark.parametrize("knob,value", [("MV3D_PATCH_MODE", "warp"), ("MV3D_TILE_PIPE", "5,192,36720,0"),
+                                        ("MV3D_TILE_PIPE", "3,256,8640,1"), ("MV3D_ATOMIC_OVERLAP", "1"),
+                                        ("MV3D_SUB_BATCH", "2"), ("MV3D_TILE_BYTES", "8192")])
+def test_experiment_knobs_stay_bit_exact(torch_cuda, oracle_mod, monkeypatch, knob, value):
+    """The recorded experiments stay selectable (profiles/strategy_experiments_r1.md) -- and stay correct: the TMA-fill
+    + warp-patch form of PATCH, the pipelined tile kernel, the overlapped atomic passes, sub-batch pipelining, small tiles."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    monkeypatch.setenv(knob, value)  # read when the context is created
+    strategy = {"MV3D_PATCH_MODE": "patch", "MV3D_ATOMIC_OVERLAP": "atomic"}.get(knob, "tile")
+    qc = {c[0]: c[1] for c in cases.quirk_cases()}
+    sweeps = [hdl64_sweep(90 + i)[: 120000 - 9000 * i] for i in range(9)] + [np.zeros((0, 4), np.float32), qc["hot_cell"]]
+    pts, offs = pack_sweeps(sweeps)
+    d = torch.from_numpy(pts).cuda()
+    enc = ViewEncoder(0, strategy=strategy)
+    for rep in range(2):
+        top, front = enc.encode_device(d, offs, KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+        torch.cuda.synchronize()
+        for i, s in enumerate(sweeps):
+            et, ef = oracle_mod.top_and_front_maps(s, KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+            assert_same(top[i].cpu().numpy(), et, f"{knob}={value} rep {rep} sweep {i} top")
+            assert_same(front[i].cpu().numpy(), ef, f"{knob}={value} rep {rep} sweep {i} front")
+    enc.close()
