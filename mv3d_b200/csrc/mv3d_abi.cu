@@ -1369,6 +1369,8 @@ extern "C" void createTopAndFrontMaps(const void *raw_data, int num, const void 
         fprintf(stderr, "libmv3d_encode: createTopAndFrontMaps failed: %s\n", g_error);
         if (X_SIZE > 0 && Y_SIZE > 0 && Z_SIZE >= 0)
             zero_host(const_cast<void *>(top_data), (double)X_SIZE * Y_SIZE * (Z_SIZE + 2));
-        if (C_SIZE > 0 && R_SIZE > 0 && F_SIZE > 0) zero_host(const_cast<void *>(front_data), (double)C_SIZE * R_SIZE * F_SIZE);
+        // a caller that hands over non-integral sizes allocated for their integer parts at most: never zero more
+        if (C_SIZE >= 1 && R_SIZE >= 1 && F_SIZE >= 1 && std::isfinite(C_SIZE) && std::isfinite(R_SIZE) && std::isfinite(F_SIZE))
+            zero_host(const_cast<void *>(front_data), std::floor((double)C_SIZE) * std::floor((double)R_SIZE) * std::floor((double)F_SIZE));
     }
 }
