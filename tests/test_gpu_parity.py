@@ -395,3 +395,33 @@ def test_experiment_knobs_stay_bit_exact(torch_cuda, oracle_mod, monkeypatch, kn
             assert_same(top[i].cpu().numpy(), et, f"{knob}={value} rep {rep} sweep {i} top")
             assert_same(front[i].cpu().numpy(), ef, f"{knob}={value} rep {rep} sweep {i} front")
     enc.close()
+
+
+@pytest.mark.parametrize("strategy", ["tile", "atomic", "sort"])
+def test_five_million_points_in_one_sweep(torch_cuda, oracle_mod, strategy):
+    """Maximum-size input: 5 M points in ONE sweep, a third of them piled onto a few hundred cells (tile bins of
+    hundreds of thousands of records, counts far past the density saturation), device path and host symbol."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.sweeps import uniform_in_box
+    pts = uniform_in_box(5_000_000, KITTI_PAPER_TOP, seed=77, margin=0.5)
+    rng = np.random.default_rng(78)
+    hot = rng.integers(0, len(pts), len(pts) // 3)
+    pts[hot, 0] = 20.0 + rng.uniform(0, 2.0, len(hot)).astype(np.float32)
+    pts[hot, 1] = -1.0 + rng.uniform(0, 1.0, len(hot)).astype(np.float32)
+    pts[hot[::5], 2] = np.float32(0.25)  # mass ties on the maximum height
+    offs = np.array([0, len(pts)], np.int32)
+    et, ef = oracle_mod.top_and_front_maps(pts, KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+    enc = ViewEncoder(0, strategy=strategy)
+    top, front = enc.encode_device(torch.from_numpy(pts).cuda(), offs, KITTI_PAPER_TOP, KITTI_FRONT_64x512)
+    torch.cuda.synchronize()
+    assert_same(top[0].cpu().numpy(), et, f"5M {strategy} top")
+    assert_same(front[0].cpu().numpy(), ef, f"5M {strategy} front")
+    enc.close()
+    if strategy == "tile":  # the host symbol takes the compact read-back with a 5 M-entry list capacity
+        from mv3d_b200.ver3 import createTopAndFrontMaps
+        out = np.ones(KITTI_PAPER_TOP.shape, np.float32)
+        fout = np.ones(KITTI_FRONT_64x512.shape, np.float32)
+        createTopAndFrontMaps(pts, len(pts), out, fout, KITTI_PAPER_TOP.as_top_paras(), KITTI_FRONT_64x512.as_front_paras())
+        assert_same(out, et, "5M host symbol top")
+        assert_same(fout, ef, "5M host symbol front")
