@@ -31,6 +31,9 @@ namespace mv3d {
 
 constexpr int kPointThreads = 256;
 constexpr int kTileThreads = 256;
+#ifndef MV3D_TILE_MIN_BLOCKS
+#define MV3D_TILE_MIN_BLOCKS 5  // register cap of the tile kernels: five CTAs of 256 threads per SM (48 registers)
+#endif
 
 // ------------------------------------------------------------------------------------------------
 // small PTX wrappers
@@ -577,7 +580,7 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
 }
 
 template <bool kPy, int kStore = kStoreTmaHint>
-__global__ void __launch_bounds__(kTileThreads, 5)
+__global__ void __launch_bounds__(kTileThreads, MV3D_TILE_MIN_BLOCKS)
 tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
                   const __grid_constant__ FrameOffsets offs,
                   const __grid_constant__ ViewParams p, const float *__restrict__ lut, float *__restrict__ top,
@@ -588,7 +591,7 @@ tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
 
 // Same, and the occupancy bits / flag of every frame for the empty-anchor filter (see tile_body).
 template <bool kPy>
-__global__ void __launch_bounds__(kTileThreads, 5)
+__global__ void __launch_bounds__(kTileThreads, MV3D_TILE_MIN_BLOCKS)
 tile_build_occupancy_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
                   const __grid_constant__ FrameOffsets offs,
                             const __grid_constant__ ViewParams p, const float *__restrict__ lut,
@@ -599,7 +602,7 @@ tile_build_occupancy_kernel(const uint4 *__restrict__ binned, const unsigned *__
 
 // Same reduction for an output the copy engine has zero-filled: only the touched cells are written (PATCH strategy).
 template <bool kPy>
-__global__ void __launch_bounds__(kTileThreads, 5)
+__global__ void __launch_bounds__(kTileThreads, MV3D_TILE_MIN_BLOCKS)
 tile_patch_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
                   const __grid_constant__ FrameOffsets offs,
                   const __grid_constant__ ViewParams p, const float *__restrict__ lut, float *__restrict__ top,
@@ -610,7 +613,7 @@ tile_patch_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__
 
 // Same reduction, compact output (see tile_body).
 template <bool kPy>
-__global__ void __launch_bounds__(kTileThreads, 5)
+__global__ void __launch_bounds__(kTileThreads, MV3D_TILE_MIN_BLOCKS)
 tile_compact_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
                   const __grid_constant__ FrameOffsets offs,
                     const __grid_constant__ ViewParams p, const float *__restrict__ lut, int total_tiles,
