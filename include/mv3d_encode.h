@@ -180,7 +180,8 @@ int mv3d_ctx_kernel_times(mv3d_ctx *ctx, double *ms_out, long long *launches_out
 /* Test hook: the per-point decisions of the encoder, for one sweep resident in device memory.
  *   cell_dev[i]      output cell (X-1)*yn + (Y-1) of point i, or -1 when the gate rejects it
  *   pix_dev[i]       front-view pixel r*C + c through the production arithmetic, or -1 (fp may be NULL: skipped)
- *   pix_exact_dev[i] the same pixel through the all-double evaluation (the two must always agree) */
+ *   pix_exact_dev[i] the same pixel through the reference's own expressions -- row bin in double, column bin in float on
+ *                    the C library's atan2f, no fast path (the two must always agree) */
 int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int num, const mv3d_top_params *tp,
                           const mv3d_front_params *fp, int semantics, int *cell_dev, int *pix_dev,
                           int *pix_exact_dev, void *stream);

@@ -317,7 +317,7 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
                 key = c.h;
                 zfield = (c.slice < p.zn ? (uint32_t)c.slice : kNoSlice) | ((c.lower && c.slice <= p.zn) ? kLowerFlag : 0u);
             } else {
-                zfield = (uint32_t)quantise(pt[j].z, p.z_min, p.z_div, p.quant_floor);
+                zfield = (uint32_t)quantise(pt[j].z, p.z_min, p.z_div, p.z_inv, p.quant_floor);
                 key = __fsub_rn(pt[j].z, p.z_min);
             }
             binned[(size_t)base + start[j] + k[j].y] =

@@ -324,6 +324,13 @@ static int resolve_for_batch(const mv3d_ctx *ctx, const mv3d_top_params *tp, int
     return r;
 }
 
+// 1/div for the fast path of quantise() (view_math.cuh); NaN sends every point through the IEEE division.
+static float fast_reciprocal(float div)
+{
+    const float inv = 1.0f / div;
+    return (div > 0.0f && std::isfinite(inv) && inv >= 1.17549435e-38f) ? inv : std::nanf("");
+}
+
 static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3d_front_params *fp, bool want_top,
                        bool want_front, int semantics, int strategy, ViewParams *out)
 {
@@ -336,6 +343,7 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
     if (cells >= (1LL << 31) - 8) return fail("grid %d x %d has too many cells", tp->xn, tp->yn);
     p.x_min = tp->x_min; p.y_min = tp->y_min; p.z_min = tp->z_min;
     p.x_div = tp->x_div; p.y_div = tp->y_div; p.z_div = tp->z_div;
+    p.x_inv = fast_reciprocal(tp->x_div); p.y_inv = fast_reciprocal(tp->y_div); p.z_inv = fast_reciprocal(tp->z_div);
     p.xn = tp->xn; p.yn = tp->yn; p.zn = tp->zn; p.planes = tp->zn + 2;
     p.quant_floor = (semantics == MV3D_SEM_TOPFRONT) ? 1 : 0;
     if (tp->flags & ~(MV3D_TOP_FLIP_XY | MV3D_TOP_FILTER_CENTER_CAR)) return fail("unknown top flags 0x%x", tp->flags);
@@ -346,7 +354,7 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
     p.top_frame_floats = cells * p.planes;
     p.tile_cells = pick_tile_cells(strategy == MV3D_STRATEGY_PATCH ? ctx->patch_tile_bytes : ctx->tile_bytes_target,
                                    p.planes, cells);
-    p.tiles_per_frame = (int)((cells + p.tile_cells - 1) / p.tile_cells);
+    p.tiles_per_frame = (cells > 0 && p.tile_cells > 0) ? (int)((cells + p.tile_cells - 1) / p.tile_cells) : 0;
     p.store_mode = ctx->tile_store;
     p.tile_magic = tile_magic_for(p.tile_cells);
     if (strategy != MV3D_STRATEGY_PATCH) apply_pipe(ctx, &p);
@@ -362,6 +370,7 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
         p.rad_to_deg = (float)(180 / 3.141596);  // sic, LidarTopAndFrontPreprocess.c:36
         p.phi_div = fp->phi_div; p.theta_div = fp->theta_div;
         p.phi_scale = p.rad_to_deg / fp->phi_div; p.theta_scale = p.rad_to_deg / fp->theta_div;
+        p.phi_eps = std::fabs(p.phi_scale) * 2.5e-6f; p.theta_eps = std::fabs(p.theta_scale) * 2.5e-6f;
         p.r_size_f = fp->r_size; p.c_size_f = fp->c_size;
         p.rn = (int)fp->r_size; p.cn = (int)fp->c_size; p.fn = (int)fp->f_size;
         p.center_c = (int)(fp->c_size / 2);  // :37
@@ -925,7 +934,7 @@ static int make_py_params(const mv3d_ctx *ctx, const mv3d_pytwin_params *pp, boo
     p.want_front = 0;  // the C routine's front view is not part of this mode
     p.top_frame_floats = cells * p.planes;
     p.tile_cells = pick_tile_cells(ctx->tile_bytes_target, p.planes, cells);
-    p.tiles_per_frame = cells ? (int)((cells + p.tile_cells - 1) / p.tile_cells) : 0;
+    p.tiles_per_frame = (cells > 0 && p.tile_cells > 0) ? (int)((cells + p.tile_cells - 1) / p.tile_cells) : 0;
     p.store_mode = ctx->tile_store;
     p.tile_magic = tile_magic_for(p.tile_cells);
     apply_pipe(ctx, &p);

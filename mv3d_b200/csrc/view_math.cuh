@@ -16,6 +16,7 @@ struct ViewParams {
     // bird's-eye view
     float x_min, y_min, z_min;
     float x_div, y_div, z_div;
+    float x_inv, y_inv, z_inv;    // 1/div rounded to float (NaN when div is not a positive normal number): fast path of quantise()
     int xn, yn, zn, planes;       // planes = zn + 2
     int quant_floor;              // 0: (int)q [T:107-109]   1: (int)floor(q) [TF:124-126]
     int py;                       // 1: semantics of the reference's PYTHON lidar_to_top (src/data.py:296-367), see py_classify
@@ -37,6 +38,7 @@ struct ViewParams {
     float rad_to_deg;             // (float)(180/3.141596) [TF:36]
     float phi_div, theta_div;
     float phi_scale, theta_scale; // rad_to_deg / div in float: only for the approximate fast path below
+    float phi_eps, theta_eps;     // |scale| * 2.5e-6: the part of the fast path's error bound that does not grow with the bin
     float r_size_f, c_size_f;     // the float bounds of TF:176
     int rn, cn, fn, center_r, center_c;
     int front_pixels;             // rn*cn
@@ -78,12 +80,28 @@ __device__ __forceinline__ int cvtt_f64(double v)
     return (v > -2147483649.0 && v < 2147483648.0) ? __double2int_rz(v) : INT32_MIN;
 }
 
-// Cell coordinate along one axis: two separately rounded float ops, then truncate or floor.
-__device__ __forceinline__ int quantise(float p, float lo, float div, int quant_floor)
+// Cell coordinate along one axis: two separately rounded float ops, then truncate or floor [T:107-109 / TF:124-126].
+// The exact form (an IEEE division) is what the reference computes.
+__device__ __forceinline__ int quantise_exact(float a, float div, int quant_floor)
 {
-    float q = __fdiv_rn(__fsub_rn(p, lo), div);
+    float q = __fdiv_rn(a, div);
     if (quant_floor) q = floorf(q);
     return cvtt_f32(q);
+}
+// Same integer from a multiplication by the rounded reciprocal, when that is provably enough: qf = RN(a * RN(1/div))
+// differs from the reference's RN(a / div) by at most |q| * 3 * 2^-24 = |q| * 1.8e-7 (three roundings). Truncation
+// and floor can only differ from the reference's when an integer lies between the two values, so qf is accepted when
+// it is at least |qf| * 1e-6 (5x that bound) away from every integer; otherwise -- on cell boundaries, about one point
+// in a thousand on real sweeps -- the IEEE division decides. NaN / huge / denormal-reciprocal cases take the exact
+// path too (inv is NaN when div is not a positive normal float). Bit-identical either way; the per-point tests
+// compare 20 M random points and the boundary-snapped fuzz clouds with the oracle.
+__device__ __forceinline__ int quantise(float p, float lo, float div, float inv, int quant_floor)
+{
+    const float a = __fsub_rn(p, lo);
+    const float qf = __fmul_rn(a, inv);
+    const float aq = fabsf(qf);
+    if (!(aq < 4.0e6f) || fabsf(__fsub_rn(qf, rintf(qf))) <= __fmul_rn(aq, 1.0e-6f)) return quantise_exact(a, div, quant_floor);
+    return quant_floor ? __float2int_rd(qf) : __float2int_rz(qf);
 }
 
 struct CellHit {
@@ -163,9 +181,9 @@ __device__ __forceinline__ CellHit classify_as(const float4 &pt, const ViewParam
         c.h = 0.0f;
         return c;
     }
-    const int X = quantise(pt.x, p.x_min, p.x_div, p.quant_floor);
-    const int Y = quantise(pt.y, p.y_min, p.y_div, p.quant_floor);
-    const int Z = quantise(pt.z, p.z_min, p.z_div, p.quant_floor);
+    const int X = quantise(pt.x, p.x_min, p.x_div, p.x_inv, p.quant_floor);
+    const int Y = quantise(pt.y, p.y_min, p.y_div, p.y_inv, p.quant_floor);
+    const int Z = quantise(pt.z, p.z_min, p.z_div, p.z_inv, p.quant_floor);
     c.keep = (X >= 1 && Y >= 1 && Z >= 0 && X < p.xn && Y < p.yn && Z < p.zn);
     c.cell = !c.keep ? kInvalidKey
                      : p.flip_xy ? (uint32_t)((p.xn - X) * p.yn + (p.yn - Y)) : (uint32_t)((X - 1) * p.yn + (Y - 1));
@@ -196,22 +214,62 @@ __device__ __forceinline__ uint32_t cell_key_index(unsigned long long key)
     return 0xFFFFFFFFu - (uint32_t)(key & 0xFFFFFFFFull);
 }
 
-// Angular bin (int)(atan2(num, den) * RAD_TO_DEG / DIV), the reference's double expression [TF:173-174].
-__device__ __forceinline__ int angle_bin_exact(double num, double den, float rad_to_deg, float div)
+// ---- front-view bins [TF:173-174] ---------------------------------------------------------------------------------
+// The reference file is C++ (<math.h> = libstdc++'s wrapper, `using namespace std`), so the two bins have different
+// types:
+//   R = (int)(atan2(z, sqrt(pow(x,2)+pow(y,2))) * RAD_TO_DEG / phi_DIVISION)   pow(float,int) -> double: all double
+//   C = (int)(atan2(y, x) * RAD_TO_DEG / theta_DIVISION)                       atan2(float,float) = atan2f: all float
+// (`nm -D` on the reference build imports atan2 and atan2f; oracle/ref_probe.c checks both bins one point per call.)
+__device__ __forceinline__ float fd_atan2f(float y, float x);
+
+// Row bin, exact: the double expression, cvttsd2si.
+__device__ __forceinline__ int row_bin_exact(double num, double den, float rad_to_deg, float div)
 {
     return cvtt_f64(__ddiv_rn(__dmul_rn(atan2(num, den), (double)rad_to_deg), (double)div));
 }
-
-// Same bin from single-precision arithmetic, when that is provably enough. The float quotient qf differs from
-// the reference's double value by at most |q|*4e-7 + |scale|*0.6e-7 (2-ulp atan2f, <=1.25-ulp sqrt/arguments,
-// two roundings for the scale); the bin is accepted only if qf is at least eps = |qf|*4e-6 + |scale|*1e-6
-// (about 10x that bound) away from every integer, where truncation cannot differ. Otherwise the caller takes
-// the exact double path. About 0.1 % of points do; the result is bit-identical either way.
-__device__ __forceinline__ bool angle_bin_fast(float num, float den, float scale, int &bin)
+// Column bin, exact: the float expression on the C library's atan2f (fd_atan2f below restates glibc's, operation for
+// operation), cvttss2si.
+__device__ __forceinline__ int col_bin_exact(float y, float x, float rad_to_deg, float div)
 {
-    const float qf = __fmul_rn(atan2f(num, den), scale);
-    const float eps = fabsf(qf) * 4e-6f + fabsf(scale) * 1e-6f;
-    if (!(fabsf(qf) < 1.0e6f) || fabsf(qf - rintf(qf)) <= eps) return false;
+    return cvtt_f32(__fdiv_rn(__fmul_rn(fd_atan2f(y, x), rad_to_deg), div));
+}
+
+// atan2 to within 4.2e-7 rad, ~25 instructions: t = min/max by the hardware reciprocal (2 ulp), atan(t) on [0, 1] by
+// the 8-term odd polynomial of Abramowitz & Stegun 4.4.49 (|error| <= 2e-8; 9.3e-8 evaluated in float32 with FMAs),
+// then the octant fix-ups (each one rounding of a value below pi, constants off by < 9e-8). Only ever used where an
+// error bound decides whether its result is good enough (angle_bin_fast); never feeds a stored value.
+__device__ __forceinline__ float approx_atan2f(float y, float x)
+{
+    const float ax = fabsf(x), ay = fabsf(y);
+    const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+    const float t = __fdividef(mn, mx);  // 0/0 -> NaN: the caller's range test sends it to the exact path
+    const float s = t * t;
+    float r = 0.0028662257f;
+    r = fmaf(r, s, -0.0161657367f);
+    r = fmaf(r, s, 0.0429096138f);
+    r = fmaf(r, s, -0.0752896400f);
+    r = fmaf(r, s, 0.1065626393f);
+    r = fmaf(r, s, -0.1420889944f);
+    r = fmaf(r, s, 0.1999355085f);
+    r = fmaf(r, s, -0.3333314528f);
+    r = fmaf(r * s, t, t);
+    if (ay > ax) r = 1.57079637f - r;
+    if (x < 0.0f) r = 3.14159274f - r;
+    return copysignf(r, y);
+}
+
+// A bin from single-precision arithmetic, when that is provably enough. qf = approx_atan2f * scale differs from the
+// value the reference truncates by at most |scale| * 5.1e-7 (the angle, incl. the approximate planar range of the row
+// bin) + |q| * 3.6e-7 (rounding of scale and product:
+// 1.2e-7; the reference's own float roundings for the column bin: 2.4e-7; none for the double row bin). The bin is
+// accepted only if qf is at least eps = |scale| * 2.5e-6 + |qf| * 2e-6 (5x / 5.5x those terms) away from every
+// integer, where truncation cannot differ. Otherwise the caller takes the exact path: a few points in a thousand do,
+// and the result is bit-identical either way (tests: 20 M random points, fast == exact == oracle).
+__device__ __forceinline__ bool angle_bin_fast(float num, float den, float scale, float scale_eps, int &bin)
+{
+    const float qf = __fmul_rn(approx_atan2f(num, den), scale);
+    const float aq = fabsf(qf);
+    if (!(aq < 1.0e6f) || fabsf(qf - rintf(qf)) <= fmaf(aq, 2.0e-6f, scale_eps)) return false;
     bin = __float2int_rz(qf);
     return true;
 }
@@ -220,34 +278,33 @@ __device__ __forceinline__ bool angle_bin_fast(float num, float den, float scale
 // reference would not store it in bounds. The reference's inclusive upper bounds are kept, so c_coord == C
 // aliases pixel (r_coord+1, 0) exactly as its linear index does, and anything at or beyond R*C (the
 // reference's out-of-bounds store) is dropped.
-__device__ __forceinline__ int front_pixel(const float4 &pt, const ViewParams &p)
+__device__ __forceinline__ int front_pixel_of(int R, int C, const ViewParams &p)
 {
-    int R, C;
-    const float planar_f = sqrtf(__fadd_rn(__fmul_rn(pt.x, pt.x), __fmul_rn(pt.y, pt.y)));
-    if (!angle_bin_fast(pt.z, planar_f, p.phi_scale, R)) {
-        const double dx = (double)pt.x, dy = (double)pt.y;
-        const double planar = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
-        R = angle_bin_exact((double)pt.z, planar, p.rad_to_deg, p.phi_div);
-    }
-    if (!angle_bin_fast(pt.y, pt.x, p.theta_scale, C))
-        C = angle_bin_exact((double)pt.y, (double)pt.x, p.rad_to_deg, p.theta_div);
     const long long r = (long long)R + p.center_r, c = (long long)C + p.center_c;
     if (!((float)r <= p.r_size_f && (float)c <= p.c_size_f && r >= 0 && c >= 0)) return -1;
     const long long pix = r * p.cn + c;
     return (pix < (long long)p.front_pixels) ? (int)pix : -1;
 }
-
-// The all-double evaluation of the same pixel (no fast path); used by the debug entry point to cross-check.
-__device__ __forceinline__ int front_pixel_exact(const float4 &pt, const ViewParams &p)
+__device__ __forceinline__ int row_bin_of(const float4 &pt, const ViewParams &p)
 {
     const double dx = (double)pt.x, dy = (double)pt.y;
     const double planar = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
-    const int R = angle_bin_exact((double)pt.z, planar, p.rad_to_deg, p.phi_div);
-    const int C = angle_bin_exact(dy, dx, p.rad_to_deg, p.theta_div);
-    const long long r = (long long)R + p.center_r, c = (long long)C + p.center_c;
-    if (!((float)r <= p.r_size_f && (float)c <= p.c_size_f && r >= 0 && c >= 0)) return -1;
-    const long long pix = r * p.cn + c;
-    return (pix < (long long)p.front_pixels) ? (int)pix : -1;
+    return row_bin_exact((double)pt.z, planar, p.rad_to_deg, p.phi_div);
+}
+__device__ __forceinline__ int front_pixel(const float4 &pt, const ViewParams &p)
+{
+    int R, C;
+    float planar_f;  // approximate on purpose (1.8e-7 relative, 9e-8 rad on the angle): fast path only
+    asm("sqrt.approx.f32 %0, %1;" : "=f"(planar_f) : "f"(fmaf(pt.x, pt.x, pt.y * pt.y)));
+    if (!angle_bin_fast(pt.z, planar_f, p.phi_scale, p.phi_eps, R)) R = row_bin_of(pt, p);
+    if (!angle_bin_fast(pt.y, pt.x, p.theta_scale, p.theta_eps, C)) C = col_bin_exact(pt.y, pt.x, p.rad_to_deg, p.theta_div);
+    return front_pixel_of(R, C, p);
+}
+
+// The reference's own expressions for the same pixel (no fast path); used by the debug entry point to cross-check.
+__device__ __forceinline__ int front_pixel_exact(const float4 &pt, const ViewParams &p)
+{
+    return front_pixel_of(row_bin_of(pt, p), col_bin_exact(pt.y, pt.x, p.rad_to_deg, p.theta_div), p);
 }
 
 // The three front-view channel values of a point [TF:185,188,192], as the floats the reference stores.
@@ -260,10 +317,12 @@ __device__ __forceinline__ void front_values(const float4 &pt, const ViewParams 
     v2 = (float)cvtt_f32(__fmul_rn(__fsub_rn(pt.w, 0.0f), 255.0f));
 }
 
-// ---- the reference's PYTHON front view (src/data.py:113-180) ---------------------------------------------------
-// np.arctan2 on float32 was the C library's atan2f when the reference was written; glibc's (<= 2.40) is the fdlibm
-// single-precision routine, which is not correctly rounded. This is that routine, operation for operation
-// (e_atan2f.c / s_atanf.c; restated on the CPU in oracle/pytwin_oracle.c and pinned there to libm's atan2f).
+// ---- the C library's atan2f ---------------------------------------------------------------------------------------
+// Used by the column bin of the C routine's front view (above) and by the reference's PYTHON front view
+// (src/data.py:113-180), where np.arctan2 on float32 was the C library's atan2f when the reference was written.
+// glibc's (<= 2.40) is the fdlibm single-precision routine, which is not correctly rounded. This is that routine,
+// operation for operation (e_atan2f.c / s_atanf.c; restated on the CPU in oracle/pytwin_oracle.c and pinned there to
+// libm's atan2f).
 __device__ __forceinline__ float fd_atanf(float x)
 {
     const float atanhi[4] = {4.6364760399e-01f, 7.8539812565e-01f, 9.8279368877e-01f, 1.5707962513e+00f};

@@ -120,7 +120,8 @@ class ViewEncoder:
         return out
 
     def debug_point_keys(self, points, top: TopParams, front: FrontParams | None = None):
-        """Test hook: per-point (cell, front pixel, front pixel by the all-double path) as int32 CUDA tensors."""
+        """Test hook: per-point (cell, front pixel, front pixel by the reference's own expressions -- no fast path)
+        as int32 CUDA tensors."""
         import torch
         n = points.shape[0]
         cell = torch.empty(n, dtype=torch.int32, device=points.device)

@@ -18,6 +18,7 @@ import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 RESTATED_SO = os.path.join(_HERE, "_build", "libview_oracle.so")
+PROBE_SO = os.path.join(_HERE, "_build", "libref_probe.so")
 REF_TOP_SO = os.path.join(_HERE, "_ref", "LidarTopPreprocess.so")
 REF_TOPFRONT_SO = os.path.join(_HERE, "_ref", "LidarTopAndFrontPreprocess.so")
 
@@ -31,6 +32,9 @@ def build(force: bool = False) -> None:
     if force or not os.path.exists(RESTATED_SO) or \
             os.path.getmtime(RESTATED_SO) < os.path.getmtime(os.path.join(_HERE, "view_oracle.c")):
         subprocess.run(["make", "-C", _HERE, "_build/libview_oracle.so"], check=True, capture_output=True)
+    if force or not os.path.exists(PROBE_SO) or \
+            os.path.getmtime(PROBE_SO) < os.path.getmtime(os.path.join(_HERE, "ref_probe.c")):
+        subprocess.run(["make", "-C", _HERE, "_build/libref_probe.so"], check=True, capture_output=True)
     if force or not reference_available():
         subprocess.run(["make", "-C", _HERE, "ref"], check=True, capture_output=True)
 
@@ -108,6 +112,25 @@ def point_keys(raw, top, front=None, semantics: str = "topfront"):
        front.phi_div if front else 1.0, front.theta_div if front else 1.0,
        float(front.cn) if front else 1.0, float(front.rn) if front else 1.0,
        cell.ctypes.data, pix.ctypes.data if pix is not None else None)
+    return cell, pix
+
+
+def reference_point_keys(raw, top, front):
+    """Per-point (cell, front pixel) decisions of the REFERENCE build, one point per call (oracle/ref_probe.c).
+    -1 = gated out / nothing stored inside the image. Needs oracle/_ref; use a small bird's-eye-view grid, the
+    reference allocates it afresh on every call."""
+    raw = _points(raw)
+    n = raw.shape[0]
+    guess = point_keys(raw, top, front)[1]
+    cell = np.empty(n, dtype=np.int32)
+    pix = np.empty(n, dtype=np.int32)
+    fn = _lib(PROBE_SO).ref_probe_points
+    fn.argtypes = [ctypes.c_char_p, _vp, _ci] + [_cf] * 9 + [_ci] * 3 + [_cf] * 2 + [_ci] * 2 + [_vp] * 3
+    fn.restype = _ci
+    rc = fn(REF_TOPFRONT_SO.encode(), raw.ctypes.data, n, *top.floats, top.xn, top.yn, top.zn, front.phi_div,
+            front.theta_div, front.cn, front.rn, guess.ctypes.data, cell.ctypes.data, pix.ctypes.data)
+    if rc:
+        raise RuntimeError("ref_probe_points: cannot load " + REF_TOPFRONT_SO)
     return cell, pix
 
 

@@ -25,9 +25,15 @@
  *       (float)((double)logf(count + 1.0f) / log(32.0)), clamped to 1       (:167-172 / :220-225)
  *   - intensity: intensity of the first point (input order) reaching the cell's max h (:141-152 / :159-171)
  *   - output cell is (X-1, Y-1); index Y_SIZE*(Z_SIZE+2)*(X-1) + (Z_SIZE+2)*(Y-1) + plane (:200,220,236)
- *   - front view (LidarTopAndFrontPreprocess.c:36-38,173-193): double-precision atan2/sqrt on promoted
- *       floats, RAD_TO_DEG = (float)(180/3.141596), truncating (int), inclusive upper bounds, plain stores
- *       (last point in input order wins). The reference writes past the end of front_data when
+ *   - front view (LidarTopAndFrontPreprocess.c:36-38,173-193), RAD_TO_DEG = (float)(180/3.141596), truncating
+ *       (int), inclusive upper bounds, plain stores (last point in input order wins). The two bins have DIFFERENT
+ *       types (the file is C++: <math.h> is libstdc++'s wrapper, `using namespace std`):
+ *         row R (:173): pow(float, int) promotes to double, so sqrt/atan2 and the scaling are all double;
+ *         col C (:174): atan2(point.y, point.x) has two float arguments -> std::atan2(float, float) = atan2f,
+ *                       and `* RAD_TO_DEG / theta_DIVISION` stays in float (cvttss2si). `nm -D` on the reference
+ *                       build imports both atan2 and atan2f. tests/test_oracle_vs_reference.py compares the
+ *                       per-point pixel with the reference build one point per call.
+ *       The reference writes past the end of front_data when
  *       r_coord == R_SIZE; this restatement applies the same linear index and DROPS stores at or
  *       beyond C_SIZE*R_SIZE*F_SIZE, so in-bounds cells stay identical.
  *
@@ -141,7 +147,7 @@ static int encode(const float *pts, int num, float *top, float *front,
             const double dx = x, dy = y, dz = z;
             const double planar = sqrt(dx * dx + dy * dy);
             const int R = cvtt_f64(atan2(dz, planar) * (double)rad_to_deg / (double)fp->phi_div);
-            const int C = cvtt_f64(atan2(dy, dx) * (double)rad_to_deg / (double)fp->theta_div);
+            const int C = cvtt_f32(atan2f(y, x) * rad_to_deg / fp->theta_div); /* float: atan2(float, float) */
             /* int + int compared against a float bound, as in the reference */
             const long r_coord = (long)R + center_r, c_coord = (long)C + center_c;
             if ((float)r_coord <= fp->r_size && (float)c_coord <= fp->c_size && r_coord >= 0 && c_coord >= 0) {
@@ -230,7 +236,7 @@ void oracle_point_keys(const void *raw_data, int num, int mode,
         if (!keep) continue;
         const double dx = x, dy = y, dz = z;
         const int R = cvtt_f64(atan2(dz, sqrt(dx * dx + dy * dy)) * (double)rad_to_deg / (double)phi_DIVISION);
-        const int C = cvtt_f64(atan2(dy, dx) * (double)rad_to_deg / (double)theta_DIVISION);
+        const int C = cvtt_f32(atan2f(y, x) * rad_to_deg / theta_DIVISION);
         const long r = (long)R + center_r, c = (long)C + center_c;
         if ((float)r <= R_SIZE && (float)c <= C_SIZE && r >= 0 && c >= 0) {
             const long q = r * (long)cvtt_f32(C_SIZE) + c;

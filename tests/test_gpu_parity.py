@@ -164,7 +164,7 @@ def test_config5_dense_cloud(torch_cuda, oracle_mod, strategy):
 @pytest.mark.parametrize("semantics", ["top", "topfront"])
 def test_per_point_decisions_20M(torch_cuda, oracle_mod, semantics):
     """Every point's gate/cell and front-view pixel, one by one, on 20 M random points: the production
-    arithmetic (float fast path + exact fallback) == the all-double GPU path == the CPU oracle."""
+    arithmetic (float fast paths + exact fallbacks) == the reference's own expressions on the GPU == the CPU oracle."""
     torch = torch_cuda
     from mv3d_b200.encoder import ViewEncoder
     from mv3d_b200.params import FrontParams
@@ -183,6 +183,26 @@ def test_per_point_decisions_20M(torch_cuda, oracle_mod, semantics):
         total += len(pts)
         mism += np.count_nonzero(cell != ecell) + np.count_nonzero(pix != epix) + np.count_nonzero(pix_exact != epix)
     assert mism == 0, f"{mism} per-point mismatches in {total} points"
+    enc.close()
+
+
+def test_per_point_pixels_equal_reference_golden(torch_cuda):
+    """Per-point cell and front-view pixel against what the REFERENCE build itself produced one point per call
+    (tests/golden/ver3_point_keys.npz, written by tests/golden/make_golden.py through oracle/ref_probe.c): all four
+    quadrants, the axes, the round-1 counter-example of the column bin (atan2f in float, (28, 304) not (28, 303))."""
+    torch = torch_cuda
+    import os
+    import golden.make_golden as mg
+    from mv3d_b200.encoder import ViewEncoder
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ver3_point_keys.npz"))
+    enc = ViewEncoder(0, semantics="topfront")
+    for name, pts in mg.point_clouds().items():
+        cell, pix, pix_exact = enc.debug_point_keys(torch.from_numpy(pts).cuda(), mg.probe_top(), KITTI_FRONT_64x512)
+        want = g[name + "/pix"]
+        for got, what in ((pix.cpu().numpy(), "production path"), (pix_exact.cpu().numpy(), "exact path")):
+            bad = np.flatnonzero(got != want)
+            assert bad.size == 0, f"{name}, {what}: {bad.size} points differ, first {pts[bad[0]]}: {got[bad[0]]} vs {want[bad[0]]}"
+        assert np.array_equal(cell.cpu().numpy(), g[name + "/cell"].astype(np.int32)), name
     enc.close()
 
 
