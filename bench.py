@@ -12,7 +12,11 @@ i mod N), no collective on the data path, so scaling is weak: every rank encodes
   e2e       sweeps/s through mv3d_encode_batch_host with pinned HOST buffers: H2D of the points, encode, D2H of
             both encoded tensors, every step
   roofline  the dominant kernel (tile_build_kernel) against measured HBM bandwidth, timed live with CUDA
-            events recorded by the library around each launch inside the timed region
+            events recorded by the library around each launch in a SECOND pass of the same K steps (event records
+            between the kernels of a step would switch off their programmatic dependent launch overlap, so the
+            first pass -- the one `value` comes from -- carries only the step marks)
+  also      short device-timed legs for the other BASELINE.json configs (1, 3, 5; config 4 = the sharded stream with
+            the ring of output slots, at every N) and for the rows widened around the path
   cpu_baseline  the reference's unmodified C code (oracle/_ref) on this box's host cores, rank 0, N=1 only
 
 Prints ONE JSON line on rank 0.
@@ -45,7 +49,11 @@ def parse_args():
     ap.add_argument("--strategy", default="auto", choices=["auto", "tile", "patch", "atomic", "sort"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
-    ap.add_argument("--no-also", action="store_true", help="skip the short legs for the widened rows (profiling runs)")
+    ap.add_argument("--no-also", action="store_true", help="skip the short legs for the other configs / widened rows (profiling runs)")
+    ap.add_argument("--only-e2e", action="store_true", help="host-buffer leg only (e2e tuning runs; prints the same line, value = e2e)")
+    ap.add_argument("--config4-frames", type=int, default=262144,
+                    help="frames of the config-4 stream leg over ALL ranks (strong scaling; 4096 x 64 by default so that "
+                         "an 8-GPU run still times >= 0.5 s per rank)")
     return ap.parse_args()
 
 
@@ -66,12 +74,17 @@ def measured_hbm_peak():
 
 
 def ncu_traffic(kernel):
-    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture, or None."""
+    """(dram bytes per launch, where it comes from) for a kernel, from the committed ncu --set full capture
+    (profiles/traffic.json: {kernel: {"bytes", "commit", "ncu_file"}}, written by profiles/summarize_ncu.py), or
+    (None, None). It is a profiler measurement of an earlier run of the same kernel, stamped with its commit."""
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            return json.load(f).get(kernel)
+            e = json.load(f).get(kernel)
+        if isinstance(e, dict):
+            return e.get("bytes"), {k: e.get(k) for k in ("commit", "ncu_file", "workload")}
+        return e, None
     except Exception:
-        return None
+        return None, None
 
 
 class ClockSampler:
@@ -127,6 +140,11 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------------
 # CPU legs (the only places bench.py executes oracle/): cpu_baseline and --impl reference
 # ------------------------------------------------------------------------------------------------------
+def bench_config():
+    """The `config` object: identical for both arms (the driver compares them), workload facts only."""
+    return {"workload": WORKLOAD, "batch_per_gpu": BATCH, "points_per_sweep": 120000}
+
+
 def cpu_baseline(top, front):
     """Bounded sample of the same workload on the host cores: every core encodes 8 config-1 sweeps."""
     from oracle.cpu_bench import CpuEncoderPool
@@ -171,7 +189,8 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "sweeps/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": elapsed / args.steps * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "batch_per_step": sample, "runs_on": "host CPU"},
+        "config": bench_config(),
+        "run": {"runs_on": "host CPU", "sweeps_per_step": sample},
         "cpu_baseline": {"value": value, "unit": "sweeps/s", "cores": pool.cores, "kind": pool.kind,
                          "sample": f"each step = {sample} sweeps of the workload's batch through "
                                    f"createTopAndFrontMaps on multiprocessing.Pool({pool.cores})"},
@@ -182,8 +201,157 @@ def run_reference(args):
 
 
 # ------------------------------------------------------------------------------------------------------
-# short legs for the rows built around the path (not the headline metric; device-resident, same 64 sweeps)
+# short legs (device-timed, outside the headline's timed region): the other BASELINE.json configs and the rows
+# built around the path. Each figure carries the algorithmic GB/s of SURVEY.md 8(d) and its fraction of the peak.
 # ------------------------------------------------------------------------------------------------------
+def _rate(torch, fn, steps, warm=3):
+    """Seconds per call of fn (CUDA events on the current stream, after warm-up)."""
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e-3 / steps
+
+
+def other_configs(device, steps, peak):
+    """BASELINE.json configs[0], [2], [4] ("config 1 / 3 / 5") on one GPU, inputs resident in HBM."""
+    import numpy as np
+    import torch
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.params import DENSE_TOP, KITTI_FRONT_64x512, KITTI_PAPER_TOP
+    from mv3d_b200.sweeps import dense_cloud, hdl64_sweep, pack_sweeps
+    from mv3d_b200.ver3 import createTopAndFrontMaps
+    dev = torch.device("cuda", device)
+    top_p, front_p = KITTI_PAPER_TOP, KITTI_FRONT_64x512
+    out = {}
+
+    def entry(sec, units, nbytes, unit, what, **extra):
+        gbs = nbytes / sec / 1e9
+        return dict({"value": units / sec, "unit": unit, "ms_per_call": sec * 1e3, "algorithmic_GBps": gbs,
+                     "frac": gbs / peak, "what": what}, **extra)
+
+    # config 1: ONE sweep per call (what AUTO picks for it), device-resident; then the reference symbol, numpy buffers
+    s0 = hdl64_sweep(0)
+    pts, offs = pack_sweeps([s0])
+    d = torch.from_numpy(pts).to(dev)
+    ab = algorithmic_bytes(top_p, front_p, s0.shape[0])
+    enc = ViewEncoder(device, semantics="topfront", strategy="auto")
+    t1 = torch.empty((1, *top_p.shape), dtype=torch.float32, device=dev)
+    f1 = torch.empty((1, *front_p.shape), dtype=torch.float32, device=dev)
+    sec = _rate(torch, lambda: enc.encode_device(d, offs, top_p, front_p, top_out=t1, front_out=f1), max(steps * 5, 50))
+    out["config1_single_sweep"] = entry(sec, 1, ab["total"], "sweeps/s",
+                                        "one 120k-pt sweep per mv3d_encode_batch_dev call, BEV 704x800x27 + FV 64x512x3",
+                                        strategy=enc.resolved_strategy(top_p) + " (AUTO refines per call: atomic for <= 4 sweeps)")
+    h_top, h_front = np.ones(top_p.shape, np.float32), np.ones(front_p.shape, np.float32)
+    for _ in range(3):
+        createTopAndFrontMaps(s0, s0.shape[0], h_top, h_front, top_p.as_top_paras(), front_p.as_front_paras())
+    t0 = time.perf_counter()
+    reps = max(steps, 10)
+    for _ in range(reps):
+        createTopAndFrontMaps(s0, s0.shape[0], h_top, h_front, top_p.as_top_paras(), front_p.as_front_paras())
+    sec = (time.perf_counter() - t0) / reps
+    out["config1_reference_symbol"] = {"value": 1.0 / sec, "unit": "sweeps/s", "ms_per_call": sec * 1e3,
+                                       "what": "createTopAndFrontMaps(...) with pageable numpy buffers: H2D, encode, "
+                                               "compact read-back, dense rebuild in the caller's buffer, wall clock"}
+    del t1, f1
+
+    # config 3: front view only, 64 sweeps per launch (the BEV gate still applies; no BEV tensor is written)
+    sweeps = [hdl64_sweep(i) for i in range(BATCH)]
+    pts, offs = pack_sweeps(sweeps)
+    d64 = torch.from_numpy(pts).to(dev)
+    f64 = torch.empty((BATCH, *front_p.shape), dtype=torch.float32, device=dev)
+    sec = _rate(torch, lambda: enc.encode_device(d64, offs, top_p, front_p, front_out=f64, want_top=False), max(steps, 10))
+    nbytes = BATCH * (ab["points"] + ab["fv"])
+    out["config3_front_only"] = entry(sec, BATCH, nbytes, "sweeps/s", "FV 64x512x3 only, 64 sweeps per launch")
+    enc.close()
+    del d64, f64
+
+    # config 5: 8 aggregated clouds of 2 M points, 1408x1600x(8+2) at 0.05 m
+    cloud = dense_cloud()
+    n5 = 8
+    pts, offs = pack_sweeps([cloud] * n5)
+    d5 = torch.from_numpy(pts).to(dev)
+    t5 = torch.empty((n5, *DENSE_TOP.shape), dtype=torch.float32, device=dev)
+    nbytes = n5 * (16 * cloud.shape[0] + 4 * DENSE_TOP.xn * DENSE_TOP.yn * (DENSE_TOP.zn + 2))
+    for strategy in ("auto", "tile"):
+        e5 = ViewEncoder(device, semantics="top", strategy=strategy)
+        sec = _rate(torch, lambda: e5.encode_device(d5, offs, DENSE_TOP, top_out=t5), max(steps, 10))
+        key = "config5_dense_cloud" if strategy == "auto" else "config5_dense_cloud_tile"
+        out[key] = entry(sec, n5, nbytes, "clouds/s", "createTopMaps on 8 clouds of 2 M points, BEV 1408x1600x10",
+                         strategy=strategy if strategy != "auto" else "auto -> atomic (points weigh 36 % of the output bytes)")
+        e5.close()
+    return out
+
+
+def config4_stream(rank, world, device, total_frames, peak):
+    """BASELINE.json configs[3] ("config 4"): a frame-sharded stream over all ranks (frame i -> rank i mod world, no
+    collective), inputs pre-staged in each GPU's HBM, a ring of two output slots, consumer = the per-frame checksum
+    kernel. Strong scaling: `total_frames` is fixed, every rank streams its share. Returns this rank's record; the
+    caller takes the max of `seconds` over ranks."""
+    import torch
+    from mv3d_b200 import shard
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.params import KITTI_FRONT_64x512, KITTI_PAPER_TOP
+    from mv3d_b200.stream import ResidentStream
+    from mv3d_b200.sweeps import hdl64_sweep, pack_sweeps
+    dev = torch.device("cuda", device)
+    top_p, front_p = KITTI_PAPER_TOP, KITTI_FRONT_64x512
+    mine = len(shard.frames_of(rank, world, total_frames))
+    # Frames repeat with period 128 (generating 262 144 distinct synthetic sweeps on the host would take minutes; the
+    # encoder never sees which frames repeat), so a rank's batches repeat too: two distinct batches, staged once.
+    staged = []
+    for k in range(2):
+        ids = [(rank + world * (BATCH * k + j)) % 128 for j in range(BATCH)]
+        pts, offs = pack_sweeps([hdl64_sweep(f) for f in ids])
+        staged.append((torch.from_numpy(pts).to(dev), offs))
+    stream = ResidentStream(device, top_p, front_p, batch=BATCH, depth=2)
+    chk = ViewEncoder(device)
+    sums = torch.zeros((2, BATCH), dtype=torch.int64, device=dev)
+
+    def batches():
+        done, k = 0, 0
+        while done < mine:
+            d_pts, offs = staged[k % 2]
+            nb = min(BATCH, mine - done)
+            yield (d_pts, offs[: nb + 1])
+            done += nb
+            k += 1
+
+    def run(limit=None):
+        n = 0
+        for k, top, front in stream.run(batches()):
+            nb = top.shape[0]
+            chk.frame_checksums(top, out=sums[0, :nb])
+            chk.frame_checksums(front, out=sums[1, :nb])
+            n += nb
+            if limit and k + 1 >= limit:
+                break
+        return n
+
+    run(limit=4)  # warm-up: workspaces, both ring slots
+    torch.cuda.synchronize()
+    launches0 = stream.launch_count + chk.launch_count
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    n = run()
+    e1.record()
+    torch.cuda.synchronize()
+    sec = e0.elapsed_time(e1) * 1e-3
+    launches = stream.launch_count + chk.launch_count - launches0
+    stream.close()
+    chk.close()
+    return {"frames_this_rank": n, "seconds": sec, "gpu_launches": launches, "total_frames": total_frames}
+
+
 def widened_rows(d_pts, offs, device, steps):
     import torch
     from mv3d_b200.anchors import AnchorFilter, make_anchors
@@ -192,16 +360,7 @@ def widened_rows(d_pts, offs, device, steps):
     from mv3d_b200.pytwin import PyTwinEncoder
 
     def rate(fn):
-        for _ in range(3):
-            fn()
-        torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
-            fn()
-        e1.record()
-        torch.cuda.synchronize()
-        return BATCH * steps / (e0.elapsed_time(e1) * 1e-3)
+        return BATCH / _rate(torch, fn, steps)
 
     out = {"unit": "sweeps/s", "steps": steps, "batch": BATCH}
     py = PyTwinEncoder(device)
@@ -234,12 +393,13 @@ def run_ours(args):
 
     # CPU baseline first: it forks worker processes, which must happen before CUDA is initialised here.
     cpu = None
-    if world == 1 and rank == 0 and not args.no_cpu_baseline:
+    if world == 1 and rank == 0 and not args.no_cpu_baseline and not args.only_e2e:
         cpu = cpu_baseline(top_p, front_p)
 
     import numpy as np
     import torch
     import torch.distributed as dist
+    from mv3d_b200 import _lib
     from mv3d_b200.encoder import ViewEncoder, pinned_empty
     from mv3d_b200.sweeps import hdl64_sweep, pack_sweeps
 
@@ -255,6 +415,20 @@ def run_ours(args):
         if world > 1:
             dist.barrier()
 
+    def max_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(x):
+        if world == 1:
+            return float(x)
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
     # frame i -> rank i mod world (BASELINE.json config 4); every rank holds BATCH sweeps
     sweeps = [hdl64_sweep(rank + world * i) for i in range(BATCH)]
     pts, offs = pack_sweeps(sweeps)
@@ -264,6 +438,8 @@ def run_ours(args):
     front_out = torch.empty((BATCH, *front_p.shape), dtype=torch.float32, device=dev)
     enc = ViewEncoder(local_rank, semantics="topfront", strategy=args.strategy)
     strategy = enc.resolved_strategy(top_p)
+    peak, peak_src = measured_hbm_peak()
+    ab = algorithmic_bytes(top_p, front_p, n_points // BATCH)
 
     def step():
         enc.encode_device(d_pts, offs, top_p, front_p, top_out=top_out, front_out=front_out)
@@ -272,40 +448,49 @@ def run_ours(args):
         step()
     torch.cuda.synchronize()
 
-    # ---- timed region: inputs resident in HBM --------------------------------------------------------
-    sampler = ClockSampler(local_rank)
-    enc.kernel_times(reset=True)
-    enc.set_profiling(True)
-    launches0 = enc.launch_count
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    torch.cuda.synchronize()
-    if rank == 0:
-        sampler.start()
-    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps - 1)]  # between steps: no synchronisation
-    ev0.record()
-    for k in range(args.steps):
-        step()
-        if k < args.steps - 1:
-            marks[k].record()
-    ev1.record()
-    torch.cuda.synchronize()
-    barrier()
-    edges = [ev0] + marks + [ev1]
-    step_times = sorted(edges[k].elapsed_time(edges[k + 1]) for k in range(args.steps))
+    value = elapsed_ms = launches = None
+    clocks = ktimes = None
+    step_times = []
+    if not args.only_e2e:
+        # ---- pass 1, the timed region: inputs resident in HBM, nothing but the step marks between the launches ----
+        sampler = ClockSampler(local_rank)
+        launches0 = enc.launch_count
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        torch.cuda.synchronize()
+        if rank == 0:
+            sampler.start()
+        marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps - 1)]  # between steps: no synchronisation
+        ev0.record()
+        for k in range(args.steps):
+            step()
+            if k < args.steps - 1:
+                marks[k].record()
+        ev1.record()
+        torch.cuda.synchronize()
+        barrier()
+        edges = [ev0] + marks + [ev1]
+        step_times = sorted(edges[k].elapsed_time(edges[k + 1]) for k in range(args.steps))
+        clocks = sampler.stop() if rank == 0 else None
+        launches = enc.launch_count - launches0
+        elapsed_ms = max_over_ranks(ev0.elapsed_time(ev1))
+        value = world * BATCH * args.steps / (elapsed_ms * 1e-3)
+
+        # ---- pass 2, the same K steps with an event pair around every kernel launch (roofline breakdown) ----------
+        enc.kernel_times(reset=True)
+        enc.set_profiling(True)
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        for k in range(args.steps):
+            step()
+        p1.record()
+        torch.cuda.synchronize()
+        enc.set_profiling(False)
+        ktimes = enc.kernel_times(reset=True)
+        profiled_ms_per_step = p0.elapsed_time(p1) / args.steps
 
     def pct(q):
         return step_times[min(len(step_times) - 1, max(0, int(round(q * (len(step_times) - 1)))))]
-    clocks = sampler.stop() if rank == 0 else None
-    elapsed_ms = ev0.elapsed_time(ev1)
-    launches = enc.launch_count - launches0
-    enc.set_profiling(False)
-    ktimes = enc.kernel_times(reset=True)
-    if world > 1:
-        t = torch.tensor([elapsed_ms], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        elapsed_ms = float(t.item())
-    value = world * BATCH * args.steps / (elapsed_ms * 1e-3)
 
     # ---- e2e: pinned host buffers through mv3d_encode_batch_host, H2D + encode + D2H every step --------
     e2e = None
@@ -321,65 +506,97 @@ def run_ours(args):
         t0 = time.perf_counter()
         for _ in range(args.steps):
             enc.encode_host(h_pts, offs, top_p, front_p, top_out=h_top, front_out=h_front)
-        e2e_s = time.perf_counter() - t0
+        e2e_s = max_over_ranks(time.perf_counter() - t0)
         h2d_total, d2h_total = enc.transfer_bytes()
         checksum = float(h_top[0, :, :, top_p.zn + 1].sum()) + float(h_front[0].sum())  # touch the result
-        if world > 1:
-            t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            e2e_s = float(t.item())
-        e2e = {"value": world * BATCH * args.steps / e2e_s, "unit": "sweeps/s",
+        result_bytes = int(h_top.nbytes + h_front.nbytes)
+        # what the host memory of THIS box takes: all ranks fill at once with the thread count and pinning the run used
+        lws = int(os.environ.get("LOCAL_WORLD_SIZE", "1"))
+        cores = os.cpu_count() or 1
+        threads = int(os.environ.get("MV3D_HOST_THREADS", "0")) or max(2, min(16, cores // max(lws, 1)))
+        pin = int(os.environ.get("MV3D_HOST_PIN", "1" if lws > 1 else "0"))
+        barrier()
+        fill = _lib.load_library().mv3d_debug_host_fill_gbs(256 << 20, threads, 4, local_rank if pin else 0, lws if pin else 0)
+        fill_all = sum_over_ranks(max(fill, 0.0))
+        e2e_value = world * BATCH * args.steps / e2e_s
+        fill_used = world * result_bytes * args.steps / e2e_s / 1e9
+        e2e = {"value": e2e_value, "unit": "sweeps/s",
                "h2d_bytes_per_step": h2d_total // args.steps, "d2h_bytes_per_step": d2h_total // args.steps,
-               "host_result_bytes_per_step": int(h_top.nbytes + h_front.nbytes),
+               "host_result_bytes_per_step": result_bytes,
                "readback": os.environ.get("MV3D_HOST_READBACK", "compact"),
                "ms_per_step": e2e_s / args.steps * 1e3, "api": "mv3d_encode_batch_host (pinned host buffers)",
+               "host_fill_gbs": fill_used,
+               "host_fill_ceiling_gbs": fill_all,
+               "host_fill_frac": fill_used / fill_all if fill_all > 0 else None,
+               "host": {"cpus": cores, "ranks_on_host": lws, "fill_threads_per_rank": threads, "pinned_to_cpu_share": bool(pin),
+                        "what": "host_fill_gbs = bytes of finished tensors written into the caller's host buffers per "
+                                "second, all ranks; ceiling = streaming zero-fill of fresh memory by the same threads "
+                                "on all ranks at once (mv3d_debug_host_fill_gbs) -- any implementation that delivers "
+                                "the dense tensor through the CPU is bound by it"},
                "result_checksum": checksum}
+        del h_top, h_front, h_pts
 
-    # ---- also (N=1 only, outside the timed region above): the rows built around the path, SURVEY.md 8(f) -------
+    # ---- also: the other configs and the widened rows (outside the timed regions above) ------------------
     also = None
-    if world == 1 and not args.no_also:
-        also = widened_rows(d_pts, offs, local_rank, max(3, min(args.steps, 10)))
+    if not args.no_also and not args.only_e2e:
+        also = {}
+        del top_out, front_out
+        torch.cuda.empty_cache()
+        c4 = config4_stream(rank, world, local_rank, args.config4_frames, peak)
+        c4_s = max_over_ranks(c4["seconds"])
+        c4_launches = sum_over_ranks(c4["gpu_launches"])
+        also["config4_stream"] = {
+            "value": args.config4_frames / c4_s, "unit": "sweeps/s", "n_gpus": world, "frames": args.config4_frames,
+            "seconds_slowest_rank": c4_s, "scaling": "strong", "gpu_launches": int(c4_launches),
+            "algorithmic_GBps": args.config4_frames * ab["total"] / c4_s / 1e9,
+            "frac_of_n_gpu_peak": args.config4_frames * ab["total"] / c4_s / 1e9 / (peak * world),
+            "what": "configs[3]: frame-sharded stream (frame i -> rank i mod N, no collective), inputs pre-staged in HBM, "
+                    "ring of two output slots, per-frame checksum kernel as the consumer (reads every output byte once)"}
+        if world == 1:
+            also.update(other_configs(local_rank, max(3, min(args.steps, 10)), peak))
+            also["widened_rows"] = widened_rows(d_pts, offs, local_rank, max(3, min(args.steps, 10)))
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel ---------------------------------------------------------------
-    ab = algorithmic_bytes(top_p, front_p, n_points // BATCH)
-    peak, peak_src = measured_hbm_peak()
-    dominant = max(ktimes, key=lambda k: ktimes[k][0])
-    dom_ms, dom_launches = ktimes[dominant]
-    step_kernel_ms = sum(v[0] for v in ktimes.values())
-    # bytes the dominant kernel is responsible for, per launch
-    # (a step may launch it several times: one launch per pipelined sub-batch)
-    per_step = {"tile_build_kernel": ab["bev"] * BATCH, "fill_tma_kernel": ab["bev"] * BATCH, "fill_zero_kernel": ab["bev"] * BATCH,
-                "ce_zero_fill": ab["bev"] * BATCH}.get(dominant, ab["total"] * BATCH)
-    per_launch = per_step * args.steps / max(dom_launches, 1)
-    achieved = per_launch / (dom_ms / max(dom_launches, 1) * 1e-3) / 1e9 if dom_ms > 0 else 0.0
-    step_achieved = ab["total"] * BATCH * args.steps / (elapsed_ms * 1e-3) / 1e9
-    traffic = ncu_traffic(dominant)
-    roofline = {"bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": per_launch,
-                "kernel_ms_per_launch": dom_ms / max(dom_launches, 1),
-                "kernel_launches_per_step": dom_launches / args.steps,
-                "kernel_share_of_step": dom_ms / step_kernel_ms if step_kernel_ms else None,
-                "step_achieved": step_achieved, "step_frac": step_achieved / peak,
-                "algorithmic_bytes_per_sweep": ab["total"],
-                "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items() if v[1]}}
-
     line = {
-        "metric": METRIC, "value": value, "unit": "sweeps/s", "n_gpus": world, "steps": args.steps,
-        "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "batch_per_gpu": BATCH, "points_per_sweep": n_points // BATCH,
-                   "strategy": strategy, "sharding": f"frame i -> rank i mod {world}, no collective",
-                   "l2": "each step writes 3.9 GB of output per GPU (>> 126 MB L2), so no step starts with a warm L2"},
-        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-        "step_ms": {"median": pct(0.5), "p5": pct(0.05), "p95": pct(0.95), "min": step_times[0], "max": step_times[-1],
-                    "what": "rank 0, CUDA events between the steps of the timed region"},
+        "metric": METRIC, "value": value if value is not None else (e2e or {}).get("value"), "unit": "sweeps/s",
+        "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": elapsed_ms / args.steps if elapsed_ms else (e2e or {}).get("ms_per_step"),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": bench_config(),
+        "run": {"strategy": strategy, "sharding": f"frame i -> rank i mod {world}, no collective",
+                "l2": "each step writes 3.9 GB of output per GPU (>> 126 MB L2), so no step starts with a warm L2",
+                "programmatic_dependent_launch": os.environ.get("MV3D_PDL", "1") != "0"},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches) if launches is not None else None,
     }
+    if ktimes is not None:
+        # ---- roofline of the dominant kernel (algorithmic bytes per launch) ----------------
+        dominant = max(ktimes, key=lambda k: ktimes[k][0])
+        dom_ms, dom_launches = ktimes[dominant]
+        step_kernel_ms = sum(v[0] for v in ktimes.values())
+        per_step = {"tile_build_kernel": ab["bev"] * BATCH, "fill_zero_kernel": ab["bev"] * BATCH,
+                    "ce_zero_fill": ab["bev"] * BATCH}.get(dominant, ab["total"] * BATCH)
+        per_launch = per_step * args.steps / max(dom_launches, 1)
+        achieved = per_launch / (dom_ms / max(dom_launches, 1) * 1e-3) / 1e9 if dom_ms > 0 else 0.0
+        step_achieved = ab["total"] * world * BATCH * args.steps / (elapsed_ms * 1e-3) / 1e9 / world  # per GPU
+        traffic, traffic_src = ncu_traffic(dominant)
+        line["roofline"] = {
+            "bound": "hbm", "kernel": dominant, "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+            "algorithmic_bytes_per_launch": per_launch,
+            "kernel_ms_per_launch": dom_ms / max(dom_launches, 1),
+            "kernel_launches_per_step": dom_launches / args.steps,
+            "kernel_share_of_step": dom_ms / step_kernel_ms if step_kernel_ms else None,
+            "step_achieved": step_achieved, "step_frac": step_achieved / peak,
+            "algorithmic_bytes_per_sweep": ab["total"],
+            "kernels_ms_per_step": {k: v[0] / args.steps for k, v in ktimes.items() if v[1]},
+            "kernel_timing": "second pass of the same steps with a CUDA event pair around every launch, on the "
+                             "launching stream; that pass ran at %.4f ms per step" % profiled_ms_per_step}
+        line["step_ms"] = {"median": pct(0.5), "p5": pct(0.05), "p95": pct(0.95), "min": step_times[0], "max": step_times[-1],
+                           "what": "rank 0, CUDA events between the steps of the timed region"}
     if cpu is not None:
         line["cpu_baseline"] = cpu
     if also is not None:

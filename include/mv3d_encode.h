@@ -201,8 +201,17 @@ int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, const unsign
  * of the finished values). */
 int mv3d_debug_expand_split(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n, int threads);
 
+/* Diagnostic (no GPU needed): GB/s at which `threads` threads of the library's host pool zero-fill `bytes` of memory
+ * with streaming stores (best of `reps` passes) -- the ceiling of any implementation that must write the caller's dense
+ * host tensor through the CPU; bench.py prints it beside the end-to-end figure. pin_sharers > 0 pins the threads to
+ * share `pin_share_index` of `pin_sharers` of this process's CPUs, as the host entry points do under torchrun.
+ * Returns < 0 on failure. */
+double mv3d_debug_host_fill_gbs(size_t bytes, int threads, int reps, int pin_share_index, int pin_sharers);
+
 /* The strategy a request resolves to for a parameter set (tile strategies fall back to _ATOMIC when a tile
- * cannot fit shared memory). AUTO additionally switches _TILE to _PATCH per call for large batches. */
+ * cannot fit shared memory). AUTO is refined per call: _ATOMIC for device calls of up to four sweeps or when the points
+ * weigh more than 7 % of the output bytes, _TILE otherwise (measured crossovers); it never picks
+ * _PATCH or _SORT. */
 int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy);
 
 /* Library / build identification, e.g. "mv3d_encode 0.1 sm_100a". */

@@ -79,13 +79,13 @@ struct HostSlot {
 
 // Kernel classes, in the order mv3d_kernel_name() reports them.
 enum KernelId { K_CLASSIFY = 0, K_TILE_SCAN, K_BIN, K_TILE_BUILD, K_FRONT_FINALIZE, K_FILL_ZERO, K_ATOMIC_SCATTER,
-                K_ATOMIC_FINALIZE, K_FILL_TMA, K_WARP_PATCH, K_TILE_COMPACT, K_PYFRONT_LINK,
+                K_ATOMIC_FINALIZE, K_TILE_COMPACT, K_PYFRONT_LINK,
                 K_PYFRONT_REDUCE, K_ANCHOR_OCCUPANCY, K_ANCHOR_TEST, K_ANCHOR_SUM, K_ANCHOR_COMPACT, K_FILL_CE,
                 K_TILE_PATCH, K_SORT_KEYS, K_RADIX_SORT, K_SORT_REDUCE, K_COUNT };
 static const char *const kKernelNames[K_COUNT] = {"classify_kernel", "tile_scan_kernel", "bin_kernel",
                                                   "tile_build_kernel", "front_finalize_kernel", "fill_zero_kernel",
                                                   "atomic_scatter_kernel", "atomic_finalize_kernel",
-                                                  "fill_tma_kernel", "warp_patch_kernel", "tile_compact_kernel",
+                                                  "tile_compact_kernel",
                                                   "pyfront_link_kernel", "pyfront_reduce_kernel",
                                                   "anchor_occupancy_kernel", "anchor_test_kernel",
                                                   "anchor_sum_kernel", "anchor_compact_kernel",
@@ -119,24 +119,13 @@ struct mv3d_ctx {
     unsigned compact_est = 0;  // entries the previous sweep produced: sizes the speculative copy of the next one
     long long launches = 0;
     size_t tile_bytes_target = 0;
-    size_t patch_tile_bytes = 0;          // tile size of the PATCH strategy (no tile store: smaller tiles, more CTAs)
-    int fill_chunk = 0;                   // sweeps per zero-fill launch of the PATCH strategy
-    int fill_ctas = 0;                    // fill CTAs per SM (one issuing thread each)
-    int fill_pending = 0;                 // bulk stores each fill CTA keeps in flight (> 16: unbounded)
-    int tile_store = 1;                   // MV3D_TILE_STORE: how the tile kernel writes a tile (1 = bulk stores, evict-first)
+    int fill_chunk = 0;                   // PATCH: sweeps per copy-engine zero-fill
     int auto_atomic_batch = 4;            // AUTO: up to this many sweeps per device call go to the atomic strategy
     double auto_atomic_ratio = 0.07;      // AUTO: ... and so do calls whose points weigh more than this share of the output bytes
-    int patch_mode = 1;                   // MV3D_PATCH_MODE: 1 = copy-engine zero-fill + tile_patch_kernel, 0 = TMA fill kernel + warp_patch_kernel
-    int pipe_groups = 0;                  // MV3D_TILE_PIPE=G[,threads[,chunk[,pending]]]: pipelined tile kernel (0 = off)
-    int pipe_group_threads = 192;
-    int pipe_chunk = 8640;
-    int pipe_pending = 0;
-    int front_aside = 1;                  // TILE: finish the front view on the side stream (MV3D_FRONT_ASIDE=0: in line)
-    int atomic_overlap = 0;               // ATOMIC: TMA zero-fill on the side stream, chunked (MV3D_ATOMIC_OVERLAP=1)
     size_t smem_per_sm = 0;
-    int patch_min_batch = 0;              // AUTO picks PATCH from this batch size on
-    int sub_batch = 0;                    // sweeps per pipeline stage of the tile strategy (0 = no pipelining)
-    cudaStream_t side_stream = nullptr;   // runs the point passes ahead of the tile kernel
+    struct TileConfig { size_t smem; int py; int blocks_per_sm; };
+    std::vector<TileConfig> tile_cfg;     // shared-memory opt-in + occupancy of the tile kernels, per (size, semantics)
+    cudaStream_t side_stream = nullptr;   // copy-engine zero-fill of the PATCH strategy
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_ready[kMaxBatchPerLaunch] = {nullptr};
     cudaEvent_t ev_order = nullptr;       // end of the latest device call on this context (see StreamOrder)
     cudaStream_t order_stream = nullptr;

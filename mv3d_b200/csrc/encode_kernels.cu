@@ -10,12 +10,10 @@
 //      touched cells in place, and writes the tile -- zeros included -- with ONE bulk async (TMA) store.
 //      Every output byte is written exactly once and never read; HBM traffic = the algorithmic bytes.
 //
-//  PATCH           fill_tma (side stream)  ||  classify -> scan -> bin ; then warp_patch per chunk of sweeps
-//      The zero-fill of the output needs no point data and almost no SM resources when it is done by bulk
-//      async (TMA) stores from one all-zero shared-memory buffer, so it runs beside the compute/latency-bound
-//      point passes instead of after them. Points are binned by small tiles; one WARP then owns a tile:
-//      it reduces the tile's records in a private shared-memory image and overwrites only the 32-byte
-//      sectors of the (already zero) output that hold a touched cell.
+//  PATCH           copy-engine zero-fill (side stream)  ||  classify -> scan -> bin ; then tile_patch per chunk of sweeps
+//      The zero-fill of the output needs no point data and no SM at all when the copy engine does it
+//      (cudaMemsetAsync: 7.0-7.3 TB/s), so it runs beside the point passes; the tile reduction then writes only
+//      the touched cells into the (already zero) output. Kept as the measured comparison point of DESIGN.md 5.1.
 //
 //  ATOMIC          fill_zero -> atomic_scatter -> atomic_finalize
 //      Zero-fill the output, reduce with global atomics straight into the output cells (tagged raw values),
@@ -26,6 +24,8 @@
 // winner and writes the whole image (zeros included) once.
 #include "encode_kernels.h"
 #include "view_math.cuh"
+
+#include <mutex>
 
 namespace mv3d {
 
@@ -86,31 +86,22 @@ __device__ __forceinline__ void bulk_wait_read_all()
 {
     asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
 }
-// How the tile kernel writes a finished tile (ViewParams::store_mode; MV3D_TILE_STORE=tma|tma_hint|tma_split|lsu|lsu_cs).
-// Default: bulk stores with an L2 evict-first policy -- the output is written once and never read back here, so it
-// should not push the bin records (read by this same kernel) out of L2. Measured in profiles/strategy_experiments_r1.md.
-// kStorePatch: the output has been zero-filled already (copy engine); write the touched cells only.
-enum TileStore { kStoreTma = 0, kStoreTmaHint = 1, kStoreTmaSplit = 2, kStoreLsu = 3, kStoreLsuStream = 4, kStoreTmaPaced = 5, kStorePatch = 6 };
-__device__ __forceinline__ void tile_bulk_store(void *gdst, const void *ssrc, uint32_t bytes, int mode)
+// How the tile kernel writes a finished tile: one bulk store of the whole image, with an L2 evict-first policy -- the
+// output is written once and never read back here, so it should not push the bin records (read by this same kernel)
+// out of L2 -- or, when the copy engine has zero-filled the output already (PATCH), the touched cells only.
+// (Round 1 also measured plain / split / paced bulk stores and LSU copies of the image: tools/experiments/.)
+enum TileStore { kStoreBulk = 0, kStorePatch = 1 };
+// Programmatic dependent launch (griddepcontrol): a kernel launched with the programmatic-serialization attribute may
+// start while its predecessor in the stream is still draining; pdl_wait() blocks until that predecessor has completed
+// and its writes are visible, pdl_trigger() lets the successor start launching once every CTA of this grid has got
+// here (or exited). Both are no-ops when the launch carries no such dependency.
+__device__ __forceinline__ void pdl_wait()
 {
-    if (mode == kStoreTmaHint) {
-        bulk_store_hint(gdst, ssrc, bytes, l2_policy_evict_first());
-    } else if (mode == kStoreTmaPaced) {  // four bulk operations, each waited for: at most a quarter tile in flight
-        const uint32_t quarter = ((bytes >> 2) + 15u) & ~15u;
-        const uint64_t pol = l2_policy_evict_first();
-        for (uint32_t off = 0; off < bytes; off += quarter) {
-            bulk_store_hint(static_cast<char *>(gdst) + off, static_cast<const char *>(ssrc) + off,
-                            min(quarter, bytes - off), pol);
-            bulk_commit();
-            bulk_wait_read_all();
-        }
-    } else if (mode == kStoreTmaSplit) {  // four bulk operations per tile instead of one
-        const uint32_t quarter = ((bytes >> 2) + 15u) & ~15u;
-        for (uint32_t off = 0; off < bytes; off += quarter)
-            bulk_store(static_cast<char *>(gdst) + off, static_cast<const char *>(ssrc) + off, min(quarter, bytes - off));
-    } else {
-        bulk_store(gdst, ssrc, bytes);
-    }
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_trigger()
+{
+    asm volatile("griddepcontrol.launch_dependents;");
 }
 __device__ __forceinline__ void store_zero16(float4 *p)
 {
@@ -135,6 +126,7 @@ classify_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOff
                 const __grid_constant__ ViewParams p, uint2 *__restrict__ keys, unsigned *__restrict__ tile_count,
                 unsigned *__restrict__ fv_winner)
 {
+    pdl_trigger();
     const int f = blockIdx.y;
     const int base = offs.off[f];
     const int n = offs.off[f + 1] - base;
@@ -214,6 +206,8 @@ tile_scan_kernel(unsigned *__restrict__ tile_count, unsigned *__restrict__ tile_
     unsigned *off = tile_off + (size_t)blockIdx.x * (tiles_per_frame + 1);
     const unsigned lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) carry = 0;
+    pdl_trigger();
+    pdl_wait();  // the histogram is classify's output
     __syncthreads();
     for (int t0 = 0; t0 < tiles_per_frame; t0 += kScanThreads * kScanItems) {
         const int first = t0 + (int)threadIdx.x * kScanItems;
@@ -258,21 +252,55 @@ tile_scan_kernel(unsigned *__restrict__ tile_count, unsigned *__restrict__ tile_
 }
 
 // ------------------------------------------------------------------------------------------------
+// Front view, second half: write the whole [R][C][F] image of sweep f from the per-pixel winners classify elected,
+// and clear the winners (self-cleaning workspace). Runs as extra CTAs of the bin pass (both only need classify's
+// output), or as a kernel of its own where there is no bin pass.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void front_finalize_body(const float4 *__restrict__ pts, const FrameOffsets &offs,
+                                                    const ViewParams &p, unsigned *__restrict__ fv_winner,
+                                                    float *__restrict__ front, int f, int block, int blocks)
+{
+    unsigned *winners = fv_winner + (size_t)f * p.front_pixels;
+    float *out = front + (size_t)f * p.front_frame_floats;
+    for (int pix = block * blockDim.x + threadIdx.x; pix < p.front_pixels; pix += blocks * blockDim.x) {
+        const unsigned w = winners[pix];
+        float v0 = 0.0f, v1 = 0.0f, v2 = 0.0f;
+        if (w) {
+            winners[pix] = 0u;
+            const float4 pt = pts[offs.off[f] + (int)(w - 1u)];
+            front_values(pt, p, v0, v1, v2);
+        }
+        float *o = out + (size_t)pix * p.fn;
+        o[0] = v0; o[1] = v1; o[2] = v2;
+        for (int c = 3; c < p.fn; c++) o[c] = 0.0f;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // TILE strategy, pass 3: move each kept point's record into its tile's bin.
 //   record = { cell-in-tile | slice << 16,  h bits,  point index,  intensity bits }   (16 bytes)
 // Order inside a bin is arbitrary; every order-dependent decision uses the point index carried along.
+// The last front_blocks CTAs of every sweep's row of the grid finish the front view instead (front_finalize_body).
 // ------------------------------------------------------------------------------------------------
 template <bool kPy>
 __global__ void __launch_bounds__(kPointThreads)
 bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets offs,
            const __grid_constant__ ViewParams p, const uint2 *__restrict__ keys,
-           const unsigned *__restrict__ tile_off, uint4 *__restrict__ binned)
+           const unsigned *__restrict__ tile_off, uint4 *__restrict__ binned, unsigned *__restrict__ fv_winner,
+           float *__restrict__ front, int front_blocks)
 {
+    pdl_trigger();
+    pdl_wait();  // keys / winners are classify's output, the bin offsets are the scan's
     const int f = blockIdx.y;
+    const int bin_blocks = (int)gridDim.x - front_blocks;
+    if ((int)blockIdx.x >= bin_blocks) {
+        front_finalize_body(pts, offs, p, fv_winner, front, f, (int)blockIdx.x - bin_blocks, front_blocks);
+        return;
+    }
     const int base = offs.off[f];
     const int n = offs.off[f + 1] - base;
     const unsigned *off = tile_off + (size_t)f * (p.tiles_per_frame + 1);
-    const int stride = gridDim.x * blockDim.x;
+    const int stride = bin_blocks * blockDim.x;
     for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += stride * kPointItems) {
         uint2 k[kPointItems];
         float4 pt[kPointItems];
@@ -357,7 +385,7 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
 constexpr int kRecordsInFlight = MV3D_RECORDS_IN_FLIGHT;  // records of a heavy tile each thread fetches before reducing them
 // kInFlight: records of a heavy tile each thread fetches before reducing them. Two pay for the plain C-routine kernel
 // (+1.6 %); the occupancy-reporting and Python-twin variants are faster with one (measured: -6.5 % / -0.5 % with two).
-template <bool kCompact, bool kOccupancy, bool kPy, int kStore = kStoreTmaHint,
+template <bool kCompact, bool kOccupancy, bool kPy, int kStore = kStoreBulk,
           int kInFlight = (kCompact || kOccupancy || kPy) ? 1 : kRecordsInFlight>
 __device__ __forceinline__ void
 tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, const FrameOffsets &offs,
@@ -383,6 +411,8 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
         for (int w = tid; w < T / 32 + 2; w += kTileThreads) occ_tile[w] = 0u;
     if (tid == 0) ndirty = 0;
     fence_proxy_async_smem();
+    pdl_trigger();
+    pdl_wait();  // everything above overlaps the tail of the bin pass; the bins themselves are its output
     __syncthreads();
 
     // Software pipeline over this CTA's tiles: the bin offsets of tile t+2 and the first record of tile t+1
@@ -425,20 +455,14 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
             // Empty tile: stream the all-zero image; nothing is modified, so no barrier.
             if (kStore == kStorePatch) {
                 // the output is zero already
-            } else if (bulk && kStore == kStoreLsu) {
-                float4 *d4 = reinterpret_cast<float4 *>(dst);
-                for (int w = tid; w < (int)(bytes >> 4); w += kTileThreads) d4[w] = make_float4(0.f, 0.f, 0.f, 0.f);
-            } else if (bulk && kStore == kStoreLsuStream) {
-                float4 *d4 = reinterpret_cast<float4 *>(dst);
-                for (int w = tid; w < (int)(bytes >> 4); w += kTileThreads) store_zero16(d4 + w);
             } else if (bulk) {
-                if (tid == 0) { tile_bulk_store(dst, img, bytes, kStore); bulk_commit(); }
+                if (tid == 0) { bulk_store_hint(dst, img, bytes, l2_policy_evict_first()); bulk_commit(); }
             } else {
                 for (int w = tid; w < ncell * planes; w += kTileThreads) dst[w] = 0.0f;
             }
         } else {
             // Earlier (empty-tile) bulk stores may still be reading the image: wait before touching it.
-            if (!kCompact && kStore < kStoreLsu) {
+            if (!kCompact && kStore == kStoreBulk) {
                 if (tid == 0) bulk_wait_read_all();
                 __syncthreads();
             }
@@ -536,16 +560,8 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                     const unsigned local = dirty[d];
                     for (int k = lane; k < planes; k += 32) dst[local * planes + k] = __uint_as_float(img[local * planes + k]);
                 }
-            } else if (bulk && kStore >= kStoreLsu) {
-                const uint4 *s4 = reinterpret_cast<const uint4 *>(img);
-                uint4 *d4 = reinterpret_cast<uint4 *>(dst);
-                if (kStore == kStoreLsu) {
-                    for (int w = tid; w < (int)(bytes >> 4); w += kTileThreads) d4[w] = s4[w];
-                } else {
-                    for (int w = tid; w < (int)(bytes >> 4); w += kTileThreads) __stcs(d4 + w, s4[w]);
-                }
             } else if (bulk) {
-                if (tid == 0) { tile_bulk_store(dst, img, bytes, kStore); bulk_commit(); bulk_wait_read_all(); }
+                if (tid == 0) { bulk_store_hint(dst, img, bytes, l2_policy_evict_first()); bulk_commit(); bulk_wait_read_all(); }
             } else {
                 for (int w = tid; w < ncell * planes; w += kTileThreads) dst[w] = __uint_as_float(img[w]);
             }
@@ -579,14 +595,14 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
     if (!kCompact && tid == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
 }
 
-template <bool kPy, int kStore = kStoreTmaHint>
+template <bool kPy>
 __global__ void __launch_bounds__(kTileThreads, MV3D_TILE_MIN_BLOCKS)
 tile_build_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
                   const __grid_constant__ FrameOffsets offs,
                   const __grid_constant__ ViewParams p, const float *__restrict__ lut, float *__restrict__ top,
                   int total_tiles)
 {
-    tile_body<false, false, kPy, kStore>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u);
+    tile_body<false, false, kPy>(binned, tile_off, offs, p, lut, top, total_tiles, nullptr, 0u);
 }
 
 // Same, and the occupancy bits / flag of every frame for the empty-anchor filter (see tile_body).
@@ -624,501 +640,13 @@ tile_compact_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict
 
 
 // ------------------------------------------------------------------------------------------------
-// TILE strategy, pass 4, pipelined form: ONE CTA per SM, G tile images in shared memory, G builder groups and one
-// store warp (MV3D_TILE_PIPE).
-//
-// Why: the bulk-store stream runs fastest when each SM keeps only ~9 KB of it in flight (6.8 TB/s, against 6.2-6.4
-// with whole 36 KB tiles of five independent CTAs in flight: profiles/tma_store_bench_r1.txt). Pacing the store inside
-// tile_build_kernel stalls the CTA that should be building the next tile, so here the two are decoupled: builder
-// group g owns image g and reduces tile (k*G + g)*grid + cta into it; the store warp walks the images in that same
-// order, writes each finished tile in chunks of pipe_chunk bytes with at most pipe_pending chunks unread, and hands
-// the image back. full[g] / empty[g] are mbarriers; a builder re-zeroes the cells its previous tile touched once
-// empty[g] says the store has read them. Same arithmetic, same order-preserving atomics as tile_body.
-// ------------------------------------------------------------------------------------------------
-constexpr int kPipeMaxGroups = 5;  // hardware barriers: 0 = whole CTA, then per group: its own and "empty"
-__device__ __forceinline__ void named_sync(int id, int threads)
-{
-    asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(threads) : "memory");
-}
-__device__ __forceinline__ void named_arrive(int id, int threads)
-{
-    asm volatile("bar.arrive %0, %1;" :: "r"(id), "r"(threads) : "memory");
-}
-__device__ __forceinline__ void mbar_init(uint64_t *bar, unsigned count)
-{
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(smem_addr(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
-{
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(smem_addr(bar)) : "memory");
-}
-__device__ __forceinline__ bool mbar_test(uint64_t *bar, unsigned parity)
-{
-    unsigned ok;
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-        "selp.u32 %0, 1, 0, p;\n\t}"
-        : "=r"(ok) : "r"(smem_addr(bar)), "r"(parity) : "memory");
-    return ok != 0u;
-}
-__device__ __forceinline__ void bulk_wait_read_pending(int n)
-{
-    switch (n) {
-    case 0: asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); break;
-    case 1: asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); break;
-    case 2: asm volatile("cp.async.bulk.wait_group.read 2;" ::: "memory"); break;
-    case 3: asm volatile("cp.async.bulk.wait_group.read 3;" ::: "memory"); break;
-    case 4: asm volatile("cp.async.bulk.wait_group.read 4;" ::: "memory"); break;
-    case 5: asm volatile("cp.async.bulk.wait_group.read 5;" ::: "memory"); break;
-    case 6: asm volatile("cp.async.bulk.wait_group.read 6;" ::: "memory"); break;
-    default: asm volatile("cp.async.bulk.wait_group.read 7;" ::: "memory"); break;
-    }
-}
-
-struct PipeLayout {
-    size_t img_bytes, key_off, dirty_off, occ_off, stride, header;
-};
-__host__ __device__ inline PipeLayout pipe_layout(int tile_cells, int planes)
-{
-    PipeLayout l;
-    l.img_bytes = ((size_t)tile_cells * planes * 4 + 15) & ~(size_t)15;
-    l.key_off = (l.img_bytes + 7) & ~(size_t)7;
-    l.dirty_off = l.key_off + (size_t)tile_cells * 8;
-    l.occ_off = l.dirty_off + (size_t)tile_cells * 4;
-    l.stride = (l.occ_off + ((size_t)tile_cells / 32 + 2) * 4 + 127) & ~(size_t)127;
-    l.header = 256;  // density table (32 floats), cnt[5][2], full[5] mbarriers
-    return l;
-}
-
-template <bool kOccupancy, bool kPy>
-__global__ void __launch_bounds__(1024, 1)
-tile_pipe_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
-                 const __grid_constant__ FrameOffsets offs, const __grid_constant__ ViewParams p,
-                 const float *__restrict__ lut, float *__restrict__ top, int total_tiles, OccupancySink sink)
-{
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    const int T = p.tile_cells, planes = p.planes, zn = p.zn;
-    const int G = p.pipe_groups, gthreads = p.pipe_group_threads;
-    const PipeLayout L = pipe_layout(T, planes);
-    float *slut = reinterpret_cast<float *>(smem_raw);
-    unsigned *cnt = reinterpret_cast<unsigned *>(smem_raw + 128);  // [G][2] touched cells of the current / previous tile
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + 192);  // full[g]: builder group g has finished its tile
-    unsigned char *bufs = smem_raw + L.header;
-    const int tid = threadIdx.x;
-    const int nbuild = G * gthreads;
-    const int hand = gthreads + 32;  // a builder group and the store warp meet on the "full" / "empty" barriers
-
-    {   // all images and keys start all-zero
-        uint4 *z = reinterpret_cast<uint4 *>(bufs);
-        const int n16 = (int)((L.stride * (size_t)G) >> 4);
-        for (int w = tid; w < n16; w += blockDim.x) z[w] = make_uint4(0u, 0u, 0u, 0u);
-        if (tid < 2 * kPipeMaxGroups) cnt[tid] = 0u;
-        if (tid < kDensityLutSize) slut[tid] = __ldg(lut + tid);
-        if (tid < G) mbar_init(full + tid, (unsigned)gthreads);
-    }
-    fence_proxy_async_smem();
-    __syncthreads();
-
-    const int grid = gridDim.x, b = blockIdx.x;
-    const int tpf = p.tiles_per_frame;
-    const long long cells_total = (long long)p.xn * p.yn;
-    const int tstep = G * grid;  // total_tiles + 2 * tstep stays far below 2^31 (checked by the launcher)
-
-    if (tid >= nbuild) {
-        // ---------------- store warp ----------------
-        // Stores whichever image is finished (build times are skewed: tiles near the sensor hold hundreds of records),
-        // polling the groups' mbarriers round-robin. The bulk stores of consecutive tiles form one stream of chunks:
-        // before a chunk is issued at most pipe_pending older chunks may still be unread, and an image goes back to
-        // its builders (the "empty" barrier) as soon as the stream has moved past its last chunk -- so the next
-        // tile is found and addressed while the previous one is still being read.
-        const int lane = tid - nbuild;
-        const uint64_t pol = l2_policy_evict_first();
-        const uint32_t chunk = (uint32_t)p.pipe_chunk;
-        const int pending = p.pipe_pending;
-        int kq[kPipeMaxGroups];  // next round of each group
-#pragma unroll
-        for (int g = 0; g < kPipeMaxGroups; g++) kq[g] = 0;
-        int left = 0;  // tiles of this CTA
-        for (int g = 0; g < G; g++) {
-            const int first = g * grid + b;
-            if (first < total_tiles) left += (total_tiles - 1 - first) / tstep + 1;
-        }
-        int prev_g = -1;  // image whose store has been issued but which has not been handed back yet
-        auto release = [&](int g) {  // all lanes
-            __syncwarp();
-            named_arrive(1 + kPipeMaxGroups + g, hand);
-        };
-        while (left > 0) {
-            int idle = 1;
-#pragma unroll
-            for (int g = 0; g < kPipeMaxGroups; g++) {
-                if (g >= G) continue;
-                const int k = kq[g];
-                const int t = (k * G + g) * grid + b;
-                if (t >= total_tiles) continue;
-                int ready = (lane == 0) ? (int)mbar_test(full + g, (unsigned)(k & 1)) : 0;
-                ready = __shfl_sync(0xffffffffu, ready, 0);
-                if (!ready) continue;
-                idle = 0;
-                kq[g] = k + 1;
-                left--;
-                const int f = t / tpf, tl = t - f * tpf;
-                const long long cell0 = (long long)tl * T;
-                const int ncell = (int)min((long long)T, cells_total - cell0);
-                const uint32_t bytes = (uint32_t)ncell * (uint32_t)planes * 4u;
-                float *dst = top + (size_t)f * p.top_frame_floats + (size_t)cell0 * planes;
-                const unsigned char *img = bufs + (size_t)g * L.stride;
-                const bool bulk = ((reinterpret_cast<uintptr_t>(dst) | (uintptr_t)bytes) & 15u) == 0;
-                const bool again = t + tstep < total_tiles;  // the builders will want this image back
-                if (bulk) {
-                    int j = 0;
-                    for (uint32_t off = 0; off < bytes; off += chunk, j++) {
-                        if (lane == 0) bulk_wait_read_pending(pending);
-                        if (prev_g >= 0 && j == pending) { release(prev_g); prev_g = -1; }
-                        if (lane == 0) {
-                            bulk_store_hint(reinterpret_cast<char *>(dst) + off, img + off, min(chunk, bytes - off), pol);
-                            bulk_commit();
-                        }
-                    }
-                    if (prev_g >= 0) {  // fewer chunks than the stream may leave unread: wait for all but this tile's
-                        if (lane == 0) bulk_wait_read_pending(j);
-                        release(prev_g);
-                    }
-                    prev_g = again ? g : -1;
-                } else {
-                    if (lane == 0) bulk_wait_read_all();
-                    if (prev_g >= 0) { release(prev_g); prev_g = -1; }
-                    const unsigned *s = reinterpret_cast<const unsigned *>(img);
-                    for (int w = lane; w < ncell * planes; w += 32) dst[w] = __uint_as_float(s[w]);
-                    if (again) release(g);
-                }
-            }
-            if (idle && prev_g >= 0) {  // nothing to issue: do not sit on the last image
-                if (lane == 0) bulk_wait_read_all();
-                release(prev_g);
-                prev_g = -1;
-            }
-        }
-        if (lane == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
-        return;
-    }
-
-    // ---------------- builder group g ----------------
-    const int g = tid / gthreads, gt = tid - g * gthreads;
-    const int lane = gt & 31, gwarp = gt >> 5, gwarps = gthreads >> 5;
-    const int bar_own = 1 + g, bar_empty = 1 + kPipeMaxGroups + g;
-    unsigned char *buf = bufs + (size_t)g * L.stride;
-    unsigned *img = reinterpret_cast<unsigned *>(buf);
-    unsigned long long *key = reinterpret_cast<unsigned long long *>(buf + L.key_off);
-    unsigned *dirty = reinterpret_cast<unsigned *>(buf + L.dirty_off);
-    unsigned *occ_tile = reinterpret_cast<unsigned *>(buf + L.occ_off);
-    unsigned *mycnt = cnt + 2 * g;
-
-    auto bin_range = [&](int t, const uint4 *&rec, int &n) {
-        n = 0;
-        rec = binned;
-        if (t < total_tiles) {
-            const int f = t / tpf, tl = t - f * tpf;
-            const unsigned *off = tile_off + (size_t)f * (tpf + 1) + tl;
-            const unsigned beg = __ldg(off);
-            n = (int)(__ldg(off + 1) - beg);
-            rec = binned + (size_t)offs.off[f] + beg;
-        }
-    };
-    const int t_first = g * grid + b;
-    const uint4 *rec0, *rec1, *rec2;
-    int n0, n1, n2;
-    bin_range(t_first, rec0, n0);
-    bin_range(t_first + tstep, rec1, n1);
-    uint4 q0 = make_uint4(0, 0, 0, 0), q1 = q0;
-    if (gt < n0) q0 = __ldg(rec0 + gt);
-
-    int k = 0;
-    for (int t = t_first; t < total_tiles; t += tstep, k++) {
-        bin_range(t + 2 * tstep, rec2, n2);
-        if (gt < n1) q1 = __ldg(rec1 + gt);
-        const int f = t / tpf, tl = t - f * tpf;
-        const long long cell0 = (long long)tl * T;
-        unsigned *cur = mycnt + (k & 1), *prev = mycnt + ((k & 1) ^ 1);
-
-        if (k > 0) named_sync(bar_empty, hand);  // the store warp has read the previous tile of this image
-        const int nd_prev = (int)*prev;
-        if (n0 > 0 || nd_prev > 0) {
-            // re-zero what the previous tile touched
-            for (int d = gwarp; d < nd_prev; d += gwarps) {
-                const unsigned local = dirty[d];
-                for (int kk = lane; kk < planes; kk += 32) img[local * planes + kk] = 0u;
-                if (lane == 0) key[local] = 0ull;
-            }
-            if (gt == 0) *cur = 0u;
-            named_sync(bar_own, gthreads);
-
-            // accumulate
-            for (int r = gt; r < n0; r += gthreads) {
-                const uint4 q = (r == gt) ? q0 : __ldg(rec0 + r);
-                const unsigned local = q.x & 0xFFFFu, Z = q.x >> 16;
-                unsigned *cellw = img + local * planes;
-                if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(cur, 1u)] = local;
-                if ((int)q.y > 0) {
-                    if (kPy) {
-                        const unsigned zs = Z & (kLowerFlag - 1u);
-                        if (zs != kNoSlice) atomicMax(cellw + zs, q.y);
-                        if (Z & kLowerFlag) {
-                            const unsigned below = (zs == kNoSlice) ? (unsigned)zn - 1u : zs - 1u;
-                            if (below < (unsigned)zn) atomicMax(cellw + below, q.y);
-                        }
-                    } else {
-                        atomicMax(cellw + Z, q.y);
-                    }
-                    atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
-                }
-            }
-            named_sync(bar_own, gthreads);
-
-            // finalise the touched cells in place
-            const int nd = (int)*cur;
-            for (int r = gt; r < n0; r += gthreads) {
-                const uint4 q = (r == gt) ? q0 : __ldg(rec0 + r);
-                const unsigned local = q.x & 0xFFFFu;
-                if ((int)q.y > 0 &&
-                    key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z))) {
-                    img[local * planes + zn] = q.w;
-                    if (kOccupancy && ((q.w >> 31) != 0u || (q.w & 0x7fffffffu) > 0x7f800000u))
-                        atomicOr(sink.flags + f, 1u);
-                }
-            }
-            for (int d = gwarp; d < nd; d += gwarps) {
-                unsigned *cellw = img + dirty[d] * planes;
-                if (kOccupancy && lane == 0) {
-                    const unsigned gc = (unsigned)cell0 + dirty[d];
-                    atomicOr(occ_tile + ((gc >> 5) - ((unsigned)cell0 >> 5)), 1u << (gc & 31u));
-                }
-                for (int kk = lane; kk < planes; kk += 32) {
-                    if (kk < zn) {
-                        const unsigned raw = cellw[kk];
-                        if (raw) cellw[kk] = __float_as_uint(kPy ? __fsub_rn(__uint_as_float(raw), (float)kk)
-                                                                  : slice_value(__uint_as_float(raw), p.z_div, kk));
-                    } else if (kk == zn + 1) {
-                        const unsigned c = cellw[kk];
-                        cellw[kk] = __float_as_uint(slut[c < 31u ? c : 31u]);
-                    }
-                }
-            }
-            if (kOccupancy) {
-                named_sync(bar_own, gthreads);
-                const int ncell = (int)min((long long)T, cells_total - cell0);
-                const unsigned w_first = (unsigned)cell0 >> 5, w_last = ((unsigned)cell0 + (unsigned)ncell - 1u) >> 5;
-                unsigned *out = sink.words + (size_t)f * sink.words_per_frame + w_first;
-                for (unsigned w = gt; w <= w_last - w_first; w += gthreads) {
-                    const unsigned bits = occ_tile[w];
-                    if (bits) {
-                        if ((T & 31) != 0 && (w == 0 || w == w_last - w_first)) atomicOr(out + w, bits);
-                        else out[w] = bits;
-                        occ_tile[w] = 0u;
-                    }
-                }
-            }
-        } else if (gt == 0) {
-            *cur = 0u;
-        }
-        fence_proxy_async_smem();
-        mbar_arrive(full + g);  // gthreads arrivals complete the phase: the image is ready for the store warp
-        rec0 = rec1; n0 = n1; q0 = q1;
-        rec1 = rec2; n1 = n2;
-    }
-}
-
-size_t tile_pipe_smem_bytes(const ViewParams &p)
-{
-    const PipeLayout l = pipe_layout(p.tile_cells, p.planes);
-    return l.header + l.stride * (size_t)p.pipe_groups;
-}
-
-// ------------------------------------------------------------------------------------------------
-// PATCH strategy, zero-fill: bulk async (TMA) stores from one all-zero shared-memory buffer. One elected thread
-// per CTA issues the stores, so the kernel holds one warp and 16 KB of shared memory per CTA and leaves the SMs
-// to the point passes running beside it on another stream.
-// ------------------------------------------------------------------------------------------------
-constexpr int kFillThreads = 32;
-constexpr uint32_t kFillChunk = 16384;  // bytes per bulk store
-__global__ void __launch_bounds__(kFillThreads) fill_tma_kernel(float *__restrict__ dst, size_t count, int max_pending)
-{
-    __shared__ __align__(128) float4 zeros[kFillChunk / 16];
-    for (int w = threadIdx.x; w < (int)(kFillChunk / 16); w += kFillThreads) zeros[w] = make_float4(0.f, 0.f, 0.f, 0.f);
-    fence_proxy_async_smem();
-    __syncthreads();
-    // head (to 16-byte alignment) and tail by plain stores, body by bulk stores
-    const uintptr_t addr = reinterpret_cast<uintptr_t>(dst);
-    size_t head = ((16 - (addr & 15)) & 15) / 4;
-    if (head > count) head = count;
-    const size_t body_bytes = ((count - head) * 4) & ~(size_t)15;
-    char *body = reinterpret_cast<char *>(dst + head);
-    if (blockIdx.x == 0) {
-        const size_t tail0 = head + body_bytes / 4;
-        if (threadIdx.x < head) dst[threadIdx.x] = 0.0f;
-        if (threadIdx.x < count - tail0) dst[tail0 + threadIdx.x] = 0.0f;
-    }
-    if (threadIdx.x == 0) {
-        const uint64_t pol = l2_policy_evict_first();
-        const size_t nchunk = (body_bytes + kFillChunk - 1) / kFillChunk;
-        for (size_t c = blockIdx.x; c < nchunk; c += gridDim.x) {
-            const size_t off = c * kFillChunk;
-            const uint32_t bytes = (uint32_t)((body_bytes - off < kFillChunk) ? body_bytes - off : kFillChunk);
-            bulk_store_hint(body + off, zeros, bytes, pol);
-            bulk_commit();
-            // Bound the bytes this SM has in flight: an unbounded queue of bulk stores delays every other
-            // memory request of the kernels running beside the fill.
-            if (max_pending <= 2) bulk_wait_pending<2>();
-            else if (max_pending <= 4) bulk_wait_pending<4>();
-            else if (max_pending <= 8) bulk_wait_pending<8>();
-            else if (max_pending <= 16) bulk_wait_pending<16>();
-        }
-        bulk_wait_all();
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
-// PATCH strategy, reduction: one WARP per tile, persistent warps, tiles taken 32 at a time (lane l reads the bin
-// range of tile 32g+l, empty tiles cost nothing more). Per non-empty tile, warp-synchronous:
-//   accumulate : as in tile_build_kernel, into the warp's private image (shared-memory atomics)
-//   finalise   : touched cells only
-//   write      : for each touched cell, the whole 32-byte sectors of the output that overlap it (clipped to the
-//                tile), taken from the image -- full sectors, so L2 never fetches a partially written one;
-//                everything else in the tile is already zero in memory (fill_tma_kernel)
-//   clean      : re-zero the touched cells
-// ------------------------------------------------------------------------------------------------
-constexpr int kPatchWarps = 8;
-__host__ __device__ inline size_t patch_warp_bytes(int tile_cells, int planes)
-{
-    const size_t img = ((size_t)tile_cells * planes * 4 + 15) & ~(size_t)15;
-    return img + (size_t)tile_cells * 8 + ((((size_t)tile_cells + 1) * 4 + 15) & ~(size_t)15);
-}
-
-__global__ void __launch_bounds__(kPatchWarps * 32)
-warp_patch_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, FrameOffsets offs,
-                  ViewParams p, const float *__restrict__ lut, float *__restrict__ top, int batch)
-{
-    extern __shared__ __align__(128) unsigned char smem_raw[];
-    constexpr unsigned kFull = 0xFFFFFFFFu;
-    const int T = p.tile_cells, planes = p.planes, zn = p.zn;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned char *mine = smem_raw + (size_t)warp * patch_warp_bytes(T, planes);
-    unsigned *img = reinterpret_cast<unsigned *>(mine);
-    unsigned long long *key = reinterpret_cast<unsigned long long *>(mine + (((size_t)T * planes * 4 + 15) & ~(size_t)15));
-    unsigned *dirty = reinterpret_cast<unsigned *>(key + T);  // dirty[0..T) cells, dirty[T] their number
-    for (int w = lane; w < T * planes; w += 32) img[w] = 0u;
-    for (int w = lane; w < T; w += 32) key[w] = 0ull;
-    if (lane == 0) dirty[T] = 0u;
-    __syncwarp();
-
-    const int tpf = p.tiles_per_frame;
-    const int groups_per_frame = (tpf + 31) >> 5;
-    const int total_groups = batch * groups_per_frame;
-    const long long cells_total = (long long)p.xn * p.yn;
-    const int nwarps = gridDim.x * kPatchWarps;
-    for (int g = blockIdx.x * kPatchWarps + warp; g < total_groups; g += nwarps) {
-        const int f = g / groups_per_frame;
-        const int t0 = (g - f * groups_per_frame) << 5;
-        const unsigned *off = tile_off + (size_t)f * (tpf + 1);
-        unsigned beg = 0, end = 0;
-        if (t0 + lane < tpf) { beg = __ldg(off + t0 + lane); end = __ldg(off + t0 + lane + 1); }
-        unsigned todo = __ballot_sync(kFull, end > beg);
-        const uint4 *frame_rec = binned + offs.off[f];
-        float *frame_top = top + (size_t)f * p.top_frame_floats;
-        while (todo) {
-            const int src = __ffs(todo) - 1;
-            todo &= todo - 1;
-            const unsigned b = __shfl_sync(kFull, beg, src);
-            const int n = (int)(__shfl_sync(kFull, end, src) - b);
-            const uint4 *rec = frame_rec + b;
-            const long long cell0 = (long long)(t0 + src) * T;
-            const int nfl = (int)min((long long)T, cells_total - cell0) * planes;
-            float *dst = frame_top + (size_t)cell0 * planes;
-
-            // accumulate
-            uint4 q0 = make_uint4(0, 0, 0, 0);
-            for (int r = lane; r < n; r += 32) {
-                const uint4 q = __ldg(rec + r);
-                if (r == lane) q0 = q;
-                const unsigned local = q.x & 0xFFFFu, Z = q.x >> 16;
-                unsigned *cellw = img + local * planes;
-                if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(dirty + T, 1u)] = local;
-                if ((int)q.y > 0) {  // h > 0: the reference's maps start at 0 and update on strict '>'
-                    atomicMax(cellw + Z, q.y);
-                    atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
-                }
-            }
-            __syncwarp();
-            const int nd = (int)dirty[T];
-            // intensity of each cell's winner
-            for (int r = lane; r < n; r += 32) {
-                const uint4 q = (r == lane) ? q0 : __ldg(rec + r);
-                const unsigned local = q.x & 0xFFFFu;
-                if ((int)q.y > 0 &&
-                    key[local] == (((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z))) {
-                    img[local * planes + zn] = q.w;
-                }
-            }
-            // heights and density of the touched cells (lanes over planes; the intensity slot is not touched here)
-            for (int d = 0; d < nd; d++) {
-                unsigned *cellw = img + dirty[d] * planes;
-                for (int k = lane; k < planes; k += 32) {
-                    if (k < zn) {
-                        const unsigned raw = cellw[k];
-                        if (raw) cellw[k] = __float_as_uint(slice_value(__uint_as_float(raw), p.z_div, k));
-                    } else if (k == zn + 1) {
-                        const unsigned c = cellw[k];
-                        cellw[k] = __float_as_uint(__ldg(lut + (c < 31u ? c : 31u)));
-                    }
-                }
-            }
-            __syncwarp();
-            // write the sectors that hold touched cells
-            const long long abs0 = (long long)(reinterpret_cast<uintptr_t>(dst) >> 2);  // tile start, in floats
-            for (int d = 0; d < nd; d++) {
-                const long long a = abs0 + (long long)dirty[d] * planes;
-                int lo = (int)((a & ~7LL) - abs0), hi = (int)(((a + planes - 1) | 7LL) + 1 - abs0);
-                lo = lo < 0 ? 0 : lo;
-                hi = hi > nfl ? nfl : hi;
-                for (int w = lo + lane; w < hi; w += 32) dst[w] = __uint_as_float(img[w]);
-            }
-            __syncwarp();
-            // clean
-            for (int d = 0; d < nd; d++) {
-                const unsigned local = dirty[d];
-                for (int k = lane; k < planes; k += 32) img[local * planes + k] = 0u;
-                if (lane == 0) key[local] = 0ull;
-            }
-            __syncwarp();
-            if (lane == 0) dirty[T] = 0u;
-            __syncwarp();
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
 // Front view: write the whole [R][C][F] image from the per-pixel winners, and clear the winners.
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kPointThreads)
-front_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p,
-                      unsigned *__restrict__ fv_winner, float *__restrict__ front)
+front_finalize_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets offs,
+                      const __grid_constant__ ViewParams p, unsigned *__restrict__ fv_winner, float *__restrict__ front)
 {
-    const int f = blockIdx.y;
-    unsigned *winners = fv_winner + (size_t)f * p.front_pixels;
-    float *out = front + (size_t)f * p.front_frame_floats;
-    for (int pix = blockIdx.x * blockDim.x + threadIdx.x; pix < p.front_pixels; pix += gridDim.x * blockDim.x) {
-        const unsigned w = winners[pix];
-        float v0 = 0.0f, v1 = 0.0f, v2 = 0.0f;
-        if (w) {
-            winners[pix] = 0u;
-            const float4 pt = pts[offs.off[f] + (int)(w - 1u)];
-            front_values(pt, p, v0, v1, v2);
-        }
-        float *o = out + (size_t)pix * p.fn;
-        o[0] = v0; o[1] = v1; o[2] = v2;
-        for (int c = 3; c < p.fn; c++) o[c] = 0.0f;
-    }
+    front_finalize_body(pts, offs, p, fv_winner, front, blockIdx.y, blockIdx.x, gridDim.x);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1330,10 +858,55 @@ point_keys_kernel(const float4 *__restrict__ pts, int n, ViewParams p, int *__re
 // ------------------------------------------------------------------------------------------------
 // launchers
 // ------------------------------------------------------------------------------------------------
+// Kernel launch with the programmatic-serialization attribute: the kernel may begin (up to its pdl_wait()) while the
+// previous kernel in the stream drains. MV3D_PDL=0 falls back to plain stream order (A/B measurements).
+static bool pdl_enabled()
+{
+    static const bool on = [] { const char *e = getenv("MV3D_PDL"); return !e || atoi(e) != 0; }();
+    return on;
+}
+template <typename... Params, typename... Args>
+static void launch_after(void (*kernel)(Params...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args &&...args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<Params>(args)...);
+}
+
 static inline int point_blocks(int max_points, int items = 1)
 {
     int b = (max_points + kPointThreads * items - 1) / (kPointThreads * items);
     return b < 1 ? 1 : (b > 4096 ? 4096 : b);
+}
+
+// CTAs per sweep for the grid-stride point passes of a batch: enough to cover the longest sweep, but no more than
+// MV3D_POINT_WAVES (default 2) waves of resident CTAs over the whole batch. A CTA that lives for one round of 512
+// points spends a quarter of its instructions on its prologue (ncu, profiles/r2b_*): with 64 sweeps per launch each
+// CTA now loops ~6 times over its sweep instead.
+static int sm_count_cached()
+{
+    static const int sms = [] {
+        int dev = 0, n = 0;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n < 1) n = 148;
+        return n;
+    }();
+    return sms;
+}
+static inline int point_blocks_batched(int max_points, int items, int batch, int ctas_per_sm)
+{
+    static const int waves = [] { const char *e = getenv("MV3D_POINT_WAVES"); const int w = e ? atoi(e) : 2; return w < 1 ? 1 << 20 : w; }();
+    const int cover = point_blocks(max_points, items);
+    long long cap = ((long long)sm_count_cached() * ctas_per_sm * waves + batch - 1) / (batch > 0 ? batch : 1);
+    if (cap < 1) cap = 1;
+    return cover < cap ? cover : (int)cap;
 }
 
 size_t tile_smem_bytes(const ViewParams &p)
@@ -1342,19 +915,45 @@ size_t tile_smem_bytes(const ViewParams &p)
     return img + (size_t)p.tile_cells * 8 + (size_t)p.tile_cells * 4 + ((size_t)p.tile_cells / 32 + 2) * 4;
 }
 
-cudaError_t tile_build_configure(const ViewParams &p, int *blocks_per_sm)
+// The opt-in is a property of the (device, kernel) pair, shared by every context of the process: only ever raise it,
+// or a context configured for a small tile would lower it under another one's cached configuration.
+template <bool kPy>
+static cudaError_t tile_kernels_opt_in(int smem)
 {
-    const size_t smem = tile_smem_bytes(p);
-    auto kernel = p.py ? tile_build_kernel<true> : tile_build_kernel<false>;
-    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    const auto attr = cudaFuncAttributeMaxDynamicSharedMemorySize;
+    cudaError_t e;
+    if ((e = cudaFuncSetAttribute(tile_build_kernel<kPy>, attr, smem)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(tile_build_occupancy_kernel<kPy>, attr, smem)) != cudaSuccess) return e;
+    if ((e = cudaFuncSetAttribute(tile_patch_kernel<kPy>, attr, smem)) != cudaSuccess) return e;
+    return cudaFuncSetAttribute(tile_compact_kernel<kPy>, attr, smem);
+}
+
+cudaError_t tile_kernels_configure(const ViewParams &p, int *blocks_per_sm)
+{
+    constexpr int kMaxDevices = 64;
+    static std::mutex mu;
+    static int opted[kMaxDevices][2] = {};
+    const int smem = (int)tile_smem_bytes(p);
+    int device = 0;
+    cudaError_t e = cudaGetDevice(&device);
     if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, kernel, kTileThreads, smem);
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        int &have = opted[device < kMaxDevices ? device : kMaxDevices - 1][p.py ? 1 : 0];
+        if (smem > have || device >= kMaxDevices) {
+            e = p.py ? tile_kernels_opt_in<true>(smem) : tile_kernels_opt_in<false>(smem);
+            if (e != cudaSuccess) return e;
+            have = smem;
+        }
+    }
+    return p.py ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, tile_build_kernel<true>, kTileThreads, smem)
+                : cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, tile_build_kernel<false>, kTileThreads, smem);
 }
 
 int launch_classify(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
                     uint2 *keys, unsigned *tile_count, unsigned *fv_winner, cudaStream_t s)
 {
-    dim3 grid(point_blocks(max_points, kPointItems), batch);
+    dim3 grid(point_blocks_batched(max_points, kPointItems, batch, MV3D_CLASSIFY_MIN_BLOCKS), batch);
     auto kernel = p.py ? classify_kernel<true> : classify_kernel<false>;
     kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_count, fv_winner);
     return 1;
@@ -1363,18 +962,20 @@ int launch_classify(const float4 *pts, const FrameOffsets &offs, const ViewParam
 int launch_tile_scan(unsigned *tile_count, unsigned *tile_off, int tiles_per_frame, int batch, cudaStream_t s)
 {
     if (tiles_per_frame > 16 * kScanThreads)
-        tile_scan_kernel<8><<<batch, kScanThreads, 0, s>>>(tile_count, tile_off, tiles_per_frame);
+        launch_after(tile_scan_kernel<8>, dim3(batch), dim3(kScanThreads), 0, s, tile_count, tile_off, tiles_per_frame);
     else
-        tile_scan_kernel<2><<<batch, kScanThreads, 0, s>>>(tile_count, tile_off, tiles_per_frame);
+        launch_after(tile_scan_kernel<2>, dim3(batch), dim3(kScanThreads), 0, s, tile_count, tile_off, tiles_per_frame);
     return 1;
 }
 
 int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
-               const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s)
+               const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s, unsigned *fv_winner,
+               float *front)
 {
-    dim3 grid(point_blocks(max_points, kPointItems), batch);
+    const int front_blocks = (front && fv_winner && p.front_pixels > 0) ? point_blocks(p.front_pixels) : 0;
+    dim3 grid(point_blocks_batched(max_points, kPointItems, batch, 8) + front_blocks, batch);
     auto kernel = p.py ? bin_kernel<true> : bin_kernel<false>;
-    kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, keys, tile_off, binned);
+    launch_after(kernel, grid, dim3(kPointThreads), 0, s, pts, offs, p, keys, tile_off, binned, fv_winner, front, front_blocks);
     return 1;
 }
 
@@ -1382,44 +983,15 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s, const OccupancySink *sink)
 {
     const int total = batch * p.tiles_per_frame;
-    if (p.pipe_groups > 0 && (long long)total + 2LL * p.pipe_groups * p.pipe_grid < 2147483647LL) {  // one CTA per SM
-        const int grid = p.pipe_grid < total ? p.pipe_grid : total;
-        const bool occ = sink && sink->words;
-        auto kernel = occ ? (p.py ? tile_pipe_kernel<true, true> : tile_pipe_kernel<true, false>)
-                          : (p.py ? tile_pipe_kernel<false, true> : tile_pipe_kernel<false, false>);
-        const size_t smem = tile_pipe_smem_bytes(p);
-        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        const int threads = p.pipe_groups * p.pipe_group_threads + 32;
-        kernel<<<grid, threads, smem, s>>>(binned, tile_off, offs, p, lut, top, total, occ ? *sink : OccupancySink());
-        return 1;
-    }
     const int grid = grid_blocks < total ? grid_blocks : total;
     if (sink && sink->words) {
         auto kernel = p.py ? tile_build_occupancy_kernel<true> : tile_build_occupancy_kernel<false>;
-        cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(p));
-        kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total, *sink);
+        launch_after(kernel, dim3(grid), dim3(kTileThreads), tile_smem_bytes(p), s, binned, tile_off, offs, p, lut, top, total, *sink);
     } else {
         auto kernel = p.py ? tile_build_kernel<true> : tile_build_kernel<false>;
-        if (!p.py && p.store_mode != kStoreTmaHint) {  // experiment knob (MV3D_TILE_STORE), C-routine semantics only
-            kernel = p.store_mode == kStoreTma ? tile_build_kernel<false, kStoreTma>
-                   : p.store_mode == kStoreTmaSplit ? tile_build_kernel<false, kStoreTmaSplit>
-                   : p.store_mode == kStoreTmaPaced ? tile_build_kernel<false, kStoreTmaPaced>
-                   : p.store_mode == kStoreLsu ? tile_build_kernel<false, kStoreLsu>
-                                               : tile_build_kernel<false, kStoreLsuStream>;
-            cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(p));
-        }
-        kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, total);
+        launch_after(kernel, dim3(grid), dim3(kTileThreads), tile_smem_bytes(p), s, binned, tile_off, offs, p, lut, top, total);
     }
     return 1;
-}
-
-cudaError_t tile_patch_configure(const ViewParams &p, int *blocks_per_sm)
-{
-    const size_t smem = tile_smem_bytes(p);
-    auto kernel = p.py ? tile_patch_kernel<true> : tile_patch_kernel<false>;
-    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, kernel, kTileThreads, smem);
 }
 
 int launch_tile_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
@@ -1439,39 +1011,7 @@ int launch_tile_compact(const uint4 *binned, const unsigned *tile_off, const Fra
     const int total = batch * p.tiles_per_frame;
     const int grid = grid_blocks < total ? grid_blocks : total;
     auto kernel = p.py ? tile_compact_kernel<true> : tile_compact_kernel<false>;
-    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tile_smem_bytes(p));
-    kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, total, compact, compact_cap);
-    return 1;
-}
-
-size_t patch_smem_bytes(const ViewParams &p) { return kPatchWarps * patch_warp_bytes(p.tile_cells, p.planes); }
-
-cudaError_t warp_patch_configure(const ViewParams &p, int *blocks_per_sm)
-{
-    const size_t smem = patch_smem_bytes(p);
-    cudaError_t e = cudaFuncSetAttribute(warp_patch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    return cudaOccupancyMaxActiveBlocksPerMultiprocessor(blocks_per_sm, warp_patch_kernel, kPatchWarps * 32, smem);
-}
-
-size_t fill_tma_smem_bytes() { return kFillChunk; }
-
-int launch_fill_tma(float *dst, size_t count, int blocks, int max_pending, cudaStream_t s)
-{
-    if (count == 0) return 0;
-    const size_t want = (count * 4 + kFillChunk - 1) / kFillChunk;
-    if ((size_t)blocks > want) blocks = (int)want;
-    fill_tma_kernel<<<blocks < 1 ? 1 : blocks, kFillThreads, 0, s>>>(dst, count, max_pending);
-    return 1;
-}
-
-int launch_warp_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
-                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s)
-{
-    const int groups = batch * ((p.tiles_per_frame + 31) / 32);
-    const int want = (groups + kPatchWarps - 1) / kPatchWarps;
-    const int grid = grid_blocks < want ? grid_blocks : want;
-    warp_patch_kernel<<<grid < 1 ? 1 : grid, kPatchWarps * 32, patch_smem_bytes(p), s>>>(binned, tile_off, offs, p, lut, top, batch);
+    launch_after(kernel, dim3(grid), dim3(kTileThreads), tile_smem_bytes(p), s, binned, tile_off, offs, p, lut, total, compact, compact_cap);
     return 1;
 }
 

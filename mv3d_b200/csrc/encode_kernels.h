@@ -20,21 +20,23 @@ struct OccupancySink {
 
 // Each launcher enqueues on `s` and returns the number of kernels it launched.
 size_t tile_smem_bytes(const ViewParams &p);
-cudaError_t tile_build_configure(const ViewParams &p, int *blocks_per_sm);
-size_t tile_pipe_smem_bytes(const ViewParams &p);
+// Opts every tile-kernel variant of this semantics into tile_smem_bytes(p) of dynamic shared memory and reports how
+// many CTAs of the dense kernel an SM holds. Callers cache the answer (mv3d_abi.cu: tile_blocks_per_sm).
+cudaError_t tile_kernels_configure(const ViewParams &p, int *blocks_per_sm);
 
 int launch_classify(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
                     uint2 *keys, unsigned *tile_count, unsigned *fv_winner, cudaStream_t s);
 int launch_tile_scan(unsigned *tile_count, unsigned *tile_off, int tiles_per_frame, int batch, cudaStream_t s);
+// fv_winner / front non-NULL: the same launch also finishes the C routine's front view (front_finalize_body)
 int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
-               const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s);
+               const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s,
+               unsigned *fv_winner = nullptr, float *front = nullptr);
 int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s,
                       const OccupancySink *sink = nullptr);
 int launch_tile_compact(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                         const float *lut, int batch, int grid_blocks, unsigned *compact, unsigned compact_cap,
                         cudaStream_t s);
-cudaError_t tile_patch_configure(const ViewParams &p, int *blocks_per_sm);
 int launch_tile_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
 // SORT strategy (sort_strategy.cu)
@@ -47,12 +49,6 @@ int launch_sort_pairs(void *temp, size_t temp_bytes, const unsigned *keys_in, un
 int launch_sort_reduce(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const float *lut,
                        const unsigned *skeys, const unsigned *svals, size_t n, unsigned invalid_key, float *top,
                        cudaStream_t s);
-size_t patch_smem_bytes(const ViewParams &p);
-cudaError_t warp_patch_configure(const ViewParams &p, int *blocks_per_sm);
-size_t fill_tma_smem_bytes();
-int launch_fill_tma(float *dst, size_t count, int blocks, int max_pending, cudaStream_t s);
-int launch_warp_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
-                      const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
 int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch,
                           unsigned *fv_winner, float *front, cudaStream_t s);
 int launch_pyfront_link(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const PyFrontParams &fp,

@@ -8,6 +8,11 @@
 #include <algorithm>
 #include <chrono>
 
+#ifdef __linux__
+#include <pthread.h>
+#include <sched.h>
+#endif
+
 #if defined(__SSE2__) || defined(__x86_64__)
 #include <emmintrin.h>
 #include <xmmintrin.h>
@@ -37,10 +42,35 @@ static bool spin_until(Pred pred)
     }
 }
 
-HostPool::HostPool(int threads)
+std::vector<int> host_cpu_share(int index, int sharers)
+{
+    std::vector<int> all;
+#ifdef __linux__
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    if (sched_getaffinity(0, sizeof(set), &set) == 0)
+        for (int c = 0; c < CPU_SETSIZE; c++)
+            if (CPU_ISSET(c, &set)) all.push_back(c);
+#endif
+    if (sharers <= 1 || index < 0 || index >= sharers || (int)all.size() < sharers) return all;
+    const size_t per = all.size() / (size_t)sharers;
+    return std::vector<int>(all.begin() + (size_t)index * per, all.begin() + ((size_t)index + 1) * per);
+}
+
+HostPool::HostPool(int threads, const std::vector<int> &cpus)
 {
     if (threads < 1) threads = 1;
-    for (int i = 0; i < threads - 1; i++) workers_.emplace_back([this] { worker(); });
+    for (int i = 0; i < threads - 1; i++) {
+        workers_.emplace_back([this] { worker(); });
+#ifdef __linux__
+        if (!cpus.empty()) {  // worker 0 leaves the first CPU of the range to the calling thread
+            cpu_set_t set;
+            CPU_ZERO(&set);
+            CPU_SET(cpus[(size_t)(i + 1) % cpus.size()], &set);
+            pthread_setaffinity_np(workers_.back().native_handle(), sizeof(set), &set);
+        }
+#endif
+    }
 }
 
 HostPool::~HostPool()

@@ -19,7 +19,9 @@ namespace mv3d {
 // A small fork-join pool: parallel_for(parts, fn) runs fn(0..parts-1) on the workers and the calling thread.
 class HostPool {
 public:
-    explicit HostPool(int threads);
+    // `cpus`: if non-empty, worker i is pinned to cpus[i % size] (ranks that share a host take disjoint core ranges,
+    // see host_cpu_share); the calling thread is never re-pinned.
+    explicit HostPool(int threads, const std::vector<int> &cpus = std::vector<int>());
     ~HostPool();
     int size() const { return (int)workers_.size() + 1; }
     // `caller_first`, if given, runs on the calling thread after the workers have been released and before the
@@ -39,6 +41,10 @@ private:
     std::atomic<unsigned long long> generation_{0};
     std::atomic<bool> stop_{false};
 };
+
+// The CPUs this process may run on (sched_getaffinity), cut into `sharers` equal consecutive ranges; returns range
+// number `index`. One process per GPU under torchrun: sharers = LOCAL_WORLD_SIZE, index = LOCAL_RANK.
+std::vector<int> host_cpu_share(int index, int sharers);
 
 // dst[cells][planes] = 0 except dst[idx[i]][:] = vals[i][:] for the n entries (a cell appears at most once).
 // Entries with a cell index >= cells (kNoCell marks an unused slot) are ignored. The destination is written once,

@@ -82,37 +82,10 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     ctx->smem_optin = prop.sharedMemPerBlockOptin;
     const char *tb = getenv("MV3D_TILE_BYTES");
     ctx->tile_bytes_target = tb ? (size_t)strtoull(tb, nullptr, 10) : (size_t)(36 * 1024);
-    if (const char *pm = getenv("MV3D_PATCH_MODE")) ctx->patch_mode = (strcmp(pm, "warp") == 0 || strcmp(pm, "0") == 0) ? 0 : 1;
-    const char *pb = getenv("MV3D_PATCH_TILE_BYTES");
-    ctx->patch_tile_bytes = pb ? (size_t)strtoull(pb, nullptr, 10) : (size_t)(ctx->patch_mode ? 36 * 1024 : 6912);
-    const char *fa = getenv("MV3D_FILL_CTAS");
-    ctx->fill_ctas = fa ? atoi(fa) : 2;
-    if (ctx->fill_ctas < 1) ctx->fill_ctas = 1;
-    if (const char *ts = getenv("MV3D_TILE_STORE")) {
-        const char *names[] = {"tma", "tma_hint", "tma_split", "lsu", "lsu_cs", "tma_paced"};
-        for (int i = 0; i < 6; i++)
-            if (strcmp(ts, names[i]) == 0) ctx->tile_store = i;
-    }
-    if (const char *tp = getenv("MV3D_TILE_PIPE")) {
-        int v[4] = {0, ctx->pipe_group_threads, ctx->pipe_chunk, ctx->pipe_pending};
-        sscanf(tp, "%d,%d,%d,%d", &v[0], &v[1], &v[2], &v[3]);
-        ctx->pipe_groups = v[0] < 0 ? 0 : (v[0] > 5 ? 5 : v[0]);
-        ctx->pipe_group_threads = v[1] < 32 ? 32 : (v[1] & ~31);
-        ctx->pipe_chunk = v[2] < 16 ? 16 : (v[2] & ~15);
-        ctx->pipe_pending = v[3] < 0 ? 0 : v[3];
-    }
-    const char *fs = getenv("MV3D_FRONT_ASIDE");
-    ctx->front_aside = fs ? atoi(fs) : 1;
-    const char *ao = getenv("MV3D_ATOMIC_OVERLAP");
-    ctx->atomic_overlap = ao ? atoi(ao) : 0;
-    const char *fpn = getenv("MV3D_FILL_PENDING");
-    ctx->fill_pending = fpn ? atoi(fpn) : 4;
     ctx->smem_per_sm = prop.sharedMemPerMultiprocessor;
     const char *fc = getenv("MV3D_FILL_CHUNK");
     ctx->fill_chunk = fc ? atoi(fc) : 8;
     if (ctx->fill_chunk < 1) ctx->fill_chunk = 1;
-    const char *pm = getenv("MV3D_PATCH_MIN_BATCH");
-    ctx->patch_min_batch = pm ? atoi(pm) : 1 << 30;
     const char *ht = getenv("MV3D_HOST_THREADS");
     ctx->host_threads = ht ? atoi(ht) : 0;
     if (const char *hs = getenv("MV3D_HOST_SPLIT_FIRST")) ctx->host_split_first = atoi(hs);
@@ -120,8 +93,6 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     ctx->host_compact = (hr && strcmp(hr, "dense") == 0) ? 0 : 1;
     if (const char *ab = getenv("MV3D_AUTO_ATOMIC_BATCH")) ctx->auto_atomic_batch = atoi(ab);
     if (const char *ar = getenv("MV3D_AUTO_ATOMIC_RATIO")) ctx->auto_atomic_ratio = atof(ar);
-    const char *sb = getenv("MV3D_SUB_BATCH");
-    ctx->sub_batch = sb ? atoi(sb) : 0;  // measured on B200: two-stream pipelining loses to one stream (profiles/)
     int prio_lo = 0, prio_hi = 0;
     cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);  // the zero-fill is the long pole of PATCH: never starve it
     bool ok = cudaStreamCreateWithPriority(&ctx->side_stream, cudaStreamNonBlocking, prio_hi) == cudaSuccess &&
@@ -264,34 +235,13 @@ static int pick_tile_cells(size_t bytes_target, int planes, long long cells)
     return (int)t;
 }
 
-// Pipelined tile kernel: as many tile images per CTA as the context asks for and shared memory holds; below two the
-// one-tile-per-CTA kernel is used.
-static void apply_pipe(const mv3d_ctx *ctx, ViewParams *p)
-{
-    p->pipe_groups = 0;
-    int g = ctx->pipe_groups;
-    if (g <= 0 || p->tile_cells <= 0) return;
-    while (g * ctx->pipe_group_threads + 32 > 1024) g--;
-    ViewParams q = *p;
-    for (; g >= 2; g--) {
-        q.pipe_groups = g;
-        if (tile_pipe_smem_bytes(q) <= ctx->smem_optin) break;
-    }
-    if (g < 2) return;
-    p->pipe_groups = g;
-    p->pipe_group_threads = ctx->pipe_group_threads;
-    p->pipe_chunk = ctx->pipe_chunk;
-    p->pipe_pending = ctx->pipe_pending;
-    p->pipe_grid = ctx->sm_count;
-}
-
-static bool tile_feasible(const mv3d_ctx *ctx, const mv3d_top_params *tp, bool patch)
+static bool tile_feasible(const mv3d_ctx *ctx, const mv3d_top_params *tp)
 {
     if (!tp || tp->zn > 65535) return false;
     const int planes = tp->zn + 2;
-    const int t = pick_tile_cells(patch ? ctx->patch_tile_bytes : ctx->tile_bytes_target, planes, (long long)tp->xn * tp->yn);
+    const int t = pick_tile_cells(ctx->tile_bytes_target, planes, (long long)tp->xn * tp->yn);
     const size_t per = (((size_t)t * planes * 4 + 15) & ~(size_t)15) + (size_t)t * 12 + 64;
-    return ((patch && ctx->patch_mode == 0) ? per * 8 : per) <= ctx->smem_optin;  // warp patch: one image per warp, 8 warps per CTA
+    return per <= ctx->smem_optin;
 }
 
 extern "C" int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params *tp, int strategy)
@@ -299,8 +249,8 @@ extern "C" int mv3d_resolve_strategy(const mv3d_ctx *ctx, const mv3d_top_params 
     if (strategy == MV3D_STRATEGY_ATOMIC) return MV3D_STRATEGY_ATOMIC;
     if (!ctx || !tp) return MV3D_STRATEGY_ATOMIC;
     if (strategy == MV3D_STRATEGY_SORT) return MV3D_STRATEGY_SORT;  // checked per call: the keys must fit 32 bits
-    if (strategy == MV3D_STRATEGY_PATCH && tile_feasible(ctx, tp, true)) return MV3D_STRATEGY_PATCH;
-    if (!tile_feasible(ctx, tp, false)) return MV3D_STRATEGY_ATOMIC;
+    if (!tile_feasible(ctx, tp)) return MV3D_STRATEGY_ATOMIC;
+    if (strategy == MV3D_STRATEGY_PATCH) return MV3D_STRATEGY_PATCH;
     return MV3D_STRATEGY_TILE;  // AUTO is refined per call by the batch size (see resolve_for_batch)
 }
 
@@ -315,7 +265,6 @@ static int resolve_for_batch(const mv3d_ctx *ctx, const mv3d_top_params *tp, int
 {
     const int r = mv3d_resolve_strategy(ctx, tp, strategy);
     if (strategy != MV3D_STRATEGY_AUTO || r != MV3D_STRATEGY_TILE) return r;
-    if (batch >= ctx->patch_min_batch && tile_feasible(ctx, tp, true)) return MV3D_STRATEGY_PATCH;
     if (points_total >= 0 && batch > 0) {
         const double out_bytes = (double)batch * tp->xn * tp->yn * (tp->zn + 2) * 4.0;
         if (batch <= ctx->auto_atomic_batch || 16.0 * (double)points_total > ctx->auto_atomic_ratio * out_bytes)
@@ -332,7 +281,7 @@ static float fast_reciprocal(float div)
 }
 
 static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3d_front_params *fp, bool want_top,
-                       bool want_front, int semantics, int strategy, ViewParams *out)
+                       bool want_front, int semantics, ViewParams *out)
 {
     if (!tp) return fail("top parameters are required (the front view is gated by the bird's-eye-view box)");
     if (semantics != MV3D_SEM_TOP && semantics != MV3D_SEM_TOPFRONT) return fail("unknown semantics %d", semantics);
@@ -352,12 +301,9 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
     p.want_top = want_top ? 1 : 0;
     p.want_front = want_front ? 1 : 0;
     p.top_frame_floats = cells * p.planes;
-    p.tile_cells = pick_tile_cells(strategy == MV3D_STRATEGY_PATCH ? ctx->patch_tile_bytes : ctx->tile_bytes_target,
-                                   p.planes, cells);
+    p.tile_cells = pick_tile_cells(ctx->tile_bytes_target, p.planes, cells);
     p.tiles_per_frame = (cells > 0 && p.tile_cells > 0) ? (int)((cells + p.tile_cells - 1) / p.tile_cells) : 0;
-    p.store_mode = ctx->tile_store;
     p.tile_magic = tile_magic_for(p.tile_cells);
-    if (strategy != MV3D_STRATEGY_PATCH) apply_pipe(ctx, &p);
     p.z_span = tp->z_max - tp->z_min;  // float subtraction, LidarTopAndFrontPreprocess.c:185
     if (want_front) {
         if (!fp) return fail("front parameters are required when a front view is requested");
@@ -385,6 +331,23 @@ static int make_params(const mv3d_ctx *ctx, const mv3d_top_params *tp, const mv3
 // ------------------------------------------------------------------------------------------------
 // enqueue one chunk (<= kMaxBatchPerLaunch sweeps) on a stream
 // ------------------------------------------------------------------------------------------------
+// Resident CTAs per SM of the tile kernels for this parameter set. The shared-memory opt-in and the occupancy query
+// cost tens of microseconds of host time, so they run once per (semantics, shared-memory size) and context, not per
+// call; the opt-in covers every variant of the tile kernel (dense, occupancy-reporting, patch, compact).
+static int tile_blocks_per_sm(mv3d_ctx *ctx, const ViewParams &p)
+{
+    const size_t smem = tile_smem_bytes(p);
+    for (const auto &c : ctx->tile_cfg)
+        if (c.smem == smem && c.py == p.py) return c.blocks_per_sm;
+    int blocks = 0;
+    if (tile_kernels_configure(p, &blocks) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    ctx->tile_cfg.push_back({smem, p.py, blocks});
+    return blocks;
+}
+
 static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, const int *offsets, int batch,
                          float *top_dev, float *front_dev, const ViewParams &p, int strategy, cudaStream_t s,
                          const CompactOut *compact = nullptr, const OccupancySink *sink = nullptr)
@@ -406,6 +369,7 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
         if (ensure(ws.fv_winner, (size_t)batch * p.front_pixels * 4, true, s)) return -1;
     }
     unsigned *winners = static_cast<unsigned *>(ws.fv_winner.ptr);
+    const bool want_front = p.want_front && p.front_pixels > 0;
 
     if (p.want_top && cells > 0 && (strategy == MV3D_STRATEGY_TILE || strategy == MV3D_STRATEGY_PATCH)) {
         const bool patch = strategy == MV3D_STRATEGY_PATCH;
@@ -414,29 +378,16 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
         const size_t hist = (size_t)batch * (p.tiles_per_frame + 1) * 4;
         if (ensure(ws.tile_count, hist, true, s)) return -1;
         if (ensure(ws.tile_off, hist, false, s)) return -1;
-        int blocks_per_sm = 0;
-        if (patch && ctx->patch_mode == 1) {
-            CUDA_TRY(tile_patch_configure(p, &blocks_per_sm));
-        } else if (patch) {
-            CUDA_TRY(warp_patch_configure(p, &blocks_per_sm));
-            // leave shared memory for the fill CTAs that must stay resident beside the patch warps
-            const size_t fill_need = (size_t)ctx->fill_ctas * (fill_tma_smem_bytes() + 1024);
-            const size_t per_cta = patch_smem_bytes(p) + 1024;
-            const int room = ctx->smem_per_sm > fill_need ? (int)((ctx->smem_per_sm - fill_need) / per_cta) : 0;
-            if (blocks_per_sm > room) blocks_per_sm = room;
-        } else {
-            CUDA_TRY(tile_build_configure(p, &blocks_per_sm));
-        }
-        if (blocks_per_sm < 1) return fail("tile kernel does not fit: %zu bytes of shared memory",
-                                           patch ? patch_smem_bytes(p) : tile_smem_bytes(p));
+        const int blocks_per_sm = tile_blocks_per_sm(ctx, p);
+        if (blocks_per_sm < 1) return fail("tile kernel does not fit: %zu bytes of shared memory", tile_smem_bytes(p));
         uint2 *keys = static_cast<uint2 *>(ws.keys.ptr);
         uint4 *binned = static_cast<uint4 *>(ws.binned.ptr);
         unsigned *tcount = static_cast<unsigned *>(ws.tile_count.ptr), *toff = static_cast<unsigned *>(ws.tile_off.ptr);
         const int grid_blocks = blocks_per_sm * ctx->sm_count;
         if (patch) {
-            // PATCH: the zero-fill of the whole output runs on the side stream as a handful of one-warp-per-SM TMA
-            // kernels (HBM-bound, almost no SM resources) while the point passes (compute/latency-bound) run on the
-            // caller's stream; each chunk of sweeps is then patched as soon as its fill has finished.
+            // PATCH: the copy engine zero-fills the output on the side stream (cudaMemsetAsync: no SM, 7.0-7.3 TB/s)
+            // while the point passes run on the caller's stream; each chunk of sweeps is then patched (touched cells
+            // only) as soon as its fill has finished. Measured comparison point of DESIGN.md 5.1, not what AUTO picks.
             const int chunk = ctx->fill_chunk;
             cudaStream_t sf = ctx->side_stream;
             CUDA_TRY(cudaEventRecord(ctx->ev_fork, s));
@@ -444,23 +395,18 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
             for (int j0 = 0, j = 0; j0 < batch; j0 += chunk, j++) {
                 const int nb = (batch - j0 < chunk) ? batch - j0 : chunk;
                 float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
-                if (ctx->patch_mode == 1) {  // the copy engine writes zeros faster than any kernel does, and needs no SM
-                    timed_launch(ctx, K_FILL_CE, sf, [&] {
-                        cudaMemsetAsync(top_j, 0, (size_t)nb * (size_t)p.top_frame_floats * 4, sf);
-                        return 0;  // not a kernel of this library: timed, but not counted as a launch
-                    });
-                    ctx->kernel_launches[K_FILL_CE]++;
-                } else
-                    timed_launch(ctx, K_FILL_TMA, sf, [&] {
-                        return launch_fill_tma(top_j, (size_t)nb * (size_t)p.top_frame_floats, ctx->sm_count * ctx->fill_ctas, ctx->fill_pending, sf);
-                    });
+                timed_launch(ctx, K_FILL_CE, sf, [&] {
+                    cudaMemsetAsync(top_j, 0, (size_t)nb * (size_t)p.top_frame_floats * 4, sf);
+                    return 0;  // not a kernel of this library: timed, but not counted as a launch
+                });
+                ctx->kernel_launches[K_FILL_CE]++;
                 CUDA_TRY(cudaEventRecord(ctx->ev_ready[j], sf));
             }
             timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, winners, s); });
             timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
-            timed_launch(ctx, K_BIN, s, [&] { return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s); });
-            if (p.want_front && p.front_pixels > 0)
-                timed_launch(ctx, K_FRONT_FINALIZE, s, [&] { return launch_front_finalize(pts, offs, p, batch, winners, front_dev, s); });
+            timed_launch(ctx, K_BIN, s, [&] {
+                return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s, want_front ? winners : nullptr, front_dev);
+            });
             for (int j0 = 0, j = 0; j0 < batch; j0 += chunk, j++) {
                 const int nb = (batch - j0 < chunk) ? batch - j0 : chunk;
                 FrameOffsets so;
@@ -469,86 +415,32 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
                 unsigned *to = toff + (size_t)j0 * (p.tiles_per_frame + 1);
                 float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
                 CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_ready[j], 0));
-                if (ctx->patch_mode == 1)
-                    timed_launch(ctx, K_TILE_PATCH, s, [&] {
-                        return launch_tile_patch(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
-                    });
-                else
-                    timed_launch(ctx, K_WARP_PATCH, s, [&] {
-                        return launch_warp_patch(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
-                    });
+                timed_launch(ctx, K_TILE_PATCH, s, [&] {
+                    return launch_tile_patch(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
+                });
             }
             CUDA_TRY(cudaGetLastError());
             return 0;
         }
-        // Sub-batch pipeline: the point passes (classify -> scan -> bin) of sub-batch j+1 run on a side stream
-        // while the memory-bound tile kernel of sub-batch j streams its output on the caller's stream.
-        const int sub = (ctx->sub_batch > 0 && ctx->sub_batch < batch && ctx->side_stream) ? ctx->sub_batch : batch;
-        const bool piped = sub < batch;
-        const bool front_aside = !piped && !compact && ctx->front_aside && ctx->side_stream && p.want_front &&
-                                 p.front_pixels > 0 && batch >= 8;
-        cudaStream_t sp = piped ? ctx->side_stream : s;
-        if (piped) {
-            CUDA_TRY(cudaEventRecord(ctx->ev_fork, s));
-            CUDA_TRY(cudaStreamWaitEvent(sp, ctx->ev_fork, 0));
-        }
-        for (int j0 = 0, j = 0; j0 < batch; j0 += sub, j++) {
-            const int nb = (batch - j0 < sub) ? batch - j0 : sub;
-            FrameOffsets so;
-            memset(&so, 0, sizeof(so));
-            int sub_max = 0;
-            for (int i = 0; i <= nb; i++) so.off[i] = offs.off[j0 + i];
-            for (int i = 0; i < nb; i++) sub_max = (so.off[i + 1] - so.off[i] > sub_max) ? so.off[i + 1] - so.off[i] : sub_max;
-            unsigned *tc = tcount + (size_t)j0 * (p.tiles_per_frame + 1), *to = toff + (size_t)j0 * (p.tiles_per_frame + 1);
-            unsigned *win = winners ? winners + (size_t)j0 * p.front_pixels : nullptr;
-            timed_launch(ctx, K_CLASSIFY, sp, [&] { return launch_classify(pts, so, p, nb, sub_max, keys, tc, win, sp); });
-            if (front_aside) {
-                // The front view only needs the winners classify just elected: finish it on the side stream, beside
-                // scan / bin / tile build, instead of after them.
-                CUDA_TRY(cudaEventRecord(ctx->ev_fork, s));
-                CUDA_TRY(cudaStreamWaitEvent(ctx->side_stream, ctx->ev_fork, 0));
-                timed_launch(ctx, K_FRONT_FINALIZE, ctx->side_stream, [&] {
-                    return launch_front_finalize(pts, offs, p, batch, winners, front_dev, ctx->side_stream);
-                });
-                CUDA_TRY(cudaEventRecord(ctx->ev_join, ctx->side_stream));
-            }
-            timed_launch(ctx, K_TILE_SCAN, sp, [&] { return launch_tile_scan(tc, to, p.tiles_per_frame, nb, sp); });
-            timed_launch(ctx, K_BIN, sp, [&] { return launch_bin(pts, so, p, nb, sub_max, keys, to, binned, sp); });
-            if (piped) {
-                CUDA_TRY(cudaEventRecord(ctx->ev_ready[j], sp));
-                CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_ready[j], 0));
-            }
-            if (compact) {  // host read-back: report the touched cells only (single sweep per call)
-                timed_launch(ctx, K_TILE_COMPACT, s, [&] {
-                    return launch_tile_compact(binned, to, so, p, ctx->lut, nb, grid_blocks, compact->entries,
-                                               compact->cap, s);
-                });
-                continue;
-            }
-            float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
-            OccupancySink sink_j;
-            if (sink && strategy == MV3D_STRATEGY_TILE) {
-                sink_j = *sink;
-                sink_j.words += (size_t)j0 * sink->words_per_frame;
-                sink_j.flags += j0;
-            }
+        // TILE: classify -> scan -> bin (+ the front view's second half, as extra CTAs of the same launch) -> tile build,
+        // each launched with programmatic serialization so that its prologue overlaps the predecessor's tail.
+        timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, winners, s); });
+        timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
+        timed_launch(ctx, K_BIN, s, [&] {
+            return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s, want_front ? winners : nullptr, front_dev);
+        });
+        if (compact) {  // host read-back: report the touched cells only (single sweep per call)
+            timed_launch(ctx, K_TILE_COMPACT, s, [&] {
+                return launch_tile_compact(binned, toff, offs, p, ctx->lut, batch, grid_blocks, compact->entries,
+                                           compact->cap, s);
+            });
+        } else {
             timed_launch(ctx, K_TILE_BUILD, s, [&] {
-                return launch_tile_build(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s, &sink_j);
+                return launch_tile_build(binned, toff, offs, p, ctx->lut, top_dev, batch, grid_blocks, s, sink);
             });
         }
-        if (front_aside) {
-            CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_join, 0));
-            CUDA_TRY(cudaGetLastError());
-            return 0;
-        }
-        if (piped) {
-            if (p.want_front && p.front_pixels > 0)
-                timed_launch(ctx, K_FRONT_FINALIZE, sp, [&] { return launch_front_finalize(pts, offs, p, batch, winners, front_dev, sp); });
-            CUDA_TRY(cudaEventRecord(ctx->ev_join, sp));
-            CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_join, 0));
-            CUDA_TRY(cudaGetLastError());
-            return 0;
-        }
+        CUDA_TRY(cudaGetLastError());
+        return 0;
     } else if (p.want_top && cells > 0 && strategy == MV3D_STRATEGY_SORT) {
         const unsigned invalid_key = sort_invalid_key(p, batch);
         if (p.py || invalid_key == 0u)
@@ -575,61 +467,23 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
     } else if (p.want_top && cells > 0) {
         if (ensure(ws.cellkey, (size_t)batch * cells * 8, false, s)) return -1;
         unsigned long long *cellkey = static_cast<unsigned long long *>(ws.cellkey.ptr);
-        const int chunk = ctx->fill_chunk;
-        if (ctx->atomic_overlap && batch > chunk && ctx->side_stream) {
-            // Zero-fill by TMA on the side stream, chunk by chunk; the atomic passes of chunk j start as soon as
-            // its fill is done and run beside the fill of the later chunks.
-            cudaStream_t sf = ctx->side_stream;
-            CUDA_TRY(cudaEventRecord(ctx->ev_fork, s));
-            CUDA_TRY(cudaStreamWaitEvent(sf, ctx->ev_fork, 0));
-            const int fill_blocks = ctx->sm_count * ctx->fill_ctas;
-            for (int j0 = 0, j = 0; j0 < batch; j0 += chunk, j++) {
-                const int nb = (batch - j0 < chunk) ? batch - j0 : chunk;
-                timed_launch(ctx, K_FILL_TMA, sf, [&] {
-                    return launch_fill_tma(top_dev + (size_t)j0 * (size_t)p.top_frame_floats,
-                                           (size_t)nb * (size_t)p.top_frame_floats, fill_blocks, ctx->fill_pending, sf) +
-                           launch_fill_tma(reinterpret_cast<float *>(cellkey + (size_t)j0 * cells), (size_t)nb * cells * 2,
-                                           fill_blocks, ctx->fill_pending, sf);
-                });
-                CUDA_TRY(cudaEventRecord(ctx->ev_ready[j], sf));
-            }
-            for (int j0 = 0, j = 0; j0 < batch; j0 += chunk, j++) {
-                const int nb = (batch - j0 < chunk) ? batch - j0 : chunk;
-                FrameOffsets so;
-                memset(&so, 0, sizeof(so));
-                int sub_max = 0;
-                for (int i = 0; i <= nb; i++) so.off[i] = offs.off[j0 + i];
-                for (int i = 0; i < nb; i++) sub_max = (so.off[i + 1] - so.off[i] > sub_max) ? so.off[i + 1] - so.off[i] : sub_max;
-                float *top_j = top_dev + (size_t)j0 * (size_t)p.top_frame_floats;
-                unsigned long long *key_j = cellkey + (size_t)j0 * cells;
-                unsigned *win = winners ? winners + (size_t)j0 * p.front_pixels : nullptr;
-                CUDA_TRY(cudaStreamWaitEvent(s, ctx->ev_ready[j], 0));
-                timed_launch(ctx, K_ATOMIC_SCATTER, s, [&] {
-                    return launch_atomic_scatter(pts, so, p, nb, sub_max, top_j, key_j, win, s);
-                });
-                timed_launch(ctx, K_ATOMIC_FINALIZE, s, [&] {
-                    return launch_atomic_finalize(pts, so, p, ctx->lut, nb, sub_max, top_j, key_j, s);
-                });
-            }
-        } else {
-            timed_launch(ctx, K_FILL_ZERO, s, [&] {
-                return launch_fill_zero(top_dev, (size_t)batch * (size_t)p.top_frame_floats, ctx->sm_count, s) +
-                       launch_fill_zero(reinterpret_cast<float *>(cellkey), (size_t)batch * cells * 2, ctx->sm_count, s);
-            });
-            timed_launch(ctx, K_ATOMIC_SCATTER, s, [&] {
-                return launch_atomic_scatter(pts, offs, p, batch, max_points, top_dev, cellkey, winners, s);
-            });
-            timed_launch(ctx, K_ATOMIC_FINALIZE, s, [&] {
-                return launch_atomic_finalize(pts, offs, p, ctx->lut, batch, max_points, top_dev, cellkey, s);
-            });
-        }
+        timed_launch(ctx, K_FILL_ZERO, s, [&] {
+            return launch_fill_zero(top_dev, (size_t)batch * (size_t)p.top_frame_floats, ctx->sm_count, s) +
+                   launch_fill_zero(reinterpret_cast<float *>(cellkey), (size_t)batch * cells * 2, ctx->sm_count, s);
+        });
+        timed_launch(ctx, K_ATOMIC_SCATTER, s, [&] {
+            return launch_atomic_scatter(pts, offs, p, batch, max_points, top_dev, cellkey, winners, s);
+        });
+        timed_launch(ctx, K_ATOMIC_FINALIZE, s, [&] {
+            return launch_atomic_finalize(pts, offs, p, ctx->lut, batch, max_points, top_dev, cellkey, s);
+        });
     } else if (p.want_front) {
         // front view only: the classify pass alone elects the winners (BEV gate still applies)
         ViewParams q = p;
         q.want_top = 0;
         timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, q, batch, max_points, nullptr, nullptr, winners, s); });
     }
-    if (p.want_front && p.front_pixels > 0)
+    if (want_front)
         timed_launch(ctx, K_FRONT_FINALIZE, s, [&] { return launch_front_finalize(pts, offs, p, batch, winners, front_dev, s); });
     CUDA_TRY(cudaGetLastError());
     return 0;
@@ -678,7 +532,7 @@ extern "C" int mv3d_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, con
     if (check_offsets(offsets_host, batch)) return -1;
     ViewParams p;
     const int strat = resolve_for_batch(ctx, tp, strategy, batch, (long long)offsets_host[batch] - offsets_host[0]);
-    if (make_params(ctx, tp, fp, top_dev != nullptr, front_dev != nullptr, semantics, strat, &p)) return -1;
+    if (make_params(ctx, tp, fp, top_dev != nullptr, front_dev != nullptr, semantics, &p)) return -1;
     if (batch == 0 || (!top_dev && !front_dev)) return 0;
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
@@ -693,7 +547,7 @@ extern "C" int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int
 {
     if (!ctx) return fail("mv3d_debug_point_keys: ctx is NULL");
     ViewParams p;
-    if (make_params(ctx, tp, fp, true, fp != nullptr, semantics, MV3D_STRATEGY_TILE, &p)) return -1;
+    if (make_params(ctx, tp, fp, true, fp != nullptr, semantics, &p)) return -1;
     if (!cell_dev || (fp && (!pix_dev || !pix_exact_dev))) return fail("mv3d_debug_point_keys: output pointer is NULL");
     std::lock_guard<std::mutex> lock(ctx->mu);
     CUDA_TRY(cudaSetDevice(ctx->device));
@@ -712,25 +566,37 @@ static int py_encode_dev_locked(mv3d_ctx *ctx, Workspace &ws, const float *point
                                 float *top_dev, float *front_dev, const ViewParams &p, const PyFrontParams &fp,
                                 cudaStream_t s, const OccupancySink *sink, const CompactOut *compact);
 
+// Host threads of the compact read-back. Processes that share the host (one per GPU under torchrun) share its cores:
+// rank r of LOCAL_WORLD_SIZE takes the r-th consecutive range of the CPUs the process may run on and pins its workers
+// there (MV3D_HOST_PIN=0: unpinned), so eight ranks do not migrate over each other's caches and memory channels.
+// Default thread count: the share's size, at most 16 (measured on the B200 hosts: 8 -> 16 streaming writers still
+// gains 40 %, beyond that the host memory is the limit); MV3D_HOST_THREADS overrides.
+static int ensure_host_pool(mv3d_ctx *ctx)
+{
+    if (ctx->pool) return 0;
+    const char *lws = getenv("LOCAL_WORLD_SIZE"), *lr = getenv("LOCAL_RANK");
+    const int sharers = lws && atoi(lws) > 0 ? atoi(lws) : 1;
+    const int index = lr ? atoi(lr) : 0;
+    std::vector<int> cpus = host_cpu_share(index, sharers);
+    int threads = ctx->host_threads;
+    if (threads <= 0) {
+        size_t hw = cpus.empty() ? std::thread::hardware_concurrency() / (unsigned)sharers : cpus.size();
+        if (hw < 2) hw = 2;
+        threads = (int)(hw < 16 ? hw : 16);
+    }
+    const char *pin = getenv("MV3D_HOST_PIN");
+    const bool want_pin = pin ? atoi(pin) != 0 : sharers > 1;
+    ctx->pool.reset(new (std::nothrow) HostPool(threads, want_pin ? cpus : std::vector<int>()));
+    if (!ctx->pool) return fail("cannot create the host thread pool");
+    return 0;
+}
+
 // pyfp: non-NULL for the Python-twin mode (its own front view and encode call; everything else is shared).
 static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const int *offsets_host, int batch,
                                float *top_host, float *front_host, const ViewParams &p,
                                const PyFrontParams *pyfp = nullptr)
 {
-    if (!ctx->pool) {
-        int threads = ctx->host_threads;
-        if (threads <= 0) {
-            // measured on the B200 host: 8 -> 16 streaming writers still gains 40 %. Processes that share the host
-            // (one per GPU under torchrun: LOCAL_WORLD_SIZE) share its cores too.
-            unsigned hw = std::thread::hardware_concurrency();
-            const char *lws = getenv("LOCAL_WORLD_SIZE");
-            const int sharers = lws && atoi(lws) > 0 ? atoi(lws) : 1;
-            if (hw) hw = hw / sharers > 2 ? hw / sharers : 2;
-            threads = hw ? (int)(hw < 16 ? hw : 16) : 4;
-        }
-        ctx->pool.reset(new (std::nothrow) HostPool(threads));
-        if (!ctx->pool) return fail("cannot create the host thread pool");
-    }
+    if (ensure_host_pool(ctx)) return -1;
     const size_t cells = (size_t)p.xn * p.yn;
     const size_t front_floats = pyfp ? (size_t)pyfp->pixels * 3 : (size_t)p.front_frame_floats;
     const size_t front_bytes = front_floats * 4;
@@ -860,7 +726,7 @@ extern "C" int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, c
     if (check_offsets(offsets_host, batch)) return -1;
     ViewParams p;
     const int strat = resolve_for_batch(ctx, tp, strategy, 1);  // the host pipeline encodes sweep by sweep
-    if (make_params(ctx, tp, fp, top_host != nullptr, front_host != nullptr, semantics, strat, &p)) return -1;
+    if (make_params(ctx, tp, fp, top_host != nullptr, front_host != nullptr, semantics, &p)) return -1;
     if (batch == 0 || (!top_host && !front_host)) return 0;
     if (offsets_host[batch] > offsets_host[0] && !points_host) return fail("points_host is NULL");
     std::lock_guard<std::mutex> lock(ctx->mu);
@@ -885,9 +751,12 @@ extern "C" int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, c
         if (ensure(slot.points, (size_t)n * 16 + 16, false, s)) { rc = -1; break; }
         if (top_host && ensure(slot.top, top_bytes + 16, false, s)) { rc = -1; break; }
         if (front_host && ensure(slot.front, front_bytes + 16, false, s)) { rc = -1; break; }
+        // A failure must not return while earlier copies are still writing the caller's buffers: break, then drain.
+        cudaError_t ce = cudaSuccess;
         if (n > 0)
-            CUDA_TRY(cudaMemcpyAsync(slot.points.ptr, points_host + (size_t)offsets_host[i] * 4, (size_t)n * 16,
-                                     cudaMemcpyHostToDevice, s));
+            ce = cudaMemcpyAsync(slot.points.ptr, points_host + (size_t)offsets_host[i] * 4, (size_t)n * 16,
+                                 cudaMemcpyHostToDevice, s);
+        if (ce != cudaSuccess) { rc = fail("copy-in of sweep %d failed: %s", i, cudaGetErrorString(ce)); break; }
         const int local_off[2] = {0, n};
         float *top_d = top_host ? static_cast<float *>(slot.top.ptr) : nullptr;
         float *front_d = front_host ? static_cast<float *>(slot.front.ptr) : nullptr;
@@ -896,11 +765,12 @@ extern "C" int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, c
         ctx->h2d_bytes += (size_t)n * 16;
         ctx->d2h_bytes += (top_host ? top_bytes : 0) + (front_host ? front_bytes : 0);
         if (top_host && top_bytes)
-            CUDA_TRY(cudaMemcpyAsync(top_host + (size_t)i * (size_t)p.top_frame_floats, top_d, top_bytes,
-                                     cudaMemcpyDeviceToHost, s));
-        if (front_host && front_bytes)
-            CUDA_TRY(cudaMemcpyAsync(front_host + (size_t)i * (size_t)p.front_frame_floats, front_d, front_bytes,
-                                     cudaMemcpyDeviceToHost, s));
+            ce = cudaMemcpyAsync(top_host + (size_t)i * (size_t)p.top_frame_floats, top_d, top_bytes,
+                                 cudaMemcpyDeviceToHost, s);
+        if (ce == cudaSuccess && front_host && front_bytes)
+            ce = cudaMemcpyAsync(front_host + (size_t)i * (size_t)p.front_frame_floats, front_d, front_bytes,
+                                 cudaMemcpyDeviceToHost, s);
+        if (ce != cudaSuccess) { rc = fail("copy-out of sweep %d failed: %s", i, cudaGetErrorString(ce)); break; }
     }
     for (auto &slot : ctx->slots)
         if (slot.stream) {
@@ -935,9 +805,7 @@ static int make_py_params(const mv3d_ctx *ctx, const mv3d_pytwin_params *pp, boo
     p.top_frame_floats = cells * p.planes;
     p.tile_cells = pick_tile_cells(ctx->tile_bytes_target, p.planes, cells);
     p.tiles_per_frame = (cells > 0 && p.tile_cells > 0) ? (int)((cells + p.tile_cells - 1) / p.tile_cells) : 0;
-    p.store_mode = ctx->tile_store;
     p.tile_magic = tile_magic_for(p.tile_cells);
-    apply_pipe(ctx, &p);
     PyFrontParams f;
     memset(&f, 0, sizeof(f));
     f.ang_res = pp->ang_res; f.vert_res = pp->vert_res; f.velodyne_height = pp->velodyne_height;
@@ -973,13 +841,12 @@ static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_de
         mv3d_top_params tp;
         memset(&tp, 0, sizeof(tp));
         tp.xn = p.xn; tp.yn = p.yn; tp.zn = p.zn;
-        if (!tile_feasible(ctx, &tp, false)) return fail("python-twin mode needs the tile strategy: a tile of this grid does not fit shared memory");
+        if (!tile_feasible(ctx, &tp)) return fail("python-twin mode needs the tile strategy: a tile of this grid does not fit shared memory");
         const size_t hist = (size_t)batch * (p.tiles_per_frame + 1) * 4;
         if (ensure(ws.tile_count, hist, true, s)) return -1;
         if (ensure(ws.tile_off, hist, false, s)) return -1;
         unsigned *tcount = static_cast<unsigned *>(ws.tile_count.ptr), *toff = static_cast<unsigned *>(ws.tile_off.ptr);
-        int blocks_per_sm = 0;
-        CUDA_TRY(tile_build_configure(p, &blocks_per_sm));
+        const int blocks_per_sm = tile_blocks_per_sm(ctx, p);
         if (blocks_per_sm < 1) return fail("tile kernel does not fit: %zu bytes of shared memory", tile_smem_bytes(p));
         timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, nullptr, s); });
         timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
@@ -1070,7 +937,6 @@ static void align_tiles_to_words(const mv3d_ctx *ctx, ViewParams *p)
     p->tile_cells = pick;
     p->tile_magic = tile_magic_for(pick);
     p->tiles_per_frame = (int)((cells + pick - 1) / pick);
-    apply_pipe(ctx, p);
 }
 
 static int check_filter_args(const char *who, mv3d_ctx *ctx, int batch, float *top_dev, int mode, int *keep_dev,
@@ -1094,7 +960,7 @@ extern "C" int mv3d_encode_filter_batch_dev(mv3d_ctx *ctx, const float *points_d
     if (check_filter_args(who, ctx, batch, top_dev, mode, keep_dev, count_dev)) return -1;
     ViewParams p;
     const int strat = resolve_for_batch(ctx, tp, strategy, batch);
-    if (make_params(ctx, tp, fp, true, front_dev != nullptr, semantics, strat, &p)) return -1;
+    if (make_params(ctx, tp, fp, true, front_dev != nullptr, semantics, &p)) return -1;
     if (anchor_check_view(who, batch, p.xn, p.yn, p.planes)) return -1;
     if (batch == 0) return 0;
     std::lock_guard<std::mutex> lock(ctx->mu);
@@ -1313,9 +1179,46 @@ extern "C" int mv3d_debug_expand_split(float *dst, size_t cells, int planes, con
     return 0;
 }
 
+// Diagnostic (no GPU needed): the rate at which `threads` host threads of this library's pool zero-fill `bytes` of
+// fresh memory with streaming stores -- the ceiling of ANY implementation that has to write the caller's dense tensor
+// through the CPU. bench.py reports it beside the end-to-end figure. Best of `reps` passes, GB/s; < 0 on failure.
+extern "C" double mv3d_debug_host_fill_gbs(size_t bytes, int threads, int reps, int pin_share_index, int pin_sharers)
+{
+    if (bytes < 4096 || threads < 1 || reps < 1) { fail("mv3d_debug_host_fill_gbs: bad arguments"); return -1.0; }
+    void *raw = nullptr;
+    if (posix_memalign(&raw, 4096, bytes) != 0) { fail("mv3d_debug_host_fill_gbs: out of memory"); return -1.0; }
+    std::vector<int> cpus;
+    if (pin_sharers > 0) cpus = host_cpu_share(pin_share_index, pin_sharers);
+    HostPool pool(threads, cpus);
+    zero_fill(pool, static_cast<float *>(raw), bytes / 4);  // first touch: page faults, not bandwidth
+    double best = 0.0;
+    for (int r = 0; r < reps; r++) {
+        const auto t0 = std::chrono::steady_clock::now();
+        zero_fill(pool, static_cast<float *>(raw), bytes / 4);
+        const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+        if (sec > 0 && (double)bytes / sec / 1e9 > best) best = (double)bytes / sec / 1e9;
+    }
+    free(raw);
+    return best;
+}
+
 // ------------------------------------------------------------------------------------------------
 // the reference symbols
 // ------------------------------------------------------------------------------------------------
+// The reference routines return void and cannot fail; these can (no GPU, out of memory, sizes the CUDA path does not
+// take). A failure zeroes the outputs, prints one line on stderr and leaves the message in mv3d_last_error() --
+// and with MV3D_STRICT=1 in the environment it aborts the process instead of handing zeros to a caller that cannot see
+// the difference (the reference's unmodified ctypes wrappers ignore everything but the buffers).
+static void reference_symbol_failed(const char *who)
+{
+    fprintf(stderr, "libmv3d_encode: %s failed: %s\n", who, g_error);
+    const char *strict = getenv("MV3D_STRICT");
+    if (strict && atoi(strict) != 0) {
+        fprintf(stderr, "libmv3d_encode: MV3D_STRICT is set, aborting\n");
+        abort();
+    }
+}
+
 static std::mutex g_default_mu;
 static mv3d_ctx *g_default_ctx = nullptr;
 
@@ -1350,7 +1253,7 @@ extern "C" void createTopMaps(const void *raw_data, int num, const void *top_dat
                                           MV3D_SEM_TOP, MV3D_STRATEGY_AUTO)
                  : -1;
     if (rc) {
-        fprintf(stderr, "libmv3d_encode: createTopMaps failed: %s\n", g_error);
+        reference_symbol_failed("createTopMaps");
         if (X_SIZE > 0 && Y_SIZE > 0 && Z_SIZE >= 0)
             zero_host(const_cast<void *>(top_data), (double)X_SIZE * Y_SIZE * (Z_SIZE + 2));
     }
@@ -1375,7 +1278,7 @@ extern "C" void createTopAndFrontMaps(const void *raw_data, int num, const void 
                                           MV3D_SEM_TOPFRONT, MV3D_STRATEGY_AUTO)
                  : -1;
     if (rc) {
-        fprintf(stderr, "libmv3d_encode: createTopAndFrontMaps failed: %s\n", g_error);
+        reference_symbol_failed("createTopAndFrontMaps");
         if (X_SIZE > 0 && Y_SIZE > 0 && Z_SIZE >= 0)
             zero_host(const_cast<void *>(top_data), (double)X_SIZE * Y_SIZE * (Z_SIZE + 2));
         // a caller that hands over non-integral sizes allocated for their integer parts at most: never zero more

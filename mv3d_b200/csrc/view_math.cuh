@@ -28,11 +28,6 @@ struct ViewParams {
     // output tiling (tile strategy): a tile is tile_cells consecutive output cells = one contiguous chunk
     int tile_cells, tiles_per_frame;
     unsigned long long tile_magic; // ceil(2^48 / tile_cells) << 16: cell / tile_cells == umul64hi(cell, tile_magic), see tile_of()
-    int store_mode;               // how the tile kernel writes a tile: see TileStore in encode_kernels.cu
-    // pipelined tile kernel (tile_pipe_kernel): 0 groups = the one-tile-per-CTA kernel
-    int pipe_groups, pipe_group_threads;  // tile images / builder groups per CTA, threads per group (multiple of 32)
-    int pipe_chunk, pipe_pending;         // bytes per bulk store of the store warp, bulk stores it leaves unread
-    int pipe_grid;                        // CTAs of the pipelined kernel = SMs of the device
     // front view
     float z_span;                 // z_MAX - z_MIN, rounded to float [TF:185]
     float rad_to_deg;             // (float)(180/3.141596) [TF:36]

@@ -86,10 +86,18 @@ class ViewEncoder:
         assert points.is_cuda and points.dtype == torch.float32 and points.is_contiguous()
         offs = np.ascontiguousarray(offsets, dtype=np.int32)
         batch = len(offs) - 1
+        _check_offsets(offs, points.numel() // 4)
         if want_top and top_out is None:
             top_out = torch.empty((batch, *top.shape), dtype=torch.float32, device=points.device)
         if front is not None and front_out is None:
             front_out = torch.empty((batch, *front.shape), dtype=torch.float32, device=points.device)
+        for name, out, shape in (("top_out", top_out if want_top else None, top.shape),
+                                 ("front_out", front_out, front.shape if front is not None else None)):
+            if out is not None:  # a wrong buffer is an out-of-bounds device write, not an exception: refuse it here
+                if not (out.is_cuda and out.device == points.device and out.dtype == torch.float32 and out.is_contiguous()):
+                    raise ValueError(f"{name} must be a contiguous float32 CUDA tensor on {points.device}")
+                if tuple(out.shape) != (batch, *shape):
+                    raise ValueError(f"{name} has shape {tuple(out.shape)}, expected {(batch, *shape)}")
         if stream is None:
             stream = torch.cuda.current_stream(points.device).cuda_stream
         rc = self._lib.mv3d_encode_batch_dev(
@@ -143,10 +151,18 @@ class ViewEncoder:
         offs = np.ascontiguousarray(offsets, dtype=np.int32)
         batch = len(offs) - 1
         assert points.dtype == np.float32 and points.flags["C_CONTIGUOUS"]
+        _check_offsets(offs, points.size // 4)
         if want_top and top_out is None:
             top_out = np.empty((batch, *top.shape), dtype=np.float32)
         if front is not None and front_out is None:
             front_out = np.empty((batch, *front.shape), dtype=np.float32)
+        for name, out, shape in (("top_out", top_out if want_top else None, top.shape),
+                                 ("front_out", front_out, front.shape if front is not None else None)):
+            if out is not None:
+                if not (isinstance(out, np.ndarray) and out.dtype == np.float32 and out.flags["C_CONTIGUOUS"] and out.flags["WRITEABLE"]):
+                    raise ValueError(f"{name} must be a writable C-contiguous float32 numpy array")
+                if out.shape != (batch, *shape):
+                    raise ValueError(f"{name} has shape {out.shape}, expected {(batch, *shape)}")
         rc = self._lib.mv3d_encode_batch_host(
             self._ctx, points.ctypes.data, offs.ctypes.data_as(ctypes.POINTER(ctypes.c_int)), batch,
             top_out.ctypes.data if (want_top and top_out is not None) else None,
@@ -156,6 +172,16 @@ class ViewEncoder:
         if rc != 0:
             raise RuntimeError("mv3d_encode_batch_host: " + _lib.last_error())
         return (top_out if want_top else None), front_out
+
+
+def _check_offsets(offs: np.ndarray, n_points: int) -> None:
+    """The library trusts `offsets` against the point buffer; a mismatch would be an out-of-bounds read."""
+    if offs.ndim != 1 or offs.size < 1:
+        raise ValueError("offsets must be a 1-d array of batch + 1 entries")
+    if offs[0] < 0 or (np.diff(offs) < 0).any():
+        raise ValueError("offsets must be non-negative and non-decreasing")
+    if int(offs[-1]) > n_points:
+        raise ValueError(f"offsets end at point {int(offs[-1])}, the point buffer holds {n_points}")
 
 
 def pinned_empty(shape, dtype=np.float32) -> np.ndarray:

@@ -114,4 +114,42 @@ class SweepStream:
                    slot.front[:nb] if self.front_p is not None else None)
 
 
-__all__ = ["SweepStream"]
+class ResidentStream:
+    """BASELINE.json config 4 as SURVEY.md 8(d) specifies it: the sweeps of this rank are ALREADY in its HBM (packed
+    batches), the encoded tensors go to a ring of `depth` output slots and never leave the device; the consumer sees
+    each batch's slot before the ring comes round to it again. `for k, top, front in ResidentStream(...).run(batches)`
+    with `batches` an iterable of `(points_dev [n, 4], offsets_host [nb + 1])`.
+
+    Everything is enqueued on the current CUDA stream, so a consumer that enqueues its own work there (e.g.
+    `ViewEncoder.frame_checksums`) is ordered before the slot is reused without any host synchronisation.
+    """
+
+    def __init__(self, device: int, top: TopParams, front: Optional[FrontParams], batch: int = 64, depth: int = 2,
+                 semantics: str = "topfront", strategy: str = "auto"):
+        import torch
+        assert depth >= 1 and batch >= 1
+        self.device = torch.device("cuda", device)
+        self.top_p, self.front_p, self.batch = top, front, batch
+        self.enc = ViewEncoder(device, semantics=semantics, strategy=strategy)
+        self.ring = [(torch.empty((batch, *top.shape), dtype=torch.float32, device=self.device),
+                      torch.empty((batch, *front.shape), dtype=torch.float32, device=self.device)
+                      if front is not None else None) for _ in range(depth)]
+
+    def close(self):
+        self.enc.close()
+
+    @property
+    def launch_count(self) -> int:
+        return self.enc.launch_count
+
+    def run(self, batches) -> Iterator[Tuple[int, object, object]]:
+        for k, (d_pts, offs) in enumerate(batches):
+            nb = len(offs) - 1
+            assert nb <= self.batch, f"batch {k} holds {nb} sweeps, the ring slots {self.batch}"
+            top, front = self.ring[k % len(self.ring)]
+            self.enc.encode_device(d_pts, offs, self.top_p, self.front_p, top_out=top[:nb],
+                                   front_out=front[:nb] if front is not None else None)
+            yield k, top[:nb], (front[:nb] if front is not None else None)
+
+
+__all__ = ["SweepStream", "ResidentStream"]

@@ -24,3 +24,10 @@ def oracle_mod():
 def encoder_lib():
     from mv3d_b200 import _lib
     return _lib.load_library()
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+    assert torch.cuda.is_available(), "these tests need a CUDA device"
+    return torch

@@ -103,3 +103,33 @@ def test_reference_wrappers_bind_this_library(encoder_lib, capfd):
         assert b"no CPU fallback" in encoder_lib.mv3d_last_error()
     else:
         assert out.any() and out2.any()  # a GPU is present: the views were encoded
+
+
+def test_strict_mode_aborts_instead_of_returning_zeros():
+    """MV3D_STRICT=1: a failing reference symbol (here: no GPU / bad sizes) must not hand zeros to a caller that cannot
+    tell them from a result -- it aborts (round-1 advisor finding). Without the switch it zero-fills and reports."""
+    import sys
+    code = (
+        "import ctypes, numpy as np, sys\n"
+        f"sys.path.insert(0, {ROOT!r})\n"
+        "from mv3d_b200 import _lib\n"
+        "lib = _lib.load_library()\n"
+        "F, I = ctypes.c_float, ctypes.c_int\n"
+        "pts = np.zeros((4, 4), np.float32); top = np.ones((2, 2, 3), np.float32); front = np.ones((4, 4, 3), np.float32)\n"
+        "lib.createTopAndFrontMaps(ctypes.c_void_p(pts.ctypes.data), I(4), ctypes.c_void_p(top.ctypes.data),\n"
+        "    ctypes.c_void_p(front.ctypes.data), F(0), F(2), F(0), F(2), F(0), F(1), F(1), F(1), F(1), I(2), I(2), I(1),\n"
+        "    F(-1), F(1), F(-1), F(1), F(0.5), F(0.5), F(4.5), F(4), F(3))\n"  # C_SIZE = 4.5: refused with or without a GPU
+        "print('returned', float(top.sum()), float(front.sum()))\n")
+    env = dict(os.environ, MV3D_STRICT="1")
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
+    assert res.returncode != 0 and "MV3D_STRICT is set, aborting" in res.stderr and "returned" not in res.stdout
+    env.pop("MV3D_STRICT")
+    res = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, env=env)
+    assert res.returncode == 0 and "returned 0.0 0.0" in res.stdout and "createTopAndFrontMaps failed" in res.stderr
+
+
+def test_host_fill_probe(encoder_lib):
+    """The diagnostic bench.py prints beside the end-to-end figure runs without a GPU and gives a plausible rate."""
+    gbs = encoder_lib.mv3d_debug_host_fill_gbs(64 << 20, 2, 2, 0, 0)
+    assert 0.5 < gbs < 5000.0
+    assert encoder_lib.mv3d_debug_host_fill_gbs(16, 2, 2, 0, 0) < 0

@@ -97,3 +97,65 @@ def test_reference_symbol_with_bad_sizes_zero_fills(oracle_mod):
     et, ef = oracle_mod.top_and_front_maps(s, SMALL, SMALL_FRONT)
     assert np.array_equal(top, et) and np.array_equal(front, ef)
     assert _lib.last_error() == ""
+
+
+@pytest.mark.parametrize("xn,yn", [(0, 24), (20, 0), (0, 0)])
+def test_empty_grid_is_a_no_op(oracle_mod, xn, yn):
+    """X_SIZE = 0 or Y_SIZE = 0: the reference's loops simply do not run (LidarTopPreprocess.c:59-84,112). Here the tile
+    count of an empty grid must not divide by zero (round-1 advisor finding); the front view of such a call is all
+    zeros too, because nothing passes the bird's-eye-view gate."""
+    import torch
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.pytwin import PyTwinEncoder
+    from mv3d_b200.params import PYTWIN_KITTI, replace
+    from mv3d_b200.ver3 import createTopAndFrontMaps, createTopMaps
+    top = TopParams(0.0, 4.0, -2.4, 2.4, -1.0, 1.0, 0.2, 0.2, 0.4, xn, yn, 5)
+    s = hdl64_sweep(3)[:3000]
+    pts, offs = pack_sweeps([s, s[:10]])
+    d = torch.from_numpy(pts).cuda()
+    for strategy in ("auto", "tile", "atomic", "sort", "patch"):
+        enc = ViewEncoder(0, strategy=strategy)
+        t, f = enc.encode_device(d, offs, top, SMALL_FRONT)
+        torch.cuda.synchronize()
+        assert t.numel() == 0 and tuple(t.shape) == (2, xn, yn, 7)
+        assert not f.any().item(), strategy
+        enc.close()
+    out = np.ones(top.shape, np.float32)
+    fo = np.ones(SMALL_FRONT.shape, np.float32)
+    createTopMaps(s, s.shape[0], out, top.as_top_paras())
+    createTopAndFrontMaps(s, s.shape[0], out, fo, top.as_top_paras(), SMALL_FRONT.as_front_paras())
+    et, ef = oracle_mod.top_and_front_maps(s, top, SMALL_FRONT)
+    assert np.array_equal(fo, ef) and not fo.any()
+    py = PyTwinEncoder(0)  # the Python-twin parameters derive their grid from the ranges: (-0.05 // 0.1) + 1 = 0 rows
+    empty = replace(PYTWIN_KITTI, x_max=PYTWIN_KITTI.x_min - 0.05)
+    assert empty.xn == 0
+    ptop, pfront = py.encode_device(d, offs, empty)
+    torch.cuda.synchronize()
+    assert ptop.numel() == 0 and not pfront.any().item()  # nothing survives the crop 0 < x < -0.05 either
+    py.close()
+
+
+def test_wrapper_refuses_mismatched_buffers():
+    """The Python mirror checks what the C ABI cannot: offsets against the point buffer, output shape / dtype / device.
+    A mismatch is an exception here instead of an out-of-bounds access on the device (round-1 advisor finding)."""
+    import torch
+    from mv3d_b200.encoder import ViewEncoder
+    enc = ViewEncoder(0)
+    d = torch.zeros((100, 4), device="cuda")
+    with pytest.raises(ValueError, match="point buffer holds"):
+        enc.encode_device(d, np.array([0, 101], np.int32), SMALL, SMALL_FRONT)
+    with pytest.raises(ValueError, match="shape"):
+        enc.encode_device(d, np.array([0, 100], np.int32), SMALL, SMALL_FRONT, top_out=torch.zeros((1, 20, 24, 6), device="cuda"))
+    with pytest.raises(ValueError, match="float32 CUDA tensor"):
+        enc.encode_device(d, np.array([0, 100], np.int32), SMALL, SMALL_FRONT, top_out=torch.zeros((1, *SMALL.shape)))
+    with pytest.raises(ValueError, match="float32 CUDA tensor"):
+        enc.encode_device(d, np.array([0, 100], np.int32), SMALL, SMALL_FRONT,
+                          front_out=torch.zeros((1, *SMALL_FRONT.shape), device="cuda", dtype=torch.float64))
+    h = np.zeros((100, 4), np.float32)
+    with pytest.raises(ValueError, match="point buffer holds"):
+        enc.encode_host(h, np.array([0, 400], np.int32), SMALL, SMALL_FRONT)
+    with pytest.raises(ValueError, match="shape"):
+        enc.encode_host(h, np.array([0, 100], np.int32), SMALL, SMALL_FRONT, top_out=np.zeros((2, *SMALL.shape), np.float32))
+    with pytest.raises(ValueError, match="float32 numpy"):
+        enc.encode_host(h, np.array([0, 100], np.int32), SMALL, SMALL_FRONT, top_out=np.zeros((1, *SMALL.shape), np.float64))
+    enc.close()
