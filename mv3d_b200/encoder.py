@@ -178,10 +178,9 @@ def _check_offsets(offs: np.ndarray, n_points: int) -> None:
     """The library trusts `offsets` against the point buffer; a mismatch would be an out-of-bounds read."""
     if offs.ndim != 1 or offs.size < 1:
         raise ValueError("offsets must be a 1-d array of batch + 1 entries")
-    if offs[0] < 0 or (np.diff(offs) < 0).any():
-        raise ValueError("offsets must be non-negative and non-decreasing")
-    if int(offs[-1]) > n_points:
-        raise ValueError(f"offsets end at point {int(offs[-1])}, the point buffer holds {n_points}")
+    # order / sign errors are the library's to report (check_offsets in mv3d_abi.cu); what it cannot see is the buffer
+    if int(offs.max()) > n_points:
+        raise ValueError(f"offsets reach point {int(offs.max())}, the point buffer holds {n_points}")
 
 
 def pinned_empty(shape, dtype=np.float32) -> np.ndarray:

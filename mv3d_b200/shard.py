@@ -49,32 +49,45 @@ def interleave(per_rank: Sequence[Sequence], num_frames: int) -> list:
 
 
 def gather_frames(local, num_frames: int, dst: int = 0, group=None):
-    """Deliver every rank's encoded frames to `dst` and put them back in stream order.
+    """Deliver every rank's encoded frames to `dst`, in stream order, without a staging copy.
 
     `local`: tensor `[n_local, ...]` holding this rank's frames (`frames_of(rank, world, num_frames)`), on the
     device the process group works with (CUDA for nccl, CPU for gloo). Returns `[num_frames, ...]` on `dst`,
-    None elsewhere. Ranks with one frame fewer are padded for the exchange; the padding is dropped.
+    None elsewhere.
+
+    Frame f of the stream lives at `local[f // world]` on rank `f % world`, so on `dst` every frame is received
+    straight into its final place `out[f]` (one point-to-point receive per frame, all posted as one batch: NCCL runs
+    them as a single grouped operation over NVLink); the only local copy is dst's own share. Peak memory on `dst` is
+    the result plus its own share -- not the 2x of a gather into per-rank buffers followed by an interleaving pass.
     """
-    import torch
     import torch.distributed as dist
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     sizes = shard_sizes(world, num_frames)
     assert local.shape[0] == sizes[rank], f"rank {rank} holds {local.shape[0]} frames, expected {sizes[rank]}"
-    most = max(sizes) if sizes else 0
-    if most == 0:
+    if num_frames == 0:
         return local.new_empty((0, *local.shape[1:])) if rank == dst else None
-    send = local
-    if local.shape[0] < most:
-        send = local.new_zeros((most, *local.shape[1:]))
-        send[: local.shape[0]] = local
-    send = send.contiguous()
-    recv = [torch.empty_like(send) for _ in range(world)] if rank == dst else None
-    dist.gather(send, recv, dst=dst, group=group)
-    if rank != dst:
-        return None
-    out = local.new_empty((num_frames, *local.shape[1:]))
-    for r in range(world):
-        out[r::world] = recv[r][: sizes[r]]  # frames r, r+world, ... in one strided copy
+    local = local.contiguous()
+
+    def peer(r):  # batch_isend_irecv takes global ranks
+        return dist.get_global_rank(group, r) if group is not None else r
+
+    ops = []
+    out = None
+    if rank == dst:
+        out = local.new_empty((num_frames, *local.shape[1:]))
+        for r in range(world):
+            if r == dst:
+                continue
+            for j in range(sizes[r]):
+                ops.append(dist.P2POp(dist.irecv, out[r + j * world], peer(r), group))
+    else:
+        for j in range(sizes[rank]):
+            ops.append(dist.P2POp(dist.isend, local[j], peer(dst), group))
+    reqs = dist.batch_isend_irecv(ops) if ops else []
+    if rank == dst and sizes[dst]:
+        out[dst::world] = local  # own share: one strided copy, overlaps the transfers
+    for q in reqs:
+        q.wait()
     return out
 
 
