@@ -347,9 +347,59 @@ def config4_stream(rank, world, device, total_frames, peak):
     torch.cuda.synchronize()
     sec = e0.elapsed_time(e1) * 1e-3
     launches = stream.launch_count + chk.launch_count - launches0
+    gather = None
+    if world > 1:
+        # the optional delivery of encoded tensors to the consumer rank (NCCL over NVLink; off the encode path):
+        # every rank hands over the 64 bird's-eye views of its last ring slot, rank 0 receives them in stream order
+        import torch.distributed as dist
+        local = stream.ring[0][0]
+        n_g = world * BATCH
+        shard.gather_frames(local[:1].contiguous(), world, dst=0)  # communicator warm-up (P2P channels)
+        torch.cuda.synchronize()
+        dist.barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        full = shard.gather_frames(local, n_g, dst=0)
+        g1.record()
+        torch.cuda.synchronize()
+        gsec = g0.elapsed_time(g1) * 1e-3
+        nbytes = n_g * local[0].numel() * 4
+        ok = None
+        if rank == 0:  # frame f of the gathered stream is rank (f % world)'s frame f // world; rank 0's own are local
+            ok = bool(torch.equal(full[0], local[0]) and torch.equal(full[world * 3], local[3]))
+        gather = {"frames": n_g, "bytes": nbytes, "seconds": gsec, "ok": ok}
+        del full
     stream.close()
     chk.close()
-    return {"frames_this_rank": n, "seconds": sec, "gpu_launches": launches, "total_frames": total_frames}
+    return {"frames_this_rank": n, "seconds": sec, "gpu_launches": launches, "total_frames": total_frames, "gather": gather}
+
+
+def reference_gpu_kernel(device, frames=3):
+    """The reference's own GPU encoder (front_top_kernel.cu, unmodified, sm_100a cubin built by oracle/Makefile) on
+    this GPU with the reference's host steps and launch shapes (tests/ref_front_top_kernel.py restates
+    front_top_preprocess.py:29-193 as bench infrastructure): ms per frame, beside the Python-twin mode it pairs with."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    try:
+        import ref_front_top_kernel as ref
+        if not ref.available():
+            return {"unavailable": "oracle/_ref/front_top_kernel.cubin or cuda-python missing"}
+        from mv3d_b200.params import PYTWIN_KITTI
+        from mv3d_b200.sweeps import hdl64_sweep
+        sweeps = [hdl64_sweep(100 + f) for f in range(frames)]
+        ref.lidar_to_top_cuda(sweeps[0], PYTWIN_KITTI)  # module load, context
+        timing = {}
+        t0 = time.perf_counter()
+        for s in sweeps:
+            ref.lidar_to_top_cuda(s, PYTWIN_KITTI, timing)
+            ref.lidar_to_front_cuda(s, PYTWIN_KITTI, timing)
+        sec = (time.perf_counter() - t0) / frames
+        return {"value": 1.0 / sec, "unit": "sweeps/s", "ms_per_frame": sec * 1e3,
+                "ms_per_frame_parts": {k.replace("_s", "_ms"): v / frames * 1e3 for k, v in timing.items()},
+                "what": "lidar_to_top_cuda + lidar_to_front_cuda of the reference (one frame per call: numpy crop / "
+                        "voxelise / lexsort, upload, its four kernels -- three of them single-threaded loops over all "
+                        "points --, download), BEV 800x600x27 + FV 1500x100x3; compare with widened_rows.python_twin_encode"}
+    except Exception as e:  # bench infrastructure must never take the line down
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
 
 
 def widened_rows(d_pts, offs, device, steps):
@@ -552,9 +602,19 @@ def run_ours(args):
             "frac_of_n_gpu_peak": args.config4_frames * ab["total"] / c4_s / 1e9 / (peak * world),
             "what": "configs[3]: frame-sharded stream (frame i -> rank i mod N, no collective), inputs pre-staged in HBM, "
                     "ring of two output slots, per-frame checksum kernel as the consumer (reads every output byte once)"}
+        if c4.get("gather"):
+            g = c4["gather"]
+            gsec = max_over_ranks(g["seconds"])
+            also["config4_gather_to_rank0"] = {
+                "frames": g["frames"], "bytes": g["bytes"], "seconds": gsec, "frames_per_s": g["frames"] / gsec,
+                "ingress_GBps": g["bytes"] * (world - 1) / world / gsec / 1e9, "checked": g["ok"],
+                "what": "optional NCCL delivery of 64 encoded BEV tensors per rank to rank 0 (shard.gather_frames: one "
+                        "receive per frame straight into its place in stream order, no staging buffer); ingress = bytes "
+                        "arriving at rank 0 over NVLink per second"}
         if world == 1:
             also.update(other_configs(local_rank, max(3, min(args.steps, 10)), peak))
             also["widened_rows"] = widened_rows(d_pts, offs, local_rank, max(3, min(args.steps, 10)))
+            also["reference_gpu_kernel"] = reference_gpu_kernel(local_rank)
 
     if rank != 0:
         if world > 1:
