@@ -888,7 +888,7 @@ static inline int point_blocks(int max_points, int items = 1)
 }
 
 // CTAs per sweep for the grid-stride point passes of a batch: enough to cover the longest sweep, but no more than
-// MV3D_POINT_WAVES (default 2) waves of resident CTAs over the whole batch. A CTA that lives for one round of 512
+// MV3D_POINT_WAVES (default 4) waves of resident CTAs over the whole batch. A CTA that lives for one round of 512
 // points spends a quarter of its instructions on its prologue (ncu, profiles/r2b_*): with 64 sweeps per launch each
 // CTA now loops ~6 times over its sweep instead.
 static int sm_count_cached()
@@ -902,7 +902,7 @@ static int sm_count_cached()
 }
 static inline int point_blocks_batched(int max_points, int items, int batch, int ctas_per_sm)
 {
-    static const int waves = [] { const char *e = getenv("MV3D_POINT_WAVES"); const int w = e ? atoi(e) : 2; return w < 1 ? 1 << 20 : w; }();
+    static const int waves = [] { const char *e = getenv("MV3D_POINT_WAVES"); const int w = e ? atoi(e) : 4; return w < 1 ? 1 << 20 : w; }();
     const int cover = point_blocks(max_points, items);
     long long cap = ((long long)sm_count_cached() * ctas_per_sm * waves + batch - 1) / (batch > 0 ? batch : 1);
     if (cap < 1) cap = 1;
