@@ -201,6 +201,22 @@ int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, const unsign
  * of the finished values). */
 int mv3d_debug_expand_split(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n, int threads);
 
+/* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * The front view [batch][R][C][F] of `batch` device-resident sweeps, exactly as mv3d_encode_batch_dev(ctx, ..., top_dev
+ * = NULL, front_dev, ...) writes it (bit-identical: same arithmetic, the bird's-eye-view gate still applies), but with
+ * NO allocation and no context: the per-pixel scratch ("last point in input order wins") lives in a static device
+ * array of MV3D_NOALLOC_MAX_PIXELS 32-bit words (1 MiB, held by every GPU that loads the library until exit). The call
+ * makes no cudaMalloc / cudaFree / allocating library call; it enqueues one memset and two kernels on `stream` of the
+ * CURRENT device (the first call on a device also looks the array's address up: make that call outside graph capture).
+ * Limits, rejected with a message in mv3d_last_error(): batch <= 64 and batch * R * C <= MV3D_NOALLOC_MAX_PIXELS
+ * (e.g. 8 sweeps of 64 x 512); tp->flags must be 0. All calls on a GPU share the scratch: each call clears what it
+ * uses first, but calls that OVERLAP on the GPU (different streams without ordering) race -- serialise them.
+ * offsets_host as for mv3d_encode_batch_dev. Returns 0, or -1 with mv3d_last_error(). */
+#define MV3D_NOALLOC_MAX_PIXELS 262144
+int mv3d_front_view_noalloc(const float *points_dev, const int *offsets_host, int batch, float *front_dev,
+                            const mv3d_top_params *tp, const mv3d_front_params *fp, int semantics, void *stream);
+
 /* Diagnostic (no GPU needed): GB/s at which `threads` threads of the library's host pool zero-fill `bytes` of memory
  * with streaming stores (best of `reps` passes) -- the ceiling of any implementation that must write the caller's dense
  * host tensor through the CPU; bench.py prints it beside the end-to-end figure. pin_sharers > 0 pins the threads to

@@ -14,7 +14,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(_HERE, "libmv3d_encode.so")
 SOURCES = ["encode_kernels.cu", "sort_strategy.cu", "mv3d_abi.cu", "host_expand.cu", "anchor_kernels.cu", "anchor_abi.cu",
-           "sweep_io.cu"]
+           "sweep_io.cu", "noalloc_front.cu"]
 HEADERS = ["encode_kernels.h", "view_math.cuh", "host_expand.h", "ctx.h", "anchor_kernels.h",
            os.path.join("..", "..", "include", "mv3d_encode.h"), os.path.join("..", "..", "include", "mv3d_anchors.h"),
            os.path.join("..", "..", "include", "mv3d_io.h")]
@@ -85,7 +85,7 @@ EXPORTED_SYMBOLS = (
     "mv3d_encode_batch_dev", "mv3d_encode_batch_host", "mv3d_host_alloc", "mv3d_host_free",
     "mv3d_ctx_launch_count", "mv3d_resolve_strategy", "mv3d_version",
     "mv3d_ctx_set_profiling", "mv3d_kernel_count", "mv3d_kernel_name", "mv3d_ctx_kernel_times",
-    "mv3d_debug_host_fill_gbs", "mv3d_debug_point_keys", "mv3d_debug_expand_compact", "mv3d_debug_expand_split", "mv3d_ctx_transfer_bytes",
+    "mv3d_front_view_noalloc", "mv3d_debug_host_fill_gbs", "mv3d_debug_point_keys", "mv3d_debug_expand_compact", "mv3d_debug_expand_split", "mv3d_ctx_transfer_bytes",
     "mv3d_pytwin_encode_batch_dev", "mv3d_pytwin_encode_batch_host", "mv3d_debug_atan2f", "mv3d_frame_checksums_dev",
     "mv3d_ctx_set_anchors", "mv3d_remove_empty_anchor_dev", "mv3d_remove_empty_anchor_host",
     "mv3d_encode_filter_batch_dev", "mv3d_pytwin_encode_filter_batch_dev",
@@ -138,6 +138,8 @@ def load_library() -> ctypes.CDLL:
     lib.mv3d_debug_atan2f.argtypes = [vp, vp, vp, vp, ci, vp]
     lib.mv3d_frame_checksums_dev.argtypes = [vp, vp, ci, ctypes.c_longlong, vp, vp]
     lib.mv3d_ctx_transfer_bytes.argtypes = [vp, ctypes.POINTER(ctypes.c_ulonglong), ctypes.POINTER(ctypes.c_ulonglong), ci]
+    lib.mv3d_front_view_noalloc.argtypes = [vp, ctypes.POINTER(ci), ci, vp, ctypes.POINTER(TopParamsC),
+                                            ctypes.POINTER(FrontParamsC), ci, vp]
     lib.mv3d_debug_host_fill_gbs.argtypes = [ctypes.c_size_t, ci, ci, ci, ci]
     lib.mv3d_debug_host_fill_gbs.restype = ctypes.c_double
     lib.mv3d_debug_expand_compact.argtypes = [vp, ctypes.c_size_t, ci, vp, ctypes.c_uint, ci]
