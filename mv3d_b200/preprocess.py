@@ -30,18 +30,37 @@ def _tag(fname: str) -> str:
 
 def preprocess_files(files: Sequence[str], top_dir: Optional[str], front_dir: Optional[str],
                      params: PyTwinParams, batch: int = 16, device: int = 0, io_threads: int = 0,
-                     compressed_top: bool = False, encoder=None) -> dict:
+                     compressed_top: bool = False, encoder=None, overwrite: bool = True) -> dict:
     """Encode `files` and write `<top_dir>/<tag>.npy`, `<front_dir>/<tag>.npy` (either directory may be None).
     `compressed_top`: write the bird's-eye views as `np.savez_compressed(path, top_view=top)` archives
-    (`<tag>.npy.npz`, the format of `src/data.py:521`) instead. Returns counters and timings."""
+    (`<tag>.npy.npz`, the format of `src/data.py:521`) instead.
+    `overwrite=False` is the reference's resume (`generate_top_view(..., overwrite=False)`, `src/data.py:497-500`): a
+    frame whose requested output files all exist already is neither read nor encoded nor rewritten. (The reference
+    tests for `<n>.npy` although `np.savez_compressed` writes `<n>.npy.npz`, so its own check never fires for the
+    compressed form; here the file that is actually written is the one tested.)
+    Returns counters and timings (`skipped` = frames left alone)."""
     from .pytwin import PyTwinEncoder
     own = encoder is None
     enc = encoder or PyTwinEncoder(device)
     for d in (top_dir, front_dir):
         if d:
             os.makedirs(d, exist_ok=True)                # `:34-35`
+    def outputs(fname):
+        tag, paths = _tag(fname), []
+        if top_dir:
+            paths.append(os.path.join(top_dir, tag + (".npy.npz" if compressed_top else ".npy")))
+        if front_dir:
+            paths.append(os.path.join(front_dir, tag + ".npy"))
+        return paths
+
+    files = list(files)
+    skipped = 0
+    if not overwrite:
+        todo = [f for f in files if not all(os.path.isfile(q) for q in outputs(f))]
+        skipped = len(files) - len(todo)
+        files = todo
     groups = [list(files[i:i + batch]) for i in range(0, len(files), batch)]
-    stats = {"frames": 0, "points": 0, "read_s": 0.0, "encode_s": 0.0, "write_s": 0.0}
+    stats = {"frames": 0, "points": 0, "read_s": 0.0, "encode_s": 0.0, "write_s": 0.0, "skipped": skipped}
     nxt = {}
 
     def read(group, slot):
@@ -135,9 +154,11 @@ def main(argv=None) -> int:
     ap.add_argument("--batch", type=int, default=16)
     ap.add_argument("--device", type=int, default=0)
     ap.add_argument("--io-threads", type=int, default=0)
+    ap.add_argument("--no-overwrite", action="store_true",
+                    help="resume: skip frames whose output files exist (the reference's overwrite=False, src/data.py:497-500)")
     args = ap.parse_args(argv)
     stats = preprocess_directory(os.path.expanduser(args.split_dir), PYTWIN_PRESETS[args.preset], batch=args.batch,
-                                 device=args.device, io_threads=args.io_threads)
+                                 device=args.device, io_threads=args.io_threads, overwrite=not args.no_overwrite)
     print(stats)
     return 0
 

@@ -79,6 +79,22 @@ def test_preprocess_run_writes_numpys_files(kitti_tree, pytwin, tmp_path):
             buf = io.BytesIO()
             np.save(buf, want)
             assert open(os.path.join(d, t + ".npy"), "rb").read() == buf.getvalue(), (d, t)
+    # resume (src/data.py:497-500, overwrite=False): only the frames with a missing output are encoded again
+    tags = sorted(sweeps)
+    os.unlink(os.path.join(front_dir, tags[1] + ".npy"))
+    os.unlink(os.path.join(top_dir, tags[3] + ".npy"))
+    marker = os.path.join(top_dir, tags[0] + ".npy")
+    open(marker, "wb").write(b"left alone")
+    stats = preprocess_files(files, top_dir, front_dir, PYTWIN_KITTI, batch=2, overwrite=False)
+    assert stats["skipped"] == 3 and stats["frames"] == 2
+    assert open(marker, "rb").read() == b"left alone"
+    for t in (tags[1], tags[3]):
+        buf = io.BytesIO()
+        np.save(buf, pytwin.lidar_to_top(sweeps[t], PYTWIN_KITTI))
+        assert open(os.path.join(top_dir, t + ".npy"), "rb").read() == buf.getvalue()
+        assert os.path.isfile(os.path.join(front_dir, t + ".npy"))
+    preprocess_files([files[0]], top_dir, None, PYTWIN_KITTI)  # default overwrite=True: rewritten
+    assert open(marker, "rb").read() != b"left alone"
     # compressed archives (src/data.py:521) load back to the same tensors
     zdir = str(tmp_path / "top")
     preprocess_files(files[:2], zdir, None, PYTWIN_KITTI, batch=2, compressed_top=True)

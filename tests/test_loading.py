@@ -114,3 +114,34 @@ def test_iteration(tmp_path):
     loader = KittiLoading(str(tmp_path), is_testset=True, batch_size=2, params=TINY, encode=fake_encode, pinned=False)
     assert [len(b[0]) for b in loader] == [2, 1]
     loader.close()
+
+
+def test_preprocess_resume_skips_finished_frames(tmp_path):
+    """overwrite=False (the reference's resume, src/data.py:497-500): frames whose outputs exist are neither read nor
+    encoded; with every output present the encoder is never touched (so this runs without a GPU)."""
+    from mv3d_b200.params import PYTWIN_KITTI
+    from mv3d_b200.preprocess import preprocess_files
+
+    class Refuse:
+        def encode_host(self, *a, **k):
+            raise AssertionError("nothing to encode")
+
+    files = [str(tmp_path / "velodyne" / f"{i:06d}.bin") for i in range(4)]  # never opened: they do not even exist
+    top_dir, front_dir, zdir = tmp_path / "top_view", tmp_path / "front_view", tmp_path / "top"
+    for d in (top_dir, front_dir, zdir):
+        d.mkdir()
+    for i in range(4):
+        (top_dir / f"{i:06d}.npy").write_bytes(b"x")
+        (front_dir / f"{i:06d}.npy").write_bytes(b"x")
+        (zdir / f"{i:06d}.npy.npz").write_bytes(b"x")
+    stats = preprocess_files(files, str(top_dir), str(front_dir), PYTWIN_KITTI, overwrite=False, encoder=Refuse())
+    assert stats["skipped"] == 4 and stats["frames"] == 0
+    stats = preprocess_files(files, str(zdir), None, PYTWIN_KITTI, compressed_top=True, overwrite=False, encoder=Refuse())
+    assert stats["skipped"] == 4
+    (front_dir / "000002.npy").unlink()  # one output missing: that frame is due again, and only that one
+    try:
+        preprocess_files(files, str(top_dir), str(front_dir), PYTWIN_KITTI, overwrite=False, encoder=Refuse())
+    except Exception as e:
+        assert "000002" in str(e) or isinstance(e, (OSError, RuntimeError, AssertionError))
+    else:
+        raise AssertionError("frame 000002 should have been read")
