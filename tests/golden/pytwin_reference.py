@@ -30,13 +30,27 @@ def _extract(tree, name, inside_class=None):
     return next(n for n in body if isinstance(n, ast.FunctionDef) and n.name == name)
 
 
-def load(params):
-    """Returns (lidar_to_top, lidar_to_front_fast) of the reference, bound to `params`."""
+class _NumpyCompat:
+    """numpy as the reference's code expects it: `np.object` (removed in numpy 1.24, used at src/data.py:402)."""
+    object = object
+
+    def __getattr__(self, name):
+        import numpy
+        return getattr(numpy, name)
+
+
+def load(params, others: bool = False):
+    """Returns (lidar_to_top, lidar_to_front_fast) of the reference, bound to `params`; with `others=True` the two
+    remaining twins instead: (lidar_to_top_fast, src/data.py:369-444; Preprocess.lidar_to_front, :56-111)."""
     import numpy as np
     src = open(REFERENCE_DATA_PY).read()
     tree = ast.parse(src)
-    funcs = [_extract(tree, "filter_center_car"), _extract(tree, "lidar_to_top"),
-             _extract(tree, "lidar_to_front_fast", inside_class="Preprocess")]
+    if others:
+        funcs = [_extract(tree, "filter_center_car"), _extract(tree, "lidar_to_top_fast"),
+                 _extract(tree, "lidar_to_front", inside_class="Preprocess")]
+    else:
+        funcs = [_extract(tree, "filter_center_car"), _extract(tree, "lidar_to_top"),
+                 _extract(tree, "lidar_to_front_fast", inside_class="Preprocess")]
     module = ast.Module(body=funcs, type_ignores=[])
     cfg = types.SimpleNamespace(
         DATA_SETS_TYPE="didi2" if params.filter_center_car else "kitti",
@@ -45,10 +59,13 @@ def load(params):
         FRONT_C_OFFSET=params.front_c_offset, FRONT_R_MAX=params.front_r_max, FRONT_R_MIN=params.front_r_min,
         FRONT_C_MAX=params.front_c_max, FRONT_C_MIN=params.front_c_min, FRONT_WIDTH=params.front_width,
         FRONT_HEIGHT=params.front_height)
-    ns = {"np": np, "numpy": np, "math": math, "cfg": cfg,
+    ns = {"np": _NumpyCompat() if others else np, "numpy": np, "math": math, "cfg": cfg,
           "TOP_X_MIN": params.x_min, "TOP_X_MAX": params.x_max, "TOP_Y_MIN": params.y_min, "TOP_Y_MAX": params.y_max,
           "TOP_Z_MIN": params.z_min, "TOP_Z_MAX": params.z_max, "TOP_X_DIVISION": params.x_div,
           "TOP_Y_DIVISION": params.y_div, "TOP_Z_DIVISION": params.z_div}
     exec(compile(module, REFERENCE_DATA_PY, "exec"), ns)
+    if others:
+        front_slow = ns["lidar_to_front"]
+        return ns["lidar_to_top_fast"], (lambda lidar: front_slow(None, lidar))
     front_fast = ns["lidar_to_front_fast"]
     return ns["lidar_to_top"], (lambda lidar: front_fast(None, lidar))

@@ -103,3 +103,27 @@ def test_known_answers(pytwin):
         assert t[row, col, k.zn + 1] == lut[min(c, 31)]
         assert t[row, col, k.zn] == np.float32(0.01)
     assert lut[31] == 1.0 and abs(lut[1] - 0.2) < 1e-7
+
+
+def test_other_two_twins_are_recorded():
+    """`lidar_to_top_fast` (src/data.py:369-444) and `Preprocess.lidar_to_front` (:56-111) are on no call path of the
+    reference; tests/golden/pytwin_other_twins.py executes them and records how they relate to the pinned pair:
+    the first IS `lidar_to_top` without the x/y flip (every plane equal after flipping), the second is a different
+    image from `lidar_to_front_fast` (double `math.atan2`, running mean) and is not reproduced. Where /root/reference
+    exists the record is re-derived and must match."""
+    import json
+    here = os.path.join(os.path.dirname(__file__), "golden")
+    rec = json.load(open(os.path.join(here, "pytwin_other_twins.json")))
+    for case in rec["cases"].values():
+        assert case["top_shape_equal"] and not case["top_equal_unflipped"]
+        assert case["heights_differ_after_flip"] == case["intensity_differs_after_flip"] == case["density_differs_after_flip"] == 0
+        assert case["occupied_cells"] > 1000
+        assert case["front_shape_equal"] and case["front_pixels_differ"] > 0
+    from golden import pytwin_reference as ref
+    if not ref.available():
+        return
+    code = ("import sys, json; sys.path.insert(0, %r); import pytwin_other_twins as m; print('REC' + json.dumps(m.compare()))" % here)
+    out = subprocess.run([sys.executable, "-c", code], env={**os.environ, **ref.LIBM_ENV}, capture_output=True, text=True)
+    line = [l for l in out.stdout.splitlines() if l.startswith("REC")]
+    assert line, out.stdout + out.stderr
+    assert json.loads(line[0][3:]) == rec
