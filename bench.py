@@ -566,7 +566,7 @@ def run_ours(args):
         threads = int(os.environ.get("MV3D_HOST_THREADS", "0")) or max(2, min(16, cores // max(lws, 1)))
         pin = int(os.environ.get("MV3D_HOST_PIN", "1" if lws > 1 else "0"))
         barrier()
-        fill = _lib.load_library().mv3d_debug_host_fill_gbs(256 << 20, threads, 4, local_rank if pin else 0, lws if pin else 0)
+        fill = _lib.load_library().mv3d_debug_host_fill_gbs(256 << 20, threads, 8, local_rank if pin else 0, lws if pin else 0)
         fill_all = sum_over_ranks(max(fill, 0.0))
         e2e_value = world * BATCH * args.steps / e2e_s
         fill_used = world * result_bytes * args.steps / e2e_s / 1e9

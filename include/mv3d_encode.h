@@ -218,7 +218,7 @@ int mv3d_front_view_noalloc(const float *points_dev, const int *offsets_host, in
                             const mv3d_top_params *tp, const mv3d_front_params *fp, int semantics, void *stream);
 
 /* Diagnostic (no GPU needed): GB/s at which `threads` threads of the library's host pool zero-fill `bytes` of memory
- * with streaming stores (best of `reps` passes) -- the ceiling of any implementation that must write the caller's dense
+ * with streaming stores (mean over `reps` passes) -- the ceiling of any implementation that must write the caller's dense
  * host tensor through the CPU; bench.py prints it beside the end-to-end figure. pin_sharers > 0 pins the threads to
  * share `pin_share_index` of `pin_sharers` of this process's CPUs, as the host entry points do under torchrun.
  * Returns < 0 on failure. */

@@ -21,8 +21,14 @@
 
 namespace mv3d {
 
-constexpr int kFusedClassifyChunk = 1024;  // points per C item (two rounds of 256 threads x kPointItems)
-constexpr int kFusedBinChunk = 2048;       // points per B item
+#ifndef MV3D_FUSED_CLASSIFY_CHUNK
+#define MV3D_FUSED_CLASSIFY_CHUNK 1024
+#endif
+#ifndef MV3D_FUSED_BIN_CHUNK
+#define MV3D_FUSED_BIN_CHUNK 2048
+#endif
+constexpr int kFusedClassifyChunk = MV3D_FUSED_CLASSIFY_CHUNK;  // points per C item (rounds of 256 threads x kPointItems)
+constexpr int kFusedBinChunk = MV3D_FUSED_BIN_CHUNK;            // points per B item
 constexpr int kFusedFrontChunk = 8192;     // pixels per F item
 constexpr int kFusedLag = 3;               // stages between a sweep's classify pass and its tiles
 
@@ -237,8 +243,28 @@ __device__ __forceinline__ void fused_front(const float4 *__restrict__ pts, cons
 
 // ---- T item: build and store output tile tl of sweep f (one iteration of tile_body's loop, dense bulk-store form) ----
 // img / key / dirty: the CTA's shared-memory tile image (all-zero between tiles), winner keys and touched-cell list.
+// The head of a tile's bin, fetched one item ahead so that its L2 round trips are off the tile's critical path.
+struct TileHead {
+    unsigned beg;
+    int n;
+    uint4 q0;     // record `threadIdx.x` of the bin (if there is one)
+    bool valid;
+};
+__device__ __forceinline__ TileHead fused_tile_head(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
+                                                    const FrameOffsets &offs, const ViewParams &p, int f, int tl)
+{
+    TileHead h;
+    const unsigned *off = tile_off + (size_t)f * (p.tiles_per_frame + 1) + tl;
+    h.beg = __ldcg(off);
+    h.n = (int)(__ldcg(off + 1) - h.beg);
+    h.q0 = make_uint4(0, 0, 0, 0);
+    if ((int)threadIdx.x < h.n) h.q0 = __ldcg(binned + (size_t)offs.off[f] + h.beg + threadIdx.x);
+    h.valid = true;
+    return h;
+}
+
 template <bool kPy>
-__device__ __forceinline__ void fused_tile(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
+__device__ __forceinline__ void fused_tile(const uint4 *__restrict__ binned, const TileHead &head,
                                            const FrameOffsets &offs, const ViewParams &p, const float *__restrict__ lut,
                                            float *__restrict__ top, int f, int tl, unsigned *img,
                                            unsigned long long *key, unsigned *dirty, unsigned *ndirty_p)
@@ -247,10 +273,8 @@ __device__ __forceinline__ void fused_tile(const uint4 *__restrict__ binned, con
     constexpr int kWarps = kTileThreads / 32;
     const int T = p.tile_cells, planes = p.planes, zn = p.zn;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const unsigned *off = tile_off + (size_t)f * (p.tiles_per_frame + 1) + tl;
-    const unsigned beg = __ldcg(off);
-    const int n0 = (int)(__ldcg(off + 1) - beg);
-    const uint4 *rec0 = binned + (size_t)offs.off[f] + beg;
+    const int n0 = head.n;
+    const uint4 *rec0 = binned + (size_t)offs.off[f] + head.beg;
 
     const long long cells_total = (long long)p.xn * p.yn;
     const long long cell0 = (long long)tl * T;
@@ -288,8 +312,8 @@ __device__ __forceinline__ void fused_tile(const uint4 *__restrict__ binned, con
             atomicMax(key + local, ((unsigned long long)q.y << 32) | (unsigned long long)(0xFFFFFFFFu - q.z));
         }
     };
-    uint4 q0 = make_uint4(0, 0, 0, 0);
-    if (tid < n0) { q0 = __ldcg(rec0 + tid); accumulate(q0); }
+    const uint4 q0 = head.q0;
+    if (tid < n0) accumulate(q0);
     for (int r = tid + kTileThreads; r < n0; r += kInFlight * kTileThreads) {
         uint4 q[kInFlight];
 #pragma unroll
@@ -371,65 +395,96 @@ encode_fused_kernel(const float4 *__restrict__ pts, const __grid_constant__ Fram
     const size_t img_bytes = ((size_t)T * planes * 4 + 15) & ~(size_t)15;
     unsigned long long *key = reinterpret_cast<unsigned long long *>(smem_raw + img_bytes);
     unsigned *dirty = reinterpret_cast<unsigned *>(key + T);
-    __shared__ unsigned ndirty, ticket_s, warp_sums[33];
+    // tk[parity] = {this iteration's ticket, the next one}: thread 0 writes the other parity's pair during an
+    // iteration, so ONE barrier per item separates writers from readers. ready_tiles: sweeps below it are fully binned
+    // (checked once per sweep and CTA, not once per tile).
+    __shared__ unsigned ndirty, tk[2][2], warp_sums[33];
+    __shared__ int ready_tiles;
     const int tid = threadIdx.x;
 
     for (int w = tid; w < T * planes; w += kTileThreads) img[w] = 0u;
     for (int w = tid; w < T; w += kTileThreads) key[w] = 0ull;
-    if (tid == 0) { ndirty = 0; ticket_s = atomicAdd(sync, 1u); }
+    if (tid == 0) {
+        ndirty = 0;
+        ready_tiles = 0;
+        tk[0][0] = atomicAdd(sync, 1u);
+        tk[0][1] = atomicAdd(sync, 1u);
+    }
     fence_proxy_async_smem();
     __syncthreads();
 
     unsigned *c_done = sync + 1, *s_done = sync + 1 + plan.batch, *b_done = sync + 1 + 2 * plan.batch;
     const unsigned total = (unsigned)plan.stages * (unsigned)plan.per_stage;
     const int tpf = p.tiles_per_frame;
-    for (;;) {
-        const unsigned ticket = ticket_s;
-        __syncthreads();                                 // everyone has read the ticket ...
-        if (ticket >= total) break;
-        unsigned next_ticket = 0u;                       // ... so the next one is requested while this item runs; it
-        if (tid == 0) next_ticket = atomicAdd(sync, 1u); // stays in a register (no stall on the round trip) until the end
-        const int stage = (int)(ticket / (unsigned)plan.per_stage);
+    // ticket -> (is a tile item, sweep, index); point items are spread evenly between the tile items of a stage
+    auto decode = [&](unsigned ticket, bool &is_tile, int &stage, int &index) {
+        stage = (int)(ticket / (unsigned)plan.per_stage);
         const int slot = (int)(ticket - (unsigned)stage * (unsigned)plan.per_stage);
-        // point items are spread evenly between the tile items of a stage
         const int before = (int)(((long long)slot * plan.n_point) / plan.per_stage);
-        const bool is_point = (int)(((long long)(slot + 1) * plan.n_point) / plan.per_stage) > before;
-        if (!is_point) {
-            const int f = stage - kFusedLag, tl = slot - before;
-            if (f >= 0 && f < plan.batch && tl < tpf) {
-                fused_wait(b_done + f, (unsigned)plan.n_bin);
-                fused_tile<kPy>(binned, tile_off, offs, p, lut, top, f, tl, img, key, dirty, &ndirty);
+        is_tile = (int)(((long long)(slot + 1) * plan.n_point) / plan.per_stage) == before;
+        index = is_tile ? slot - before : before;
+    };
+    TileHead have;
+    have.valid = false;
+    for (int it = 0;; it++) {
+        const int par = it & 1;
+        const unsigned ticket = tk[par][0], ticket_next = tk[par][1];
+        if (ticket >= total) break;
+        unsigned ticket_after = 0u;  // requested now, needed at the end of the item: stays in a register meanwhile
+        if (tid == 0) ticket_after = atomicAdd(sync, 1u);
+        const int ready = ready_tiles;
+        bool is_tile, next_is_tile;
+        int stage, index, next_stage, next_index;
+        decode(ticket, is_tile, stage, index);
+        TileHead ahead;
+        ahead.valid = false;
+        if (ticket_next < total) {
+            decode(ticket_next, next_is_tile, next_stage, next_index);
+            const int nf = next_stage - kFusedLag;
+            if (next_is_tile && nf >= 0 && nf < ready && next_index < tpf)
+                ahead = fused_tile_head(binned, tile_off, offs, p, nf, next_index);
+        }
+        if (is_tile) {
+            const int f = stage - kFusedLag;
+            if (f >= 0 && f < plan.batch && index < tpf) {
+                if (f >= ready) {  // first tile of this sweep on this CTA: wait until all its points are binned
+                    fused_wait(b_done + f, (unsigned)plan.n_bin);
+                    if (tid == 0) ready_tiles = f + 1;
+                    have.valid = false;
+                }
+                if (!have.valid) have = fused_tile_head(binned, tile_off, offs, p, f, index);
+                fused_tile<kPy>(binned, have, offs, p, lut, top, f, index, img, key, dirty, &ndirty);
             }
-        } else if (before < plan.n_classify) {
-            const int f = stage;
-            if (f < plan.batch) {
-                fused_classify<kPy>(pts, offs, p, keys, tile_count, fv_winner, f, before * kFusedClassifyChunk,
-                                    (before + 1) * kFusedClassifyChunk);
-                fused_signal(c_done + f);
+        } else if (index < plan.n_classify) {
+            if (stage < plan.batch) {
+                fused_classify<kPy>(pts, offs, p, keys, tile_count, fv_winner, stage, index * kFusedClassifyChunk,
+                                    (index + 1) * kFusedClassifyChunk);
+                fused_signal(c_done + stage);
             }
-        } else if (before == plan.n_classify) {
+        } else if (index == plan.n_classify) {
             const int f = stage - 1;
             if (f >= 0 && f < plan.batch) {
                 fused_wait(c_done + f, (unsigned)plan.n_classify);
                 fused_scan(tile_count, tile_off, tpf, f, warp_sums);
                 fused_signal(s_done + f);
             }
-        } else if (before <= plan.n_classify + plan.n_bin) {
-            const int f = stage - 2, c = before - plan.n_classify - 1;
+        } else if (index <= plan.n_classify + plan.n_bin) {
+            const int f = stage - 2, c = index - plan.n_classify - 1;
             if (f >= 0 && f < plan.batch) {
                 fused_wait(s_done + f, 1u);
                 fused_bin<kPy>(pts, offs, p, keys, tile_off, binned, f, c * kFusedBinChunk, (c + 1) * kFusedBinChunk);
                 fused_signal(b_done + f);
             }
         } else {
-            const int f = stage - 2, c = before - plan.n_classify - 1 - plan.n_bin;
+            const int f = stage - 2, c = index - plan.n_classify - 1 - plan.n_bin;
             if (f >= 0 && f < plan.batch) {
                 fused_wait(c_done + f, (unsigned)plan.n_classify);
                 fused_front(pts, offs, p, fv_winner, front, f, c * kFusedFrontChunk, (c + 1) * kFusedFrontChunk);
             }
         }
-        if (tid == 0) ticket_s = next_ticket;
-        __syncthreads();  // the item is over for the whole CTA, and the next ticket is published
+        have = ahead;
+        if (tid == 0) { tk[par ^ 1][0] = ticket_next; tk[par ^ 1][1] = ticket_after; }
+        __syncthreads();  // the item is over for the whole CTA, and the next pair of tickets is published
     }
     if (tid == 0) bulk_wait_read_all();  // shared memory must outlive the last bulk read
 }

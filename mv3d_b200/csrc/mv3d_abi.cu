@@ -1206,7 +1206,7 @@ extern "C" int mv3d_debug_expand_split(float *dst, size_t cells, int planes, con
 
 // Diagnostic (no GPU needed): the rate at which `threads` host threads of this library's pool zero-fill `bytes` of
 // fresh memory with streaming stores -- the ceiling of ANY implementation that has to write the caller's dense tensor
-// through the CPU. bench.py reports it beside the end-to-end figure. Best of `reps` passes, GB/s; < 0 on failure.
+// through the CPU. bench.py reports it beside the end-to-end figure. Mean over `reps` passes, GB/s; < 0 on failure.
 extern "C" double mv3d_debug_host_fill_gbs(size_t bytes, int threads, int reps, int pin_share_index, int pin_sharers)
 {
     if (bytes < 4096 || threads < 1 || reps < 1) { fail("mv3d_debug_host_fill_gbs: bad arguments"); return -1.0; }
@@ -1216,13 +1216,12 @@ extern "C" double mv3d_debug_host_fill_gbs(size_t bytes, int threads, int reps, 
     if (pin_sharers > 0) cpus = host_cpu_share(pin_share_index, pin_sharers);
     HostPool pool(threads, cpus);
     zero_fill(pool, static_cast<float *>(raw), bytes / 4);  // first touch: page faults, not bandwidth
-    double best = 0.0;
-    for (int r = 0; r < reps; r++) {
-        const auto t0 = std::chrono::steady_clock::now();
-        zero_fill(pool, static_cast<float *>(raw), bytes / 4);
-        const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-        if (sec > 0 && (double)bytes / sec / 1e9 > best) best = (double)bytes / sec / 1e9;
-    }
+    // the MEAN over all passes, not the best one: ranks that share a host run this at the same time, and the best pass
+    // of a rank is the one during which its neighbours happened to be idle
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int r = 0; r < reps; r++) zero_fill(pool, static_cast<float *>(raw), bytes / 4);
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    const double best = sec > 0 ? (double)bytes * reps / sec / 1e9 : 0.0;
     free(raw);
     return best;
 }

@@ -280,11 +280,21 @@ __device__ __forceinline__ int front_pixel_of(int R, int C, const ViewParams &p)
     const long long pix = r * p.cn + c;
     return (pix < (long long)p.front_pixels) ? (int)pix : -1;
 }
+// The exact bins are the RARE path (a few points in a thousand): kept out of line, so that the double-precision atan2
+// and the fdlibm atan2f do not take registers from the loops that call them.
+static __device__ __noinline__ int row_bin_slow(float x, float y, float z, float rad_to_deg, float phi_div)
+{
+    const double dx = (double)x, dy = (double)y;
+    const double planar = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
+    return row_bin_exact((double)z, planar, rad_to_deg, phi_div);
+}
+static __device__ __noinline__ int col_bin_slow(float y, float x, float rad_to_deg, float theta_div)
+{
+    return col_bin_exact(y, x, rad_to_deg, theta_div);
+}
 __device__ __forceinline__ int row_bin_of(const float4 &pt, const ViewParams &p)
 {
-    const double dx = (double)pt.x, dy = (double)pt.y;
-    const double planar = sqrt(__dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy)));
-    return row_bin_exact((double)pt.z, planar, p.rad_to_deg, p.phi_div);
+    return row_bin_slow(pt.x, pt.y, pt.z, p.rad_to_deg, p.phi_div);
 }
 __device__ __forceinline__ int front_pixel(const float4 &pt, const ViewParams &p)
 {
@@ -292,7 +302,7 @@ __device__ __forceinline__ int front_pixel(const float4 &pt, const ViewParams &p
     float planar_f;  // approximate on purpose (1.8e-7 relative, 9e-8 rad on the angle): fast path only
     asm("sqrt.approx.f32 %0, %1;" : "=f"(planar_f) : "f"(fmaf(pt.x, pt.x, pt.y * pt.y)));
     if (!angle_bin_fast(pt.z, planar_f, p.phi_scale, p.phi_eps, R)) R = row_bin_of(pt, p);
-    if (!angle_bin_fast(pt.y, pt.x, p.theta_scale, p.theta_eps, C)) C = col_bin_exact(pt.y, pt.x, p.rad_to_deg, p.theta_div);
+    if (!angle_bin_fast(pt.y, pt.x, p.theta_scale, p.theta_eps, C)) C = col_bin_slow(pt.y, pt.x, p.rad_to_deg, p.theta_div);
     return front_pixel_of(R, C, p);
 }
 
