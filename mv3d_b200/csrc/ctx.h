@@ -119,7 +119,7 @@ struct mv3d_ctx {
     unsigned compact_est = 0;  // entries the previous sweep produced: sizes the speculative copy of the next one
     long long launches = 0;
     size_t tile_bytes_target = 0;
-    int fused_min_batch = 8;              // TILE: calls of at least this many sweeps run as ONE persistent kernel (encode_fused.cuh); MV3D_FUSED=0 / =<n>
+    int fused_min_batch = 1 << 30;        // TILE: calls of at least this many sweeps run as ONE persistent kernel (encode_fused.cuh); opt-in with MV3D_FUSED=<n> -- measured 2.5x slower than the four launches (profiles/variants_r2i.txt)
     int fill_chunk = 0;                   // PATCH: sweeps per copy-engine zero-fill
     int auto_atomic_batch = 4;            // AUTO: up to this many sweeps per device call go to the atomic strategy
     double auto_atomic_ratio = 0.07;      // AUTO: ... and so do calls whose points weigh more than this share of the output bytes
