@@ -371,7 +371,7 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
 // kCompact: instead of storing the dense tile, report the touched cells in a per-sweep list
 //   compact[f] = { cell index [cap] , values [cap][planes] }   (structure of arrays)
 // A tile with n records touches at most n cells, so it owns the slots [beg, beg + n) of its own bin range
-// (tile_off): the first nd hold its touched cells (any order), the rest are marked kNoCell. The list is therefore
+// (tile_off): the first nd hold its touched cells in ASCENDING cell order, the rest are marked kNoCell. The list is therefore
 // ordered by tile with no atomics and no scan, and tile_off tells the reader where each tile's slots are. This is
 // what the host-buffer path reads back over PCIe instead of the 95 %-zero dense tensor.
 // kOccupancy (dense output only): also report, for the empty-anchor filter that consumes the view next
@@ -546,10 +546,27 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                 unsigned *out_idx = compact + (size_t)f * compact_cap * ((unsigned)planes + 1u);
                 unsigned *out_val = out_idx + compact_cap;
                 const unsigned beg = (unsigned)(rec0 - (binned + (size_t)offs.off[f]));
+                // Ascending cell order, so the host rebuilds the view in one linear walk (host_expand.cu, expand_sorted):
+                // a bit per cell "touched" (a finished density is > 0), a cell's slot = the touched cells below it.
+                const int nwords = (T + 31) >> 5;
+                for (int c = tid; c < nwords * 32; c += kTileThreads) {  // whole warps: c - lane is warp-uniform
+                    const bool touched = c < T && img[c * planes + zn + 1] != 0u;
+                    const unsigned bits = __ballot_sync(0xFFFFFFFFu, touched);
+                    if (lane == 0) occ_tile[c >> 5] = bits;
+                }
+                __syncthreads();
                 for (int d = warp; d < nd; d += kWarps) {
-                    const unsigned slot = beg + (unsigned)d;
-                    if (slot >= compact_cap) continue;  // cap >= points of the sweep: cannot happen, never overrun
                     const unsigned local = dirty[d];
+                    unsigned below = 0;
+                    for (unsigned w = (unsigned)lane; w <= (local >> 5); w += 32u) {
+                        unsigned bits = occ_tile[w];
+                        if (w == (local >> 5)) bits &= (1u << (local & 31u)) - 1u;
+                        below += (unsigned)__popc(bits);
+                    }
+#pragma unroll
+                    for (int o = 16; o > 0; o >>= 1) below += __shfl_xor_sync(0xFFFFFFFFu, below, o);
+                    const unsigned slot = beg + below;
+                    if (slot >= compact_cap) continue;  // cap >= points of the sweep: cannot happen, never overrun
                     if (lane == 0) out_idx[slot] = (unsigned)cell0 + local;
                     for (int k = lane; k < planes; k += 32) out_val[(size_t)slot * planes + k] = img[local * planes + k];
                 }

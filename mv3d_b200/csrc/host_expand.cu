@@ -351,4 +351,96 @@ void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const 
     pool.parallel_for(parts, body, caller_first);
 }
 
+// ---- expand_sorted: the rebuild as ONE linear walk ---------------------------------------------------------------
+// The tile kernel reports a tile's touched cells in ascending cell order, so the whole list is ascending once the
+// unused slots are skipped: a part (a run of whole tiles = a contiguous byte range of the destination) walks its
+// entries front to back, streams zeros over the gaps and composes only the few 64-byte lines a cell (or a run of
+// neighbouring cells) touches in a small window. No sorting, no per-block tables, every byte written once.
+void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
+                   unsigned n, const unsigned *tile_off, int tiles, int tile_cells,
+                   const std::function<void()> *caller_first)
+{
+    if (!dst || cells == 0 || planes <= 0) {
+        if (caller_first) (*caller_first)();
+        return;
+    }
+    constexpr size_t kWin = 1024;  // window of composed lines; a cell must fit with a line to spare on either side
+    const size_t cell_bytes = (size_t)planes * 4;
+    if (!tile_off || tiles <= 0 || tile_cells <= 0 || cell_bytes + 192 > kWin) {  // no tile order / very deep grids
+        expand_compact(pool, dst, cells, planes, idx, vals, n, tile_off, tiles, tile_cells, caller_first);
+        return;
+    }
+    // Parts are claimed dynamically; several per thread, so that the caller's errand and a slow core cost a fraction
+    // of a part, not a whole share.
+    int parts = pool.size() * 6;
+    if (parts > tiles) parts = tiles;
+    const size_t tiles_per_part = ((size_t)tiles + parts - 1) / parts;
+    const std::function<void(int)> body = [&](int part) {
+        const size_t t0 = (size_t)part * tiles_per_part;
+        if (t0 >= (size_t)tiles) return;
+        const size_t t1 = (t0 + tiles_per_part < (size_t)tiles) ? t0 + tiles_per_part : (size_t)tiles;
+        const size_t c0 = t0 * (size_t)tile_cells;
+        if (c0 >= cells) return;
+        const size_t c1 = (t1 * (size_t)tile_cells < cells && t1 < (size_t)tiles) ? t1 * (size_t)tile_cells : cells;
+        char *const base = reinterpret_cast<char *>(dst);
+        const uintptr_t A0 = reinterpret_cast<uintptr_t>(base + c0 * cell_bytes);  // this part = addresses [A0, A1)
+        const uintptr_t A1 = reinterpret_cast<uintptr_t>(base + c1 * cell_bytes);
+        alignas(64) char win[kWin];
+        uintptr_t done = A0;        // [A0, done) has been emitted
+        uintptr_t wlo = 0, whi = 0; // the open window holds [wlo, whi), wlo == done; whi is line-aligned or A1
+        bool open = false;
+        size_t floor_cell = c0;     // the next accepted cell must be >= this: ascending order, and memory safety
+        for (size_t t = t0; t < t1; t++) {
+            unsigned i = tile_off[t] < n ? tile_off[t] : n;
+            const unsigned i1 = tile_off[t + 1] < n ? tile_off[t + 1] : n;
+            if (floor_cell < t * (size_t)tile_cells) floor_cell = t * (size_t)tile_cells;
+            const size_t tile_end = ((t + 1) * (size_t)tile_cells < c1) ? (t + 1) * (size_t)tile_cells : c1;
+            for (; i < i1; i++) {
+                const size_t cell = idx[i];
+                if (cell >= cells) break;                            // first unused slot: the tile is done
+                if (cell < floor_cell || cell >= tile_end) continue; // out of contract: never written
+                floor_cell = cell + 1;
+#ifdef MV3D_HAVE_NT_STORES
+                _mm_prefetch(reinterpret_cast<const char *>(vals + (size_t)(i + 6) * planes), _MM_HINT_T0);
+#endif
+                const uintptr_t a = reinterpret_cast<uintptr_t>(base + cell * cell_bytes);
+                uintptr_t end = (a + cell_bytes + 63) & ~(uintptr_t)63;
+                if (end > A1) end = A1;
+                if (open && a <= whi) {                              // touches the window's last line: extend it
+                    if (end - wlo > kWin) {                          // full: emit the lines in front of this cell
+                        const uintptr_t f = a & ~(uintptr_t)63;      // > wlo here, and every byte below `a` is final
+                        copy_stream(reinterpret_cast<char *>(wlo), win, (size_t)(f - wlo));
+                        memmove(win, win + (f - wlo), (size_t)(whi - f));
+                        wlo = done = f;
+                    }
+                    if (end > whi) {
+                        memset(win + (whi - wlo), 0, (size_t)(end - whi));
+                        whi = end;
+                    }
+                } else {
+                    if (open) {
+                        copy_stream(reinterpret_cast<char *>(wlo), win, (size_t)(whi - wlo));
+                        done = whi;
+                    }
+                    uintptr_t lo = a & ~(uintptr_t)63;
+                    if (lo < done) lo = done;                        // only the part's first line can be cut
+                    if (lo > done) zero_stream(reinterpret_cast<char *>(done), (size_t)(lo - done));
+                    wlo = done = lo;
+                    whi = end;
+                    open = true;
+                    memset(win, 0, (size_t)(whi - wlo));
+                }
+                memcpy(win + (a - wlo), vals + (size_t)i * planes, cell_bytes);
+            }
+        }
+        if (open) {
+            copy_stream(reinterpret_cast<char *>(wlo), win, (size_t)(whi - wlo));
+            done = whi;
+        }
+        if (A1 > done) zero_stream(reinterpret_cast<char *>(done), (size_t)(A1 - done));
+        store_fence();
+    };
+    pool.parallel_for(parts, body, caller_first);
+}
+
 } // namespace mv3d

@@ -717,8 +717,8 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         if (split)
             scatter_compact(*ctx->pool, top_host, cells, p.planes, stage, stage + cap, used, &errand);
         else
-            expand_compact(*ctx->pool, top_host + (size_t)i * (size_t)p.top_frame_floats, cells, p.planes, stage,
-                           stage + cap, used, toff, p.tiles_per_frame, p.tile_cells, &errand);
+            expand_sorted(*ctx->pool, top_host + (size_t)i * (size_t)p.top_frame_floats, cells, p.planes, stage,
+                          stage + cap, used, toff, p.tiles_per_frame, p.tile_cells, &errand);
         t_expand += now() - t0;
         if (enq_rc) return -1;
     }
@@ -1186,6 +1186,18 @@ extern "C" int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, c
     }
     HostPool pool(threads);
     expand_compact(pool, dst, cells, planes, idx.data(), vals.data(), n, nullptr, 0, 0, nullptr);
+    return 0;
+}
+
+// The linear-walk rebuild the host entry points use: idx / vals / tile_off laid out as tile_compact_kernel writes them
+// (tile t owns the slots [tile_off[t], tile_off[t + 1]); its touched cells first, ascending, then unused slots).
+extern "C" int mv3d_debug_expand_sorted(float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
+                                        unsigned n, const unsigned *tile_off, int tiles, int tile_cells, int threads)
+{
+    if (!dst || planes <= 0 || (n && (!idx || !vals)) || !tile_off || tiles <= 0 || tile_cells <= 0)
+        return fail("mv3d_debug_expand_sorted: bad arguments");
+    HostPool pool(threads);
+    expand_sorted(pool, dst, cells, planes, idx, vals, n, tile_off, tiles, tile_cells, nullptr);
     return 0;
 }
 

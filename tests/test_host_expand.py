@@ -51,3 +51,61 @@ def test_expand_preserves_nan_and_bit_patterns(encoder_lib):
     vals = np.array([[np.nan, -0.0, np.inf, 1e-45]], np.float32)
     got = _expand(encoder_lib, 10, 4, np.array([5], np.uint32), vals, 2)
     assert np.array_equal(got[5].view(np.uint32), vals[0].view(np.uint32))
+
+
+def _sorted_list(rng, cells, planes, tile_cells, fill, spare):
+    """A list laid out as tile_compact_kernel writes it: per tile its touched cells ascending, then unused slots."""
+    tiles = (cells + tile_cells - 1) // tile_cells
+    touched = np.sort(rng.choice(cells, size=int(cells * fill), replace=False)) if fill > 0 else np.zeros(0, np.int64)
+    per_tile = np.bincount(touched // tile_cells, minlength=tiles)
+    slots = per_tile + rng.integers(0, spare + 1, tiles)  # a tile owns at least as many slots as it has touched cells
+    tile_off = np.zeros(tiles + 1, np.uint32)
+    tile_off[1:] = np.cumsum(slots)
+    n = int(tile_off[-1])
+    idx = np.full(n, 0xFFFFFFFF, np.uint32)
+    vals = rng.random((n, planes), dtype=np.float32) + 0.5  # unused slots carry garbage that must not land anywhere
+    first = np.searchsorted(touched // tile_cells, np.arange(tiles))
+    where = tile_off[touched // tile_cells] + (np.arange(len(touched)) - first[touched // tile_cells])
+    idx[where] = touched
+    expect = np.zeros((cells, planes), np.float32)
+    expect[touched] = vals[where]
+    return idx, vals, tile_off, tiles, expect
+
+
+@pytest.mark.parametrize("threads", [1, 3, 8])
+@pytest.mark.parametrize("cells,planes,tile_cells,fill", [(563200, 27, 340, 0.05), (563200, 27, 352, 0.6), (5000, 10, 64, 1.0),
+                                                          (1000, 1, 7, 0.3), (999, 3, 1000, 0.5), (77, 27, 340, 0.2),
+                                                          (4096, 16, 32, 0.0), (300, 700, 10, 0.3)])
+def test_expand_sorted_matches_numpy_scatter(encoder_lib, threads, cells, planes, tile_cells, fill):
+    """The linear-walk rebuild (what the host entry points run) on lists shaped like the compact tile kernel's:
+    sparse, dense, every cell touched, one-plane cells, a single tile, cells wider than the compose window (falls back),
+    aligned and misaligned destinations; guard floats on both sides stay untouched."""
+    rng = np.random.default_rng(cells * 31 + threads)
+    idx, vals, tile_off, tiles, expect = _sorted_list(rng, cells, planes, tile_cells, fill, spare=3)
+    for offset in (0, 1, 5, 16):
+        buf = np.full(cells * planes + offset + 40, 7.0, dtype=np.float32)
+        dst = buf[offset:offset + cells * planes]
+        rc = encoder_lib.mv3d_debug_expand_sorted(dst.ctypes.data, cells, planes, idx.ctypes.data, vals.ctypes.data, len(idx),
+                                                  tile_off.ctypes.data, tiles, tile_cells, threads)
+        assert rc == 0
+        assert (buf[:offset] == 7.0).all() and (buf[offset + cells * planes:] == 7.0).all()
+        assert np.array_equal(dst.reshape(cells, planes).view(np.uint32), expect.view(np.uint32))
+
+
+def test_expand_sorted_never_writes_out_of_contract_entries(encoder_lib):
+    """An entry that breaks the ascending order, repeats a cell or names a cell of another tile is skipped -- the walk
+    never writes outside its own part, whatever the list holds."""
+    cells, planes, tile_cells = 64, 5, 16
+    tile_off = np.array([0, 4, 8, 12, 16], np.uint32)
+    idx = np.array([3, 2, 3, 15,   40, 16, 17, 0xFFFFFFFF,   0xFFFFFFFF, 33, 34, 35,   48, 63, 64, 5], np.uint32)
+    vals = (np.arange(16 * planes, dtype=np.float32).reshape(16, planes) + 1)
+    expect = np.zeros((cells, planes), np.float32)
+    for slot in (0, 3, 5, 6, 12, 13):  # 2 and the second 3 are out of order; 40 is another tile's; tile 2 starts unused
+        expect[idx[slot]] = vals[slot]
+    for threads in (1, 4):
+        buf = np.full(cells * planes + 16, 9.0, np.float32)
+        dst = buf[8:8 + cells * planes]
+        assert encoder_lib.mv3d_debug_expand_sorted(dst.ctypes.data, cells, planes, idx.ctypes.data, vals.ctypes.data, 16,
+                                                    tile_off.ctypes.data, 4, tile_cells, threads) == 0
+        assert (buf[:8] == 9.0).all() and (buf[8 + cells * planes:] == 9.0).all()
+        assert np.array_equal(dst.reshape(cells, planes), expect)

@@ -1,0 +1,63 @@
+// host_rebuild_bench.cu -- the host half of the compact read-back alone, on a realistic entry list, against the plain
+// streaming zero-fill of the same bytes by the same threads. Needs no GPU (pageable memory).
+//   nvcc -O3 -std=c++17 -o /tmp/host_rebuild_bench tools/host_rebuild_bench.cu mv3d_b200/csrc/host_expand.cu -lpthread
+//   /tmp/host_rebuild_bench list.bin [sweeps=16]     (list.bin: u32 n, tiles, tile_cells; tile_off[tiles+1]; idx[n])
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <thread>
+#include <vector>
+#include "../mv3d_b200/csrc/host_expand.h"
+using namespace mv3d;
+static double now() { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); }
+int main(int argc, char **argv)
+{
+    if (argc < 2) { printf("usage: %s list.bin [sweeps]\n", argv[0]); return 2; }
+    FILE *f = fopen(argv[1], "rb");
+    if (!f) { printf("cannot open %s\n", argv[1]); return 1; }
+    unsigned hdr[3];
+    if (fread(hdr, 4, 3, f) != 3) return 1;
+    const unsigned n = hdr[0], tiles = hdr[1], tile_cells = hdr[2];
+    std::vector<unsigned> toff(tiles + 1), idx(n);
+    if (fread(toff.data(), 4, tiles + 1, f) != tiles + 1 || fread(idx.data(), 4, n, f) != n) return 1;
+    fclose(f);
+    const size_t cells = 563200; const int planes = 27;
+    const int sweeps = argc > 2 ? atoi(argv[2]) : 16;
+    const size_t frame = cells * planes;
+    float *dst = nullptr;
+    if (posix_memalign((void **)&dst, 4096, frame * 4 * sweeps)) return 1;
+    memset(dst, 1, frame * 4 * sweeps);
+    // one staging copy per sweep, so the values are as cold as a DMA would leave them
+    std::vector<std::vector<unsigned>> vals(sweeps, std::vector<unsigned>((size_t)n * planes, 0x3f800000u));
+    const unsigned hw = std::thread::hardware_concurrency();
+    for (int threads : {1, 2, 4, 8, 16, 32}) {
+        if ((unsigned)threads > hw) break;
+        HostPool pool(threads);
+        double best_z = 1e9, best_e = 1e9, best_s = 1e9, best_l = 1e9;
+        for (int rep = 0; rep < 3; rep++) {
+            double t0 = now();
+            for (int s = 0; s < sweeps; s++) zero_fill(pool, dst + (size_t)s * frame, frame);
+            best_z = std::min(best_z, (now() - t0) / sweeps);
+            t0 = now();
+            for (int s = 0; s < sweeps; s++)
+                expand_compact(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, toff.data(), (int)tiles, (int)tile_cells, nullptr);
+            best_e = std::min(best_e, (now() - t0) / sweeps);
+            t0 = now();
+            for (int s = 0; s < sweeps; s++) {
+                zero_fill(pool, dst + (size_t)s * frame, frame);
+                scatter_compact(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, nullptr);
+            }
+            best_s = std::min(best_s, (now() - t0) / sweeps);
+            t0 = now();
+            for (int s = 0; s < sweeps; s++)
+                expand_sorted(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, toff.data(), (int)tiles, (int)tile_cells, nullptr);
+            best_l = std::min(best_l, (now() - t0) / sweeps);
+        }
+        printf("threads=%d expand_sorted %.3f ms/sweep %.1f GB/s\n", threads, best_l * 1e3, frame * 4 / best_l / 1e9);
+        printf("threads=%d fill+scatter %.3f ms/sweep %.1f GB/s\n", threads, best_s * 1e3, frame * 4 / best_s / 1e9);
+        printf("threads=%d zero_fill %.3f ms/sweep %.1f GB/s | expand %.3f ms/sweep %.1f GB/s | ratio %.2f\n", threads, best_z * 1e3,
+               frame * 4 / best_z / 1e9, best_e * 1e3, frame * 4 / best_e / 1e9, best_e / best_z);
+    }
+    return 0;
+}
