@@ -35,7 +35,7 @@ struct DeviceBuffer {
 // Scratch for one in-flight encode call. Zero-initialised where the kernels rely on it (tile histogram,
 // front-view winners) and left zero by them, so no per-call memset is needed on the tile path.
 struct Workspace {
-    DeviceBuffer keys, binned, tile_count, tile_off, fv_winner, cellkey, sort_temp, fused_sync;
+    DeviceBuffer keys, binned, tile_count, tile_off, fv_winner, cellkey, sort_temp;
 };
 
 constexpr int kSlots = 4;  // host pipeline depth: copy-in / encode / copy-out / host rebuild of consecutive sweeps overlap
@@ -81,7 +81,7 @@ struct HostSlot {
 enum KernelId { K_CLASSIFY = 0, K_TILE_SCAN, K_BIN, K_TILE_BUILD, K_FRONT_FINALIZE, K_FILL_ZERO, K_ATOMIC_SCATTER,
                 K_ATOMIC_FINALIZE, K_TILE_COMPACT, K_PYFRONT_LINK,
                 K_PYFRONT_REDUCE, K_ANCHOR_OCCUPANCY, K_ANCHOR_TEST, K_ANCHOR_SUM, K_ANCHOR_COMPACT, K_FILL_CE,
-                K_TILE_PATCH, K_SORT_KEYS, K_RADIX_SORT, K_SORT_REDUCE, K_FUSED, K_COUNT };
+                K_TILE_PATCH, K_SORT_KEYS, K_RADIX_SORT, K_SORT_REDUCE, K_COUNT };
 static const char *const kKernelNames[K_COUNT] = {"classify_kernel", "tile_scan_kernel", "bin_kernel",
                                                   "tile_build_kernel", "front_finalize_kernel", "fill_zero_kernel",
                                                   "atomic_scatter_kernel", "atomic_finalize_kernel",
@@ -90,7 +90,7 @@ static const char *const kKernelNames[K_COUNT] = {"classify_kernel", "tile_scan_
                                                   "anchor_occupancy_kernel", "anchor_test_kernel",
                                                   "anchor_sum_kernel", "anchor_compact_kernel",
                                                   "ce_zero_fill", "tile_patch_kernel", "sort_keys_kernel",
-                                                  "cub_radix_sort", "sort_reduce_kernel", "encode_fused_kernel"};
+                                                  "cub_radix_sort", "sort_reduce_kernel"};
 
 struct TimedLaunch {
     cudaEvent_t start, stop;
@@ -119,7 +119,6 @@ struct mv3d_ctx {
     unsigned compact_est = 0;  // entries the previous sweep produced: sizes the speculative copy of the next one
     long long launches = 0;
     size_t tile_bytes_target = 0;
-    int fused_min_batch = 1 << 30;        // TILE: calls of at least this many sweeps run as ONE persistent kernel (encode_fused.cuh); opt-in with MV3D_FUSED=<n> -- measured 2.5x slower than the four launches (profiles/variants_r2i.txt)
     int fill_chunk = 0;                   // PATCH: sweeps per copy-engine zero-fill
     int auto_atomic_batch = 4;            // AUTO: up to this many sweeps per device call go to the atomic strategy
     double auto_atomic_ratio = 0.07;      // AUTO: ... and so do calls whose points weigh more than this share of the output bytes
@@ -196,7 +195,7 @@ inline void release(DeviceBuffer &b)
 inline void release(Workspace &w)
 {
     release(w.keys); release(w.binned); release(w.tile_count); release(w.tile_off);
-    release(w.fv_winner); release(w.cellkey); release(w.sort_temp); release(w.fused_sync);
+    release(w.fv_winner); release(w.cellkey); release(w.sort_temp);
 }
 
 // Optional per-kernel timing: CUDA events recorded on the launching stream around each kernel.

@@ -873,7 +873,6 @@ point_keys_kernel(const float4 *__restrict__ pts, int n, ViewParams p, int *__re
 }
 
 } // namespace mv3d
-#include "encode_fused.cuh"
 namespace mv3d {
 
 // ------------------------------------------------------------------------------------------------
@@ -946,7 +945,6 @@ static cudaError_t tile_kernels_opt_in(int smem)
     if ((e = cudaFuncSetAttribute(tile_build_kernel<kPy>, attr, smem)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(tile_build_occupancy_kernel<kPy>, attr, smem)) != cudaSuccess) return e;
     if ((e = cudaFuncSetAttribute(tile_patch_kernel<kPy>, attr, smem)) != cudaSuccess) return e;
-    if ((e = cudaFuncSetAttribute(encode_fused_kernel<kPy>, attr, smem)) != cudaSuccess) return e;
     return cudaFuncSetAttribute(tile_compact_kernel<kPy>, attr, smem);
 }
 
@@ -998,33 +996,6 @@ int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p,
     dim3 grid(point_blocks_batched(max_points, kPointItems, batch, 8) + front_blocks, batch);
     auto kernel = p.py ? bin_kernel<true> : bin_kernel<false>;
     launch_after(kernel, grid, dim3(kPointThreads), 0, s, pts, offs, p, keys, tile_off, binned, fv_winner, front, front_blocks);
-    return 1;
-}
-
-size_t fused_sync_bytes(int batch) { return (size_t)fused_sync_words(batch) * sizeof(unsigned); }
-
-// The whole tile strategy as one persistent launch (encode_fused.cuh). `sync` must hold fused_sync_bytes(batch); it is
-// cleared here, stream-ordered. fv_winner / front may be NULL (no front view).
-int launch_encode_fused(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
-                        uint2 *keys, unsigned *tile_count, unsigned *tile_off, uint4 *binned, unsigned *fv_winner,
-                        float *front, const float *lut, float *top, unsigned *sync, int grid_blocks, cudaStream_t s)
-{
-    FusedPlan plan;
-    plan.batch = batch;
-    plan.n_classify = (max_points + kFusedClassifyChunk - 1) / kFusedClassifyChunk;
-    plan.n_bin = (max_points + kFusedBinChunk - 1) / kFusedBinChunk;
-    const bool with_front = fv_winner && front && p.front_pixels > 0;
-    plan.n_front = with_front ? (p.front_pixels + kFusedFrontChunk - 1) / kFusedFrontChunk : 0;
-    plan.n_point = plan.n_classify + 1 + plan.n_bin + plan.n_front;
-    plan.per_stage = plan.n_point + p.tiles_per_frame;
-    plan.stages = batch + kFusedLag;
-    cudaMemsetAsync(sync, 0, fused_sync_bytes(batch), s);
-    const long long total = (long long)plan.stages * plan.per_stage;
-    const int grid = (long long)grid_blocks < total ? grid_blocks : (int)total;
-    auto kernel = p.py ? encode_fused_kernel<true> : encode_fused_kernel<false>;
-    kernel<<<grid, kTileThreads, tile_smem_bytes(p), s>>>(pts, offs, p, plan, keys, tile_count, tile_off, binned,
-                                                          with_front ? fv_winner : nullptr, with_front ? front : nullptr,
-                                                          lut, top, sync);
     return 1;
 }
 

@@ -31,10 +31,6 @@ int launch_tile_scan(unsigned *tile_count, unsigned *tile_off, int tiles_per_fra
 int launch_bin(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
                const uint2 *keys, const unsigned *tile_off, uint4 *binned, cudaStream_t s,
                unsigned *fv_winner = nullptr, float *front = nullptr);
-size_t fused_sync_bytes(int batch);
-int launch_encode_fused(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, int batch, int max_points,
-                        uint2 *keys, unsigned *tile_count, unsigned *tile_off, uint4 *binned, unsigned *fv_winner,
-                        float *front, const float *lut, float *top, unsigned *sync, int grid_blocks, cudaStream_t s);
 int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s,
                       const OccupancySink *sink = nullptr);

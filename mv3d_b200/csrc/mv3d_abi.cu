@@ -86,7 +86,6 @@ extern "C" int mv3d_ctx_create(int device, mv3d_ctx **out)
     const char *fc = getenv("MV3D_FILL_CHUNK");
     ctx->fill_chunk = fc ? atoi(fc) : 8;
     if (ctx->fill_chunk < 1) ctx->fill_chunk = 1;
-    if (const char *fu = getenv("MV3D_FUSED")) ctx->fused_min_batch = atoi(fu) > 0 ? atoi(fu) : 1 << 30;
     const char *ht = getenv("MV3D_HOST_THREADS");
     ctx->host_threads = ht ? atoi(ht) : 0;
     if (const char *hs = getenv("MV3D_HOST_SPLIT_FIRST")) ctx->host_split_first = atoi(hs);
@@ -420,18 +419,6 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
                     return launch_tile_patch(binned, to, so, p, ctx->lut, top_j, nb, grid_blocks, s);
                 });
             }
-            CUDA_TRY(cudaGetLastError());
-            return 0;
-        }
-        // TILE, batches: the four phases as items of ONE persistent kernel, so that the issue-bound point passes of one
-        // sweep run beside the store-bound tile build of an earlier one (encode_fused.cuh).
-        if (!compact && !(sink && sink->words) && batch >= ctx->fused_min_batch) {
-            if (ensure(ws.fused_sync, fused_sync_bytes(kMaxBatchPerLaunch), false, s)) return -1;
-            timed_launch(ctx, K_FUSED, s, [&] {
-                return launch_encode_fused(pts, offs, p, batch, max_points, keys, tcount, toff, binned,
-                                           want_front ? winners : nullptr, front_dev, ctx->lut, top_dev,
-                                           static_cast<unsigned *>(ws.fused_sync.ptr), grid_blocks, s);
-            });
             CUDA_TRY(cudaGetLastError());
             return 0;
         }
@@ -861,22 +848,10 @@ static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_de
         unsigned *tcount = static_cast<unsigned *>(ws.tile_count.ptr), *toff = static_cast<unsigned *>(ws.tile_off.ptr);
         const int blocks_per_sm = tile_blocks_per_sm(ctx, p);
         if (blocks_per_sm < 1) return fail("tile kernel does not fit: %zu bytes of shared memory", tile_smem_bytes(p));
-        const bool fused = !compact && !(sink && sink->words) && batch >= ctx->fused_min_batch;
-        if (fused) {
-            if (ensure(ws.fused_sync, fused_sync_bytes(kMaxBatchPerLaunch), false, s)) return -1;
-            timed_launch(ctx, K_FUSED, s, [&] {
-                return launch_encode_fused(pts, offs, p, batch, max_points, keys, tcount, toff, binned, nullptr, nullptr,
-                                           ctx->lut_py, top_dev, static_cast<unsigned *>(ws.fused_sync.ptr),
-                                           blocks_per_sm * ctx->sm_count, s);
-            });
-        } else {
         timed_launch(ctx, K_CLASSIFY, s, [&] { return launch_classify(pts, offs, p, batch, max_points, keys, tcount, nullptr, s); });
         timed_launch(ctx, K_TILE_SCAN, s, [&] { return launch_tile_scan(tcount, toff, p.tiles_per_frame, batch, s); });
         timed_launch(ctx, K_BIN, s, [&] { return launch_bin(pts, offs, p, batch, max_points, keys, toff, binned, s); });
-        }
-        if (fused) {
-            // everything is done by the one launch above
-        } else if (compact)  // host read-back: report the touched cells only (single sweep per call)
+        if (compact)  // host read-back: report the touched cells only (single sweep per call)
             timed_launch(ctx, K_TILE_COMPACT, s, [&] {
                 return launch_tile_compact(binned, toff, offs, p, ctx->lut_py, batch, blocks_per_sm * ctx->sm_count,
                                            compact->entries, compact->cap, s);

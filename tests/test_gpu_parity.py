@@ -393,11 +393,12 @@ def test_outputs_inside_guard_bands(torch_cuda, oracle_mod, strategy, pad):
 
 
 @pytest.mark.parametrize("knob,value", [("MV3D_TILE_BYTES", "8192"), ("MV3D_TILE_BYTES", "46080"), ("MV3D_FILL_CHUNK", "3"),
-                                        ("MV3D_PDL", "0"), ("MV3D_FUSED", "1")])
+                                        ("MV3D_PDL", "0")])
 def test_tuning_knobs_stay_bit_exact(torch_cuda, oracle_mod, monkeypatch, knob, value):
-    """The tuning knobs that remain in the library (tile size, chunking of the PATCH fill, plain stream order instead of programmatic dependent launch, the opt-in single persistent kernel of encode_fused.cuh) change
+    """The tuning knobs that remain in the library (tile size, chunking of the PATCH fill, plain stream order instead of programmatic dependent launch) change
     the schedule, never the result. The round-1 experiment kernels they used to sit beside were removed from the
-    product translation unit (tools/experiments/r1_rejected_variants.patch)."""
+    product translation unit (tools/experiments/r1_rejected_variants.patch), as were round 2's two overlap experiments
+    (tools/experiments/r2_fused_persistent_kernel.patch, r2_guest_overlap.patch)."""
     torch = torch_cuda
     from mv3d_b200.encoder import ViewEncoder
     monkeypatch.setenv(knob, value)  # read when the context is created
