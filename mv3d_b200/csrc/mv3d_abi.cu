@@ -744,7 +744,10 @@ extern "C" int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, c
     int rc = 0;
     for (int i = 0; i < batch && rc == 0; i++) {
         HostSlot &slot = ctx->slots[i % kSlots];
-        if (!slot.stream) CUDA_TRY(cudaStreamCreateWithFlags(&slot.stream, cudaStreamNonBlocking));
+        if (!slot.stream) {
+            const cudaError_t se = cudaStreamCreateWithFlags(&slot.stream, cudaStreamNonBlocking);
+            if (se != cudaSuccess) { slot.stream = nullptr; rc = fail("cannot create a stream: %s", cudaGetErrorString(se)); break; }
+        }
         cudaStream_t s = slot.stream;
         const int n = offsets_host[i + 1] - offsets_host[i];
         // Stream order makes the slot's previous copy-out finish before its buffers are reused.
@@ -1035,15 +1038,21 @@ extern "C" int mv3d_pytwin_encode_batch_host(mv3d_ctx *ctx, const float *points_
     int rc = 0;
     for (int i = 0; i < batch && rc == 0; i++) {
         HostSlot &slot = ctx->slots[i % kSlots];
-        if (!slot.stream) CUDA_TRY(cudaStreamCreateWithFlags(&slot.stream, cudaStreamNonBlocking));
+        if (!slot.stream) {
+            const cudaError_t se = cudaStreamCreateWithFlags(&slot.stream, cudaStreamNonBlocking);
+            if (se != cudaSuccess) { slot.stream = nullptr; rc = fail("cannot create a stream: %s", cudaGetErrorString(se)); break; }
+        }
         cudaStream_t s = slot.stream;
         const int n = offsets_host[i + 1] - offsets_host[i];
         if (ensure(slot.points, (size_t)n * 16 + 16, false, s)) { rc = -1; break; }
         if (top_host && ensure(slot.top, top_bytes + 16, false, s)) { rc = -1; break; }
         if (front_host && ensure(slot.front, front_bytes + 16, false, s)) { rc = -1; break; }
+        // A failure must not return while earlier copies are still writing the caller's buffers: break, then drain.
+        cudaError_t ce = cudaSuccess;
         if (n > 0)
-            CUDA_TRY(cudaMemcpyAsync(slot.points.ptr, points_host + (size_t)offsets_host[i] * 4, (size_t)n * 16,
-                                     cudaMemcpyHostToDevice, s));
+            ce = cudaMemcpyAsync(slot.points.ptr, points_host + (size_t)offsets_host[i] * 4, (size_t)n * 16,
+                                 cudaMemcpyHostToDevice, s);
+        if (ce != cudaSuccess) { rc = fail("copy-in of sweep %d failed: %s", i, cudaGetErrorString(ce)); break; }
         const int local_off[2] = {0, n};
         float *top_d = top_host ? static_cast<float *>(slot.top.ptr) : nullptr;
         float *front_d = front_host ? static_cast<float *>(slot.front.ptr) : nullptr;
@@ -1052,11 +1061,12 @@ extern "C" int mv3d_pytwin_encode_batch_host(mv3d_ctx *ctx, const float *points_
         ctx->h2d_bytes += (size_t)n * 16;
         ctx->d2h_bytes += (top_host ? top_bytes : 0) + (front_host ? front_bytes : 0);
         if (top_host && top_bytes)
-            CUDA_TRY(cudaMemcpyAsync(top_host + (size_t)i * (size_t)p.top_frame_floats, top_d, top_bytes,
-                                     cudaMemcpyDeviceToHost, s));
-        if (front_host && front_bytes)
-            CUDA_TRY(cudaMemcpyAsync(front_host + (size_t)i * (size_t)fp.pixels * 3, front_d, front_bytes,
-                                     cudaMemcpyDeviceToHost, s));
+            ce = cudaMemcpyAsync(top_host + (size_t)i * (size_t)p.top_frame_floats, top_d, top_bytes,
+                                 cudaMemcpyDeviceToHost, s);
+        if (ce == cudaSuccess && front_host && front_bytes)
+            ce = cudaMemcpyAsync(front_host + (size_t)i * (size_t)fp.pixels * 3, front_d, front_bytes,
+                                 cudaMemcpyDeviceToHost, s);
+        if (ce != cudaSuccess) { rc = fail("copy-out of sweep %d failed: %s", i, cudaGetErrorString(ce)); break; }
     }
     for (auto &slot : ctx->slots)
         if (slot.stream) {
