@@ -201,11 +201,11 @@ int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, const unsign
  * of the finished values). */
 int mv3d_debug_expand_split(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n, int threads);
 /* The form the host entry points run: the list as the compact tile kernel writes it -- cell indices idx[n] and values
- * vals[n][planes] in separate arrays, tile t (tile_cells consecutive cells) owning the slots
- * [tile_off[t], tile_off[t + 1]), its touched cells first in ascending order, then unused slots (cell >= cells).
- * One linear walk per thread; an entry out of order or out of its tile's range is skipped, never written. */
+ * vals[n][planes] in separate arrays, tile t (tile_cells consecutive cells) owning the entries
+ * [table[2t], table[2t] + table[2t+1]) in ascending cell order. One linear walk per thread; an entry out of order or
+ * out of its tile's cell range is skipped, never written; ranges are clamped to n. */
 int mv3d_debug_expand_sorted(float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals, unsigned n,
-                             const unsigned *tile_off, int tiles, int tile_cells, int threads);
+                             const unsigned *table, int tiles, int tile_cells, int threads);
 
 /* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

@@ -48,8 +48,9 @@ struct PinnedBuffer {
 
 // Where the compact variant of the tile kernel reports the touched cells of ONE sweep (device memory).
 struct CompactOut {
-    unsigned *entries = nullptr;  // cell indices [cap], then values [cap][planes]; slots follow the sweep's tile_off
+    unsigned *entries = nullptr;  // cell indices [cap], then values [cap][planes]: the sweep's touched cells, contiguous
     unsigned cap = 0;             // >= points of the sweep
+    unsigned *table = nullptr;    // {first entry, entries} per tile, then the sweep's entry counter (zeroed before the launch)
 };
 
 // Empty-anchor filter (anchor_abi.cu): the anchor set stays resident, scratch grows on demand.
@@ -70,8 +71,8 @@ struct HostSlot {
     Workspace ws;
     DeviceBuffer points, top, front;
     // compact read-back
-    DeviceBuffer compact;
-    PinnedBuffer stage, front_stage, toff_stage;
+    DeviceBuffer compact, ctable;  // the sweep's touched cells; its tile table + entry counter
+    PinnedBuffer stage, front_stage, toff_stage;  // toff_stage receives the tile table
     cudaEvent_t done = nullptr;
     unsigned copied = 0;          // entries already copied to `stage` by the speculative D2H
     unsigned cap = 0;             // entry capacity of the sweep in flight (indices [cap], then values [cap][planes])

@@ -370,10 +370,11 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
 // ------------------------------------------------------------------------------------------------
 // kCompact: instead of storing the dense tile, report the touched cells in a per-sweep list
 //   compact[f] = { cell index [cap] , values [cap][planes] }   (structure of arrays)
-// A tile with n records touches at most n cells, so it owns the slots [beg, beg + n) of its own bin range
-// (tile_off): the first nd hold its touched cells in ASCENDING cell order, the rest are marked kNoCell. The list is therefore
-// ordered by tile with no atomics and no scan, and tile_off tells the reader where each tile's slots are. This is
-// what the host-buffer path reads back over PCIe instead of the 95 %-zero dense tensor.
+//   table[f]   = { first slot, touched cells } per tile, then the sweep's slot counter (zeroed by the caller)
+// A non-empty tile takes as many consecutive slots as it touched cells from the sweep's counter and fills them in
+// ASCENDING cell order; the list is contiguous (touched cells of the sweep <= its points <= cap), and the table tells
+// the reader where each tile's cells are. This is what the host-buffer path reads back over PCIe instead of the
+// 95 %-zero dense tensor.
 // kOccupancy (dense output only): also report, for the empty-anchor filter that consumes the view next
 // (anchor_kernels.cu), one bit per cell "touched" -- touched cells carry a density > 0, untouched cells are all
 // zero -- into a pre-zeroed per-frame bit map, and raise the frame's flag when an intensity is negative, -0 or NaN
@@ -390,7 +391,8 @@ template <bool kCompact, bool kOccupancy, bool kPy, int kStore = kStoreBulk,
 __device__ __forceinline__ void
 tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off, const FrameOffsets &offs,
           const ViewParams &p, const float *__restrict__ lut, float *__restrict__ top, int total_tiles,
-          unsigned *__restrict__ compact, unsigned compact_cap, OccupancySink sink = OccupancySink())
+          unsigned *__restrict__ compact, unsigned compact_cap, OccupancySink sink = OccupancySink(),
+          unsigned *__restrict__ compact_table = nullptr)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     const int T = p.tile_cells;
@@ -450,7 +452,12 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
         const bool bulk = ((reinterpret_cast<uintptr_t>(dst) | (uintptr_t)bytes) & 15u) == 0;
 
         if (kCompact && n0 == 0) {
-            // nothing to report for an empty tile
+            // nothing to report for an empty tile but its (empty) range
+            if (tid == 0) {
+                unsigned *tab = compact_table + (size_t)f * (2u * (unsigned)tpf + 1u) + 2u * (unsigned)tl;
+                tab[0] = 0u;
+                tab[1] = 0u;
+            }
         } else if (n0 == 0) {
             // Empty tile: stream the all-zero image; nothing is modified, so no barrier.
             if (kStore == kStorePatch) {
@@ -542,12 +549,20 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
             __syncthreads();
 
             if (kCompact) {
-                // the tile's slots are those of its records: touched cells first, one warp per cell
+                // The sweep's list is CONTIGUOUS: a tile takes nd consecutive slots from the sweep's counter (one atomic
+                // per non-empty tile) and records {first slot, nd} in the sweep's table, so the read-back copies only
+                // touched cells. Inside its range a tile's cells are in ascending order, so the host rebuilds the view
+                // in one linear walk (host_expand.cu, expand_sorted): a bit per cell "touched" (a finished density
+                // is > 0), a cell's slot = the touched cells below it.
                 unsigned *out_idx = compact + (size_t)f * compact_cap * ((unsigned)planes + 1u);
                 unsigned *out_val = out_idx + compact_cap;
-                const unsigned beg = (unsigned)(rec0 - (binned + (size_t)offs.off[f]));
-                // Ascending cell order, so the host rebuilds the view in one linear walk (host_expand.cu, expand_sorted):
-                // a bit per cell "touched" (a finished density is > 0), a cell's slot = the touched cells below it.
+                unsigned *tab = compact_table + (size_t)f * (2u * (unsigned)tpf + 1u);
+                __shared__ unsigned compact_base;
+                if (tid == 0) {
+                    compact_base = atomicAdd(tab + 2u * (unsigned)tpf, (unsigned)nd);
+                    tab[2 * tl] = compact_base;
+                    tab[2 * tl + 1] = (unsigned)nd;
+                }
                 const int nwords = (T + 31) >> 5;
                 for (int c = tid; c < nwords * 32; c += kTileThreads) {  // whole warps: c - lane is warp-uniform
                     const bool touched = c < T && img[c * planes + zn + 1] != 0u;
@@ -555,6 +570,7 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                     if (lane == 0) occ_tile[c >> 5] = bits;
                 }
                 __syncthreads();
+                const unsigned beg = compact_base;
                 for (int d = warp; d < nd; d += kWarps) {
                     const unsigned local = dirty[d];
                     unsigned below = 0;
@@ -566,12 +582,10 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
 #pragma unroll
                     for (int o = 16; o > 0; o >>= 1) below += __shfl_xor_sync(0xFFFFFFFFu, below, o);
                     const unsigned slot = beg + below;
-                    if (slot >= compact_cap) continue;  // cap >= points of the sweep: cannot happen, never overrun
+                    if (slot >= compact_cap) continue;  // cap >= points of the sweep >= touched cells: never overrun
                     if (lane == 0) out_idx[slot] = (unsigned)cell0 + local;
                     for (int k = lane; k < planes; k += 32) out_val[(size_t)slot * planes + k] = img[local * planes + k];
                 }
-                for (int d = nd + tid; d < n0; d += kTileThreads)
-                    if (beg + (unsigned)d < compact_cap) out_idx[beg + (unsigned)d] = kNoCell;
             } else if (kStore == kStorePatch) {
                 for (int d = warp; d < nd; d += kWarps) {  // one warp per touched cell: its planes are contiguous
                     const unsigned local = dirty[d];
@@ -650,9 +664,10 @@ __global__ void __launch_bounds__(kTileThreads, MV3D_TILE_MIN_BLOCKS)
 tile_compact_kernel(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_off,
                   const __grid_constant__ FrameOffsets offs,
                     const __grid_constant__ ViewParams p, const float *__restrict__ lut, int total_tiles,
-                    unsigned *__restrict__ compact, unsigned compact_cap)
+                    unsigned *__restrict__ compact, unsigned compact_cap, unsigned *__restrict__ compact_table)
 {
-    tile_body<true, false, kPy>(binned, tile_off, offs, p, lut, nullptr, total_tiles, compact, compact_cap);
+    tile_body<true, false, kPy>(binned, tile_off, offs, p, lut, nullptr, total_tiles, compact, compact_cap, OccupancySink(),
+                                compact_table);
 }
 
 
@@ -1026,12 +1041,13 @@ int launch_tile_patch(const uint4 *binned, const unsigned *tile_off, const Frame
 
 int launch_tile_compact(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                         const float *lut, int batch, int grid_blocks, unsigned *compact, unsigned compact_cap,
-                        cudaStream_t s)
+                        unsigned *compact_table, cudaStream_t s)
 {
     const int total = batch * p.tiles_per_frame;
     const int grid = grid_blocks < total ? grid_blocks : total;
     auto kernel = p.py ? tile_compact_kernel<true> : tile_compact_kernel<false>;
-    launch_after(kernel, dim3(grid), dim3(kTileThreads), tile_smem_bytes(p), s, binned, tile_off, offs, p, lut, total, compact, compact_cap);
+    launch_after(kernel, dim3(grid), dim3(kTileThreads), tile_smem_bytes(p), s, binned, tile_off, offs, p, lut, total, compact, compact_cap,
+                 compact_table);
     return 1;
 }
 

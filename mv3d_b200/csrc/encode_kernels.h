@@ -36,7 +36,7 @@ int launch_tile_build(const uint4 *binned, const unsigned *tile_off, const Frame
                       const OccupancySink *sink = nullptr);
 int launch_tile_compact(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                         const float *lut, int batch, int grid_blocks, unsigned *compact, unsigned compact_cap,
-                        cudaStream_t s);
+                        unsigned *compact_table, cudaStream_t s);
 int launch_tile_patch(const uint4 *binned, const unsigned *tile_off, const FrameOffsets &offs, const ViewParams &p,
                       const float *lut, float *top, int batch, int grid_blocks, cudaStream_t s);
 // SORT strategy (sort_strategy.cu)

@@ -352,12 +352,13 @@ void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const 
 }
 
 // ---- expand_sorted: the rebuild as ONE linear walk ---------------------------------------------------------------
-// The tile kernel reports a tile's touched cells in ascending cell order, so the whole list is ascending once the
-// unused slots are skipped: a part (a run of whole tiles = a contiguous byte range of the destination) walks its
-// entries front to back, streams zeros over the gaps and composes only the few 64-byte lines a cell (or a run of
-// neighbouring cells) touches in a small window. No sorting, no per-block tables, every byte written once.
+// The tile kernel reports a tile's touched cells in ascending cell order in a range of the list that the tile table
+// names ({first entry, entries} per tile), so a part (a run of whole tiles = a contiguous byte range of the
+// destination) walks its tiles' entries front to back, streams zeros over the gaps and composes only the few 64-byte
+// lines a cell (or a run of neighbouring cells) touches in a small window. No sorting, no per-block tables, every byte
+// written once.
 void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                   unsigned n, const unsigned *tile_off, int tiles, int tile_cells,
+                   unsigned n, const unsigned *table, int tiles, int tile_cells,
                    const std::function<void()> *caller_first)
 {
     if (!dst || cells == 0 || planes <= 0) {
@@ -366,8 +367,8 @@ void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const u
     }
     constexpr size_t kWin = 1024;  // window of composed lines; a cell must fit with a line to spare on either side
     const size_t cell_bytes = (size_t)planes * 4;
-    if (!tile_off || tiles <= 0 || tile_cells <= 0 || cell_bytes + 192 > kWin) {  // no tile order / very deep grids
-        expand_compact(pool, dst, cells, planes, idx, vals, n, tile_off, tiles, tile_cells, caller_first);
+    if (!table || tiles <= 0 || tile_cells <= 0 || cell_bytes + 192 > kWin) {  // no tile table / very deep grids
+        expand_compact(pool, dst, cells, planes, idx, vals, n, nullptr, 0, 0, caller_first);
         return;
     }
     // Parts are claimed dynamically; several per thread, so that the caller's errand and a slow core cost a fraction
@@ -391,13 +392,13 @@ void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const u
         bool open = false;
         size_t floor_cell = c0;     // the next accepted cell must be >= this: ascending order, and memory safety
         for (size_t t = t0; t < t1; t++) {
-            unsigned i = tile_off[t] < n ? tile_off[t] : n;
-            const unsigned i1 = tile_off[t + 1] < n ? tile_off[t + 1] : n;
+            unsigned i = table[2 * t] < n ? table[2 * t] : n;
+            const unsigned i1 = (table[2 * t + 1] < n - i) ? i + table[2 * t + 1] : n;
             if (floor_cell < t * (size_t)tile_cells) floor_cell = t * (size_t)tile_cells;
             const size_t tile_end = ((t + 1) * (size_t)tile_cells < c1) ? (t + 1) * (size_t)tile_cells : c1;
             for (; i < i1; i++) {
                 const size_t cell = idx[i];
-                if (cell >= cells) break;                            // first unused slot: the tile is done
+                if (cell >= cells) break;                            // not a cell: the tile's range ends here
                 if (cell < floor_cell || cell >= tile_end) continue; // out of contract: never written
                 floor_cell = cell + 1;
 #ifdef MV3D_HAVE_NT_STORES

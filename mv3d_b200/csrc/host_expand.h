@@ -54,11 +54,12 @@ void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const 
                     unsigned n, const unsigned *tile_off = nullptr, int tiles = 0, int tile_cells = 0,
                     const std::function<void()> *caller_first = nullptr);
 
-// The same, for a list whose tiles report their touched cells in ASCENDING cell order followed by unused slots (what
-// tile_compact_kernel writes): one linear walk per part, no sorting. An entry that breaks the order or leaves its
-// part's cell range is skipped, never written out of range. Without tile_off it falls back to expand_compact.
+// The same, for the list tile_compact_kernel writes: tile t (tile_cells consecutive cells) owns the entries
+// [table[2t], table[2t] + table[2t + 1]), in ASCENDING cell order. One linear walk per part, no sorting. An entry that
+// breaks the order or leaves its tile's cell range is skipped, never written out of range; ranges are clamped to n.
+// Without a table it falls back to expand_compact.
 void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                   unsigned n, const unsigned *tile_off, int tiles, int tile_cells,
+                   unsigned n, const unsigned *table, int tiles, int tile_cells,
                    const std::function<void()> *caller_first = nullptr);
 
 // The same result in two steps, for a call that has nothing else to overlap with (one sweep per call, the reference

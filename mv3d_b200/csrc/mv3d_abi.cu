@@ -139,6 +139,7 @@ extern "C" void mv3d_ctx_destroy(mv3d_ctx *ctx)
         release(s.ws);
         release(s.points); release(s.top); release(s.front);
         release(s.compact);
+        release(s.ctable);
         if (s.stage.ptr) cudaFreeHost(s.stage.ptr);
         if (s.front_stage.ptr) cudaFreeHost(s.front_stage.ptr);
         if (s.toff_stage.ptr) cudaFreeHost(s.toff_stage.ptr);
@@ -432,7 +433,7 @@ static int enqueue_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_dev, 
         if (compact) {  // host read-back: report the touched cells only (single sweep per call)
             timed_launch(ctx, K_TILE_COMPACT, s, [&] {
                 return launch_tile_compact(binned, toff, offs, p, ctx->lut, batch, grid_blocks, compact->entries,
-                                           compact->cap, s);
+                                           compact->cap, compact->table, s);
             });
         } else {
             timed_launch(ctx, K_TILE_BUILD, s, [&] {
@@ -600,10 +601,10 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
     const size_t cells = (size_t)p.xn * p.yn;
     const size_t front_floats = pyfp ? (size_t)pyfp->pixels * 3 : (size_t)p.front_frame_floats;
     const size_t front_bytes = front_floats * 4;
-    const size_t toff_words = (size_t)p.tiles_per_frame + 1;
+    const size_t toff_words = 2 * (size_t)p.tiles_per_frame + 1;  // the tile table {first entry, entries} + the entry counter
 
-    // Layout of the list on both sides: cell indices [cap], then values [cap][planes], cap = points of the sweep.
-    // Slots follow the sweep's bin offsets (tile_off), so only the first tile_off[tiles] slots are in use.
+    // Layout of the list on both sides: cell indices [cap], then values [cap][planes], cap = points of the sweep. The
+    // touched cells are contiguous from entry 0 (tile by tile in the order the tiles finished; the table says where).
     auto enqueue = [&](int i) -> int {
         HostSlot &slot = ctx->slots[i % kSlots];
         if (!slot.stream) CUDA_TRY(cudaStreamCreateWithFlags(&slot.stream, cudaStreamNonBlocking));
@@ -615,6 +616,7 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         if (ensure(slot.points, (size_t)n * 16 + 16, false, s)) return -1;
         if (ensure(slot.compact, list_bytes, false, s)) return -1;
         if (ensure_pinned(slot.stage, list_bytes)) return -1;
+        if (ensure(slot.ctable, toff_words * 4, false, s)) return -1;
         if (ensure_pinned(slot.toff_stage, toff_words * 4)) return -1;
         if (front_host) {
             if (ensure(slot.front, front_bytes + 16, false, s)) return -1;
@@ -628,6 +630,8 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         CompactOut out;
         out.entries = static_cast<unsigned *>(slot.compact.ptr);
         out.cap = (unsigned)cap;
+        out.table = static_cast<unsigned *>(slot.ctable.ptr);
+        CUDA_TRY(cudaMemsetAsync(out.table + 2 * (size_t)p.tiles_per_frame, 0, 4, s));  // the sweep's entry counter
         float *front_d = front_host ? static_cast<float *>(slot.front.ptr) : nullptr;
         // `top` only has to be non-NULL here: the compact kernel never dereferences it
         const float *pts_d = static_cast<const float *>(slot.points.ptr);
@@ -635,7 +639,7 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         if (pyfp ? py_encode_dev_locked(ctx, slot.ws, pts_d, local_off, 1, top_stub, front_d, p, *pyfp, s, nullptr, &out)
                  : encode_dev_locked(ctx, slot.ws, pts_d, local_off, 1, top_stub, front_d, p, MV3D_STRATEGY_TILE, s, &out))
             return -1;
-        CUDA_TRY(cudaMemcpyAsync(slot.toff_stage.ptr, slot.ws.tile_off.ptr, toff_words * 4, cudaMemcpyDeviceToHost, s));
+        CUDA_TRY(cudaMemcpyAsync(slot.toff_stage.ptr, slot.ctable.ptr, toff_words * 4, cudaMemcpyDeviceToHost, s));
         // Speculative copy sized from the previous sweep (first sweep: every slot); topped up later if short.
         size_t guess = ctx->compact_est ? (size_t)ctx->compact_est + ctx->compact_est / 4 + 1024 : cap;
         if (guess > cap) guess = cap;
@@ -676,8 +680,8 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         t_wait += now() - t0;
         const size_t cap = slot.cap;
         const unsigned *toff = static_cast<const unsigned *>(slot.toff_stage.ptr);
-        const unsigned used = toff[p.tiles_per_frame];  // = points that passed the gate
-        if (used > cap) return fail("compact read-back: %u slots in use, capacity %zu", used, cap);
+        const unsigned used = toff[2 * (size_t)p.tiles_per_frame];  // = touched cells of the sweep
+        if (used > cap) return fail("compact read-back: %u entries, capacity %zu", used, cap);
         unsigned *stage = static_cast<unsigned *>(slot.stage.ptr), *dev = static_cast<unsigned *>(slot.compact.ptr);
         if (used > slot.copied) {  // the guess was short: fetch the rest
             const size_t more = used - slot.copied;
@@ -857,7 +861,7 @@ static int enqueue_py_chunk(mv3d_ctx *ctx, Workspace &ws, const float *points_de
         if (compact)  // host read-back: report the touched cells only (single sweep per call)
             timed_launch(ctx, K_TILE_COMPACT, s, [&] {
                 return launch_tile_compact(binned, toff, offs, p, ctx->lut_py, batch, blocks_per_sm * ctx->sm_count,
-                                           compact->entries, compact->cap, s);
+                                           compact->entries, compact->cap, compact->table, s);
             });
         else
             timed_launch(ctx, K_TILE_BUILD, s, [&] {
@@ -1174,15 +1178,15 @@ extern "C" int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, c
     return 0;
 }
 
-// The linear-walk rebuild the host entry points use: idx / vals / tile_off laid out as tile_compact_kernel writes them
-// (tile t owns the slots [tile_off[t], tile_off[t + 1]); its touched cells first, ascending, then unused slots).
+// The linear-walk rebuild the host entry points use: idx / vals / table laid out as tile_compact_kernel writes them
+// (tile t owns the entries [table[2t], table[2t] + table[2t + 1]), ascending cells).
 extern "C" int mv3d_debug_expand_sorted(float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                                        unsigned n, const unsigned *tile_off, int tiles, int tile_cells, int threads)
+                                        unsigned n, const unsigned *table, int tiles, int tile_cells, int threads)
 {
-    if (!dst || planes <= 0 || (n && (!idx || !vals)) || !tile_off || tiles <= 0 || tile_cells <= 0)
+    if (!dst || planes <= 0 || (n && (!idx || !vals)) || !table || tiles <= 0 || tile_cells <= 0)
         return fail("mv3d_debug_expand_sorted: bad arguments");
     HostPool pool(threads);
-    expand_sorted(pool, dst, cells, planes, idx, vals, n, tile_off, tiles, tile_cells, nullptr);
+    expand_sorted(pool, dst, cells, planes, idx, vals, n, table, tiles, tile_cells, nullptr);
     return 0;
 }
 

@@ -54,22 +54,32 @@ def test_expand_preserves_nan_and_bit_patterns(encoder_lib):
 
 
 def _sorted_list(rng, cells, planes, tile_cells, fill, spare):
-    """A list laid out as tile_compact_kernel writes it: per tile its touched cells ascending, then unused slots."""
+    """A list laid out as tile_compact_kernel writes it: every tile's touched cells ascending in a range of its own, the
+    ranges in the order the tiles happened to finish (shuffled here), a table {first entry, entries} per tile."""
     tiles = (cells + tile_cells - 1) // tile_cells
     touched = np.sort(rng.choice(cells, size=int(cells * fill), replace=False)) if fill > 0 else np.zeros(0, np.int64)
     per_tile = np.bincount(touched // tile_cells, minlength=tiles)
-    slots = per_tile + rng.integers(0, spare + 1, tiles)  # a tile owns at least as many slots as it has touched cells
-    tile_off = np.zeros(tiles + 1, np.uint32)
-    tile_off[1:] = np.cumsum(slots)
-    n = int(tile_off[-1])
-    idx = np.full(n, 0xFFFFFFFF, np.uint32)
-    vals = rng.random((n, planes), dtype=np.float32) + 0.5  # unused slots carry garbage that must not land anywhere
-    first = np.searchsorted(touched // tile_cells, np.arange(tiles))
-    where = tile_off[touched // tile_cells] + (np.arange(len(touched)) - first[touched // tile_cells])
+    order = rng.permutation(tiles)
+    gaps = rng.integers(0, spare + 1, tiles)  # junk between ranges: never referenced by the table, must land nowhere
+    first = np.zeros(tiles, np.int64)
+    pos = 0
+    for t in order:
+        pos += int(gaps[t])
+        first[t] = pos
+        pos += int(per_tile[t])
+    n = pos + 2
+    table = np.zeros(2 * tiles + 1, np.uint32)
+    table[0:2 * tiles:2] = first
+    table[1:2 * tiles:2] = per_tile
+    table[2 * tiles] = n
+    idx = rng.integers(0, cells, n).astype(np.uint32)  # junk everywhere the table does not point
+    vals = rng.random((n, planes), dtype=np.float32) + 0.5
+    start_of = np.searchsorted(touched // tile_cells, np.arange(tiles))
+    where = first[touched // tile_cells] + (np.arange(len(touched)) - start_of[touched // tile_cells])
     idx[where] = touched
     expect = np.zeros((cells, planes), np.float32)
     expect[touched] = vals[where]
-    return idx, vals, tile_off, tiles, expect
+    return idx, vals, table, tiles, expect
 
 
 @pytest.mark.parametrize("threads", [1, 3, 8])
@@ -81,31 +91,36 @@ def test_expand_sorted_matches_numpy_scatter(encoder_lib, threads, cells, planes
     sparse, dense, every cell touched, one-plane cells, a single tile, cells wider than the compose window (falls back),
     aligned and misaligned destinations; guard floats on both sides stay untouched."""
     rng = np.random.default_rng(cells * 31 + threads)
-    idx, vals, tile_off, tiles, expect = _sorted_list(rng, cells, planes, tile_cells, fill, spare=3)
+    idx, vals, table, tiles, expect = _sorted_list(rng, cells, planes, tile_cells, fill, spare=3)
+    if planes > 200:  # the fallback scatters every entry of the list: give it a list without junk
+        keep = np.concatenate([np.arange(table[2 * t], table[2 * t] + table[2 * t + 1]) for t in range(tiles)]).astype(np.int64)
+        idx, vals = idx[keep].copy(), vals[keep].copy()
+        table[0:2 * tiles:2] = np.concatenate([[0], np.cumsum(table[1:2 * tiles:2])[:-1]])
     for offset in (0, 1, 5, 16):
         buf = np.full(cells * planes + offset + 40, 7.0, dtype=np.float32)
         dst = buf[offset:offset + cells * planes]
         rc = encoder_lib.mv3d_debug_expand_sorted(dst.ctypes.data, cells, planes, idx.ctypes.data, vals.ctypes.data, len(idx),
-                                                  tile_off.ctypes.data, tiles, tile_cells, threads)
+                                                  table.ctypes.data, tiles, tile_cells, threads)
         assert rc == 0
         assert (buf[:offset] == 7.0).all() and (buf[offset + cells * planes:] == 7.0).all()
         assert np.array_equal(dst.reshape(cells, planes).view(np.uint32), expect.view(np.uint32))
 
 
 def test_expand_sorted_never_writes_out_of_contract_entries(encoder_lib):
-    """An entry that breaks the ascending order, repeats a cell or names a cell of another tile is skipped -- the walk
-    never writes outside its own part, whatever the list holds."""
+    """An entry that breaks the ascending order, repeats a cell or names a cell of another tile is skipped, a range that
+    runs past the list is clamped -- the walk never writes outside its own tile, whatever the list and table hold."""
     cells, planes, tile_cells = 64, 5, 16
-    tile_off = np.array([0, 4, 8, 12, 16], np.uint32)
-    idx = np.array([3, 2, 3, 15,   40, 16, 17, 0xFFFFFFFF,   0xFFFFFFFF, 33, 34, 35,   48, 63, 64, 5], np.uint32)
+    #              tile 0: slots 0-3      tile 1: slots 4-7           tile 3: slots 8-11      junk
+    idx = np.array([3, 2, 3, 15,          40, 16, 17, 0xFFFFFFFF,     48, 63, 64, 5,          1, 2, 33, 34], np.uint32)
+    table = np.array([0, 4,   4, 4,   14, 100,   8, 4,   16], np.uint32)  # tile 2: entries 14.. "100 of them" (list has 16)
     vals = (np.arange(16 * planes, dtype=np.float32).reshape(16, planes) + 1)
     expect = np.zeros((cells, planes), np.float32)
-    for slot in (0, 3, 5, 6, 12, 13):  # 2 and the second 3 are out of order; 40 is another tile's; tile 2 starts unused
+    for slot in (0, 3, 5, 6, 8, 9, 14, 15):  # 2 and the second 3 are out of order; 40 is another tile's; 64 is no cell
         expect[idx[slot]] = vals[slot]
     for threads in (1, 4):
         buf = np.full(cells * planes + 16, 9.0, np.float32)
         dst = buf[8:8 + cells * planes]
         assert encoder_lib.mv3d_debug_expand_sorted(dst.ctypes.data, cells, planes, idx.ctypes.data, vals.ctypes.data, 16,
-                                                    tile_off.ctypes.data, 4, tile_cells, threads) == 0
+                                                    table.ctypes.data, 4, tile_cells, threads) == 0
         assert (buf[:8] == 9.0).all() and (buf[8 + cells * planes:] == 9.0).all()
         assert np.array_equal(dst.reshape(cells, planes), expect)

@@ -1,7 +1,7 @@
 // host_rebuild_bench.cu -- the host half of the compact read-back alone, on a realistic entry list, against the plain
 // streaming zero-fill of the same bytes by the same threads. Needs no GPU (pageable memory).
 //   nvcc -O3 -std=c++17 -o /tmp/host_rebuild_bench tools/host_rebuild_bench.cu mv3d_b200/csrc/host_expand.cu -lpthread
-//   /tmp/host_rebuild_bench list.bin [sweeps=16]     (list.bin: u32 n, tiles, tile_cells; tile_off[tiles+1]; idx[n])
+//   /tmp/host_rebuild_bench list.bin [sweeps=16]     (list.bin from tools/host_rebuild_list.py: u32 n, tiles, tile_cells; table[2*tiles+1]; idx[n])
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -19,8 +19,8 @@ int main(int argc, char **argv)
     unsigned hdr[3];
     if (fread(hdr, 4, 3, f) != 3) return 1;
     const unsigned n = hdr[0], tiles = hdr[1], tile_cells = hdr[2];
-    std::vector<unsigned> toff(tiles + 1), idx(n);
-    if (fread(toff.data(), 4, tiles + 1, f) != tiles + 1 || fread(idx.data(), 4, n, f) != n) return 1;
+    std::vector<unsigned> toff(2 * tiles + 1), idx(n);
+    if (fread(toff.data(), 4, 2 * tiles + 1, f) != 2 * tiles + 1 || fread(idx.data(), 4, n, f) != n) return 1;
     fclose(f);
     const size_t cells = 563200; const int planes = 27;
     const int sweeps = argc > 2 ? atoi(argv[2]) : 16;
@@ -41,7 +41,7 @@ int main(int argc, char **argv)
             best_z = std::min(best_z, (now() - t0) / sweeps);
             t0 = now();
             for (int s = 0; s < sweeps; s++)
-                expand_compact(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, toff.data(), (int)tiles, (int)tile_cells, nullptr);
+                expand_compact(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, nullptr, 0, 0, nullptr);
             best_e = std::min(best_e, (now() - t0) / sweeps);
             t0 = now();
             for (int s = 0; s < sweeps; s++) {
