@@ -566,7 +566,8 @@ def run_ours(args):
         threads = int(os.environ.get("MV3D_HOST_THREADS", "0")) or max(2, min(16, cores // max(lws, 1)))
         pin = int(os.environ.get("MV3D_HOST_PIN", "1" if lws > 1 else "0"))
         barrier()
-        fill = _lib.load_library().mv3d_debug_host_fill_gbs(256 << 20, threads, 8, local_rank if pin else 0, lws if pin else 0)
+        fill = _lib.load_library().mv3d_debug_host_fill_buffer_gbs(h_top.ctypes.data, h_top.nbytes, threads, 2,
+                                                                   local_rank if pin else 0, lws if pin else 0)
         fill_all = sum_over_ranks(max(fill, 0.0))
         e2e_value = world * BATCH * args.steps / e2e_s
         fill_used = world * result_bytes * args.steps / e2e_s / 1e9
@@ -580,8 +581,8 @@ def run_ours(args):
                "host_fill_frac": fill_used / fill_all if fill_all > 0 else None,
                "host": {"cpus": cores, "ranks_on_host": lws, "fill_threads_per_rank": threads, "pinned_to_cpu_share": bool(pin),
                         "what": "host_fill_gbs = bytes of finished tensors written into the caller's host buffers per "
-                                "second, all ranks; ceiling = streaming zero-fill of fresh memory by the same threads "
-                                "on all ranks at once (mv3d_debug_host_fill_gbs) -- any implementation that delivers "
+                                "second, all ranks; ceiling = streaming zero-fill of the SAME page-locked result buffers by the "
+                                "same threads on all ranks at once, two passes (mv3d_debug_host_fill_buffer_gbs) -- any implementation that delivers "
                                 "the dense tensor through the CPU is bound by it"},
                "result_checksum": checksum}
         del h_top, h_front, h_pts

@@ -229,6 +229,9 @@ int mv3d_front_view_noalloc(const float *points_dev, const int *offsets_host, in
  * share `pin_share_index` of `pin_sharers` of this process's CPUs, as the host entry points do under torchrun.
  * Returns < 0 on failure. */
 double mv3d_debug_host_fill_gbs(size_t bytes, int threads, int reps, int pin_share_index, int pin_sharers);
+/* The same on a buffer of the caller's (it is overwritten with zeros): the rate at which THAT memory -- e.g. the
+ * page-locked tensor an end-to-end run just received -- takes streaming stores from `threads` threads. */
+double mv3d_debug_host_fill_buffer_gbs(float *dst, size_t bytes, int threads, int reps, int pin_share_index, int pin_sharers);
 
 /* The strategy a request resolves to for a parameter set (tile strategies fall back to _ATOMIC when a tile
  * cannot fit shared memory). AUTO is refined per call: _ATOMIC for device calls of up to four sweeps or when the points

@@ -1227,6 +1227,22 @@ extern "C" double mv3d_debug_host_fill_gbs(size_t bytes, int threads, int reps, 
     return best;
 }
 
+// The same measurement on a buffer of the caller's -- bench.py hands over the very host tensor its end-to-end leg just
+// filled (page-locked, 4 KiB pages, already touched), so ceiling and achieved rate are measured on the same memory.
+extern "C" double mv3d_debug_host_fill_buffer_gbs(float *dst, size_t bytes, int threads, int reps, int pin_share_index,
+                                                  int pin_sharers)
+{
+    if (!dst || bytes < 4096 || threads < 1 || reps < 1) { fail("mv3d_debug_host_fill_buffer_gbs: bad arguments"); return -1.0; }
+    std::vector<int> cpus;
+    if (pin_sharers > 0) cpus = host_cpu_share(pin_share_index, pin_sharers);
+    HostPool pool(threads, cpus);
+    zero_fill(pool, dst, (64u << 20) / 4 < bytes / 4 ? (64u << 20) / 4 : bytes / 4);  // wake the pool up
+    const auto t0 = std::chrono::steady_clock::now();
+    for (int r = 0; r < reps; r++) zero_fill(pool, dst, bytes / 4);
+    const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+    return sec > 0 ? (double)bytes * reps / sec / 1e9 : 0.0;
+}
+
 // ------------------------------------------------------------------------------------------------
 // the reference symbols
 // ------------------------------------------------------------------------------------------------
