@@ -239,8 +239,7 @@ void scatter_compact(HostPool &pool, float *dst, size_t cells, int planes, const
 }
 
 void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                    unsigned n, const unsigned *tile_off, int tiles, int tile_cells,
-                    const std::function<void()> *caller_first)
+                    unsigned n, const std::function<void()> *caller_first)
 {
     if (!dst || cells == 0 || planes <= 0) {
         if (caller_first) (*caller_first)();
@@ -256,32 +255,15 @@ void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const 
 #define MV3D_EXPAND_BLOCK 256
 #endif
     constexpr uintptr_t kBlock = MV3D_EXPAND_BLOCK;
-    // With tile_off (the list is ordered by tile: tile t owns the entries [tile_off[t], tile_off[t + 1])) a part is
-    // a run of whole tiles and looks only at its own entries; without it every part filters the whole list.
+    // The list is in no particular order: every part filters the whole list for its own cells.
     const int parts = pool.size() * 2;
-    const bool by_tile = tile_off && tiles > 0 && tile_cells > 0;
-    const size_t tiles_per_part = by_tile ? ((size_t)tiles + parts - 1) / parts : 0;
-    const size_t per = by_tile ? tiles_per_part * (size_t)tile_cells : (cells + parts - 1) / parts;
+    const size_t per = (cells + parts - 1) / parts;
     const size_t cell_bytes = (size_t)planes * 4;
     const std::function<void(int)> body = [&](int part) {
         const size_t c0 = (size_t)part * per;
         if (c0 >= cells) return;
         const size_t c1 = (c0 + per < cells) ? c0 + per : cells;
-        unsigned i0 = 0, i1 = n;  // the entries this part has to look at
-        if (by_tile) {
-            const size_t t0 = (size_t)part * tiles_per_part;
-            const size_t t1 = (t0 + tiles_per_part < (size_t)tiles) ? t0 + tiles_per_part : (size_t)tiles;
-            i0 = tile_off[t0] < n ? tile_off[t0] : n;
-            i1 = tile_off[t1] < n ? tile_off[t1] : n;
-#ifdef MV3D_HAVE_NT_STORES
-            // The values were just written by the GPU's DMA, so they are in no cache, and they are consumed below
-            // in block order, not list order: pull this part's (contiguous) slice in now, while the counting sort
-            // runs, instead of paying one memory round trip per cell later.
-            const char *pf0 = reinterpret_cast<const char *>(vals + (size_t)i0 * planes);
-            const char *pf1 = reinterpret_cast<const char *>(vals + (size_t)i1 * planes);
-            for (const char *q = pf0; q < pf1; q += 64) _mm_prefetch(q, _MM_HINT_T1);
-#endif
-        }
+        const unsigned i0 = 0, i1 = n;
         char *const base = reinterpret_cast<char *>(dst);
         if (cell_bytes > kBlock / 2) {  // very deep grids: plain zero-fill, then scatter (a cell may span several blocks)
             zero_stream(base + c0 * cell_bytes, (c1 - c0) * cell_bytes);
@@ -368,7 +350,7 @@ void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const u
     constexpr size_t kWin = 1024;  // window of composed lines; a cell must fit with a line to spare on either side
     const size_t cell_bytes = (size_t)planes * 4;
     if (!table || tiles <= 0 || tile_cells <= 0 || cell_bytes + 192 > kWin) {  // no tile table / very deep grids
-        expand_compact(pool, dst, cells, planes, idx, vals, n, nullptr, 0, 0, caller_first);
+        expand_compact(pool, dst, cells, planes, idx, vals, n, caller_first);
         return;
     }
     // Parts are claimed dynamically; several per thread, so that the caller's errand and a slow core cost a fraction

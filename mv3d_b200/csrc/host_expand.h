@@ -46,13 +46,11 @@ private:
 // number `index`. One process per GPU under torchrun: sharers = LOCAL_WORLD_SIZE, index = LOCAL_RANK.
 std::vector<int> host_cpu_share(int index, int sharers);
 
-// dst[cells][planes] = 0 except dst[idx[i]][:] = vals[i][:] for the n entries (a cell appears at most once).
-// Entries with a cell index >= cells (kNoCell marks an unused slot) are ignored. The destination is written once,
-// with streaming stores. If the list is ordered by tile -- tile t (tile_cells consecutive cells) owns the entries
-// [tile_off[t], tile_off[t + 1]) -- pass tile_off/tiles/tile_cells and every thread reads only its own entries.
+// dst[cells][planes] = 0 except dst[idx[i]][:] = vals[i][:] for the n entries (a cell appears at most once, in any
+// order). Entries with a cell index >= cells are ignored. The destination is written once, with streaming stores: every
+// thread filters the list for its own cell range and groups its entries by 256-byte destination block (counting sort).
 void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                    unsigned n, const unsigned *tile_off = nullptr, int tiles = 0, int tile_cells = 0,
-                    const std::function<void()> *caller_first = nullptr);
+                    unsigned n, const std::function<void()> *caller_first = nullptr);
 
 // The same, for the list tile_compact_kernel writes: tile t (tile_cells consecutive cells) owns the entries
 // [table[2t], table[2t] + table[2t + 1]), in ASCENDING cell order. One linear walk per part, no sorting. An entry that

@@ -1174,7 +1174,7 @@ extern "C" int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, c
         memcpy(vals.data() + (size_t)i * planes, entries + (size_t)i * (planes + 1) + 1, (size_t)planes * 4);
     }
     HostPool pool(threads);
-    expand_compact(pool, dst, cells, planes, idx.data(), vals.data(), n, nullptr, 0, 0, nullptr);
+    expand_compact(pool, dst, cells, planes, idx.data(), vals.data(), n, nullptr);
     return 0;
 }
 

@@ -24,7 +24,7 @@ int main(int argc, char **argv)
         for (unsigned nn : {0u, n}) {
             for (int rep = 0; rep < 2; rep++) {
                 double t0 = now();
-                for (int s = 0; s < sweeps; s++) expand_compact(pool, dst + (size_t)s * cells * planes, cells, planes, idx.data(), vals.data(), nn, nullptr, 0, 0, nullptr);
+                for (int s = 0; s < sweeps; s++) expand_compact(pool, dst + (size_t)s * cells * planes, cells, planes, idx.data(), vals.data(), nn, nullptr);
                 double dt = (now() - t0) / sweeps;
                 if (rep) printf("threads=%d entries=%u: %.3f ms/sweep  %.1f GB/s\n", threads, nn, dt * 1e3, cells * planes * 4 / dt / 1e9);
             }

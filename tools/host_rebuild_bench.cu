@@ -41,7 +41,7 @@ int main(int argc, char **argv)
             best_z = std::min(best_z, (now() - t0) / sweeps);
             t0 = now();
             for (int s = 0; s < sweeps; s++)
-                expand_compact(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, nullptr, 0, 0, nullptr);
+                expand_compact(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, nullptr);
             best_e = std::min(best_e, (now() - t0) / sweeps);
             t0 = now();
             for (int s = 0; s < sweeps; s++) {
