@@ -193,19 +193,16 @@ int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int num, const
 int mv3d_frame_checksums_dev(mv3d_ctx *ctx, const float *views_dev, int frames, long long floats_per_frame,
                              unsigned long long *sums_dev, void *stream);
 
-/* Test hook (no GPU needed): the host half of the compact read-back used by the host-buffer entry points.
- * dst[cells][planes] is zero-filled by `threads` host threads, then every entry {cell, planes values}
- * (planes + 1 words each) is copied to dst[cell]; entries with cell >= cells are ignored. */
-int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n, int threads);
-/* Same result in the two steps the first sweep of a host call takes (zero-fill while the GPU encodes, then a scatter
- * of the finished values). */
-int mv3d_debug_expand_split(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n, int threads);
-/* The form the host entry points run: the list as the compact tile kernel writes it -- cell indices idx[n] and values
- * vals[n][planes] in separate arrays, tile t (tile_cells consecutive cells) owning the entries
- * [table[2t], table[2t] + table[2t+1]) in ascending cell order. One linear walk per thread; an entry out of order or
- * out of its tile's cell range is skipped, never written; ranges are clamped to n. */
-int mv3d_debug_expand_sorted(float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals, unsigned n,
+/* Test hooks (no GPU needed): the host half of the compact read-back used by the host-buffer entry points. `words` is
+ * what the compact tile kernel reports for one sweep -- per touched cell {cell index, ceil(planes / 32) plane masks, the
+ * values of the planes whose bit is set} -- and `table` holds {first word, touched cells} per tile (tile t = tile_cells
+ * consecutive cells, its cells in ascending order). dst[cells][planes] is rebuilt by `threads` host threads: _sorted in
+ * one pass of streaming stores (what every sweep but the first of a call takes), _split as zero-fill + scatter (the
+ * first sweep: the fill overlaps the GPU's work). Whatever words/table hold, nothing is written outside dst. */
+int mv3d_debug_expand_sorted(float *dst, size_t cells, int planes, const unsigned *words, unsigned n_words,
                              const unsigned *table, int tiles, int tile_cells, int threads);
+int mv3d_debug_expand_split(float *dst, size_t cells, int planes, const unsigned *words, unsigned n_words,
+                            const unsigned *table, int tiles, int tile_cells, int threads);
 
 /* NO COUNTERPART IN THE REFERENCE -- added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).

@@ -48,9 +48,9 @@ struct PinnedBuffer {
 
 // Where the compact variant of the tile kernel reports the touched cells of ONE sweep (device memory).
 struct CompactOut {
-    unsigned *entries = nullptr;  // cell indices [cap], then values [cap][planes]: the sweep's touched cells, contiguous
-    unsigned cap = 0;             // >= points of the sweep
-    unsigned *table = nullptr;    // {first entry, entries} per tile, then the sweep's entry counter (zeroed before the launch)
+    unsigned *entries = nullptr;  // the sweep's stream of words: per touched cell {index, plane masks, non-zero values}
+    unsigned cap = 0;             // its capacity in words: >= points x (planes + 1 + ceil(planes / 32))
+    unsigned *table = nullptr;    // {first word, touched cells} per tile, then the sweep's word counter (zeroed before the launch)
 };
 
 // Empty-anchor filter (anchor_abi.cu): the anchor set stays resident, scratch grows on demand.
@@ -74,8 +74,8 @@ struct HostSlot {
     DeviceBuffer compact, ctable;  // the sweep's touched cells; its tile table + entry counter
     PinnedBuffer stage, front_stage, toff_stage;  // toff_stage receives the tile table
     cudaEvent_t done = nullptr;
-    unsigned copied = 0;          // entries already copied to `stage` by the speculative D2H
-    unsigned cap = 0;             // entry capacity of the sweep in flight (indices [cap], then values [cap][planes])
+    unsigned copied = 0;          // words already copied to `stage` by the speculative D2H
+    unsigned cap = 0;             // capacity in words of the stream of the sweep in flight
 };
 
 // Kernel classes, in the order mv3d_kernel_name() reports them.

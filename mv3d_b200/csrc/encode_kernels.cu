@@ -369,12 +369,11 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
 // tile first waits for those in-flight reads of the image before accumulating into it.
 // ------------------------------------------------------------------------------------------------
 // kCompact: instead of storing the dense tile, report the touched cells in a per-sweep list
-//   compact[f] = { cell index [cap] , values [cap][planes] }   (structure of arrays)
-//   table[f]   = { first slot, touched cells } per tile, then the sweep's slot counter (zeroed by the caller)
-// A non-empty tile takes as many consecutive slots as it touched cells from the sweep's counter and fills them in
-// ASCENDING cell order; the list is contiguous (touched cells of the sweep <= its points <= cap), and the table tells
-// the reader where each tile's cells are. This is what the host-buffer path reads back over PCIe instead of the
-// 95 %-zero dense tensor.
+//   compact[f] = one stream of words: per touched cell { cell index, plane masks, non-zero values } (compact_cap words)
+//   table[f]   = { first word, touched cells } per tile, then the sweep's word counter (zeroed by the caller)
+// A non-empty tile takes the words of its touched cells from the sweep's counter and writes them in ASCENDING cell
+// order; the stream is contiguous and holds finished non-zero values only, and the table tells the reader where each
+// tile's cells are. This is what the host-buffer path reads back over PCIe instead of the 95 %-zero dense tensor.
 // kOccupancy (dense output only): also report, for the empty-anchor filter that consumes the view next
 // (anchor_kernels.cu), one bit per cell "touched" -- touched cells carry a density > 0, untouched cells are all
 // zero -- into a pre-zeroed per-frame bit map, and raise the frame's flag when an intensity is negative, -0 or NaN
@@ -549,42 +548,66 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
             __syncthreads();
 
             if (kCompact) {
-                // The sweep's list is CONTIGUOUS: a tile takes nd consecutive slots from the sweep's counter (one atomic
-                // per non-empty tile) and records {first slot, nd} in the sweep's table, so the read-back copies only
-                // touched cells. Inside its range a tile's cells are in ascending order, so the host rebuilds the view
-                // in one linear walk (host_expand.cu, expand_sorted): a bit per cell "touched" (a finished density
-                // is > 0), a cell's slot = the touched cells below it.
-                unsigned *out_idx = compact + (size_t)f * compact_cap * ((unsigned)planes + 1u);
-                unsigned *out_val = out_idx + compact_cap;
+                // The sweep's list is one stream of 32-bit words, SPARSE and CONTIGUOUS: a touched cell is
+                //   { cell index, plane masks [G = ceil(planes / 32)], the non-zero planes' values in plane order }
+                // (a touched cell of a KITTI sweep has 4-5 non-zero planes of 27). A tile's cells are in ASCENDING order;
+                // the tile takes its words from the sweep's counter (one atomic per non-empty tile) and records
+                // {first word, cells} in the sweep's table, so the read-back copies nothing but finished non-zero values
+                // and the host rebuilds the view in one linear walk (host_expand.cu, expand_sorted).
+                unsigned *out = compact + (size_t)f * compact_cap;
                 unsigned *tab = compact_table + (size_t)f * (2u * (unsigned)tpf + 1u);
+                const int G = (planes + 31) >> 5;
                 __shared__ unsigned compact_base;
-                if (tid == 0) {
-                    compact_base = atomicAdd(tab + 2u * (unsigned)tpf, (unsigned)nd);
-                    tab[2 * tl] = compact_base;
-                    tab[2 * tl + 1] = (unsigned)nd;
-                }
-                const int nwords = (T + 31) >> 5;
-                for (int c = tid; c < nwords * 32; c += kTileThreads) {  // whole warps: c - lane is warp-uniform
-                    const bool touched = c < T && img[c * planes + zn + 1] != 0u;
-                    const unsigned bits = __ballot_sync(0xFFFFFFFFu, touched);
-                    if (lane == 0) occ_tile[c >> 5] = bits;
-                }
-                __syncthreads();
-                const unsigned beg = compact_base;
+                // (1) words per touched cell, left in the cell's (now dead) winner key; untouched cells hold 0
                 for (int d = warp; d < nd; d += kWarps) {
                     const unsigned local = dirty[d];
-                    unsigned below = 0;
-                    for (unsigned w = (unsigned)lane; w <= (local >> 5); w += 32u) {
-                        unsigned bits = occ_tile[w];
-                        if (w == (local >> 5)) bits &= (1u << (local & 31u)) - 1u;
-                        below += (unsigned)__popc(bits);
+                    unsigned words = 1u + (unsigned)G;
+                    for (int g = 0; g < G; g++) {
+                        const int k = g * 32 + lane;
+                        const unsigned v = k < planes ? img[local * planes + k] : 0u;
+                        words += (unsigned)__popc(__ballot_sync(0xFFFFFFFFu, v != 0u));
                     }
+                    if (lane == 0) key[local] = (unsigned long long)words;
+                }
+                __syncthreads();
+                // (2) exclusive prefix over the tile's cells in cell order (one warp), the tile's words from the counter
+                if (warp == 0) {
+                    unsigned carry = 0;
+                    for (int c0 = 0; c0 < T; c0 += 32) {
+                        const int c = c0 + lane;
+                        const unsigned w = c < T ? (unsigned)key[c] : 0u;
+                        unsigned incl = w;
 #pragma unroll
-                    for (int o = 16; o > 0; o >>= 1) below += __shfl_xor_sync(0xFFFFFFFFu, below, o);
-                    const unsigned slot = beg + below;
-                    if (slot >= compact_cap) continue;  // cap >= points of the sweep >= touched cells: never overrun
-                    if (lane == 0) out_idx[slot] = (unsigned)cell0 + local;
-                    for (int k = lane; k < planes; k += 32) out_val[(size_t)slot * planes + k] = img[local * planes + k];
+                        for (int o = 1; o < 32; o <<= 1) {
+                            const unsigned up = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+                            if (lane >= o) incl += up;
+                        }
+                        if (w) key[c] = ((unsigned long long)(carry + incl - w) << 32) | (unsigned long long)w;
+                        carry += __shfl_sync(0xFFFFFFFFu, incl, 31);
+                    }
+                    if (lane == 0) {
+                        compact_base = atomicAdd(tab + 2u * (unsigned)tpf, carry);
+                        tab[2 * tl] = compact_base;
+                        tab[2 * tl + 1] = (unsigned)nd;
+                    }
+                }
+                __syncthreads();
+                // (3) one warp per touched cell writes its entry
+                for (int d = warp; d < nd; d += kWarps) {
+                    const unsigned local = dirty[d];
+                    const unsigned long long kk = key[local];
+                    const unsigned pos = compact_base + (unsigned)(kk >> 32);
+                    if (pos + (unsigned)kk > compact_cap) continue;  // the stream holds every point's worst case: never
+                    if (lane == 0) out[pos] = (unsigned)cell0 + local;
+                    unsigned at = pos + 1u + (unsigned)G;
+                    for (int g = 0; g < G; g++) {
+                        const int k = g * 32 + lane;
+                        const unsigned v = k < planes ? img[local * planes + k] : 0u;
+                        const unsigned m = __ballot_sync(0xFFFFFFFFu, v != 0u);
+                        if (lane == 0) out[pos + 1u + (unsigned)g] = m;
+                        if (v != 0u) out[at + (unsigned)__popc(m & ((1u << lane) - 1u))] = v;
+                        at += (unsigned)__popc(m);
+                    }
                 }
             } else if (kStore == kStorePatch) {
                 for (int d = warp; d < nd; d += kWarps) {  // one warp per touched cell: its planes are contiguous

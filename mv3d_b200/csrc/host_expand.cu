@@ -206,7 +206,7 @@ static void store_fence()
 void zero_fill(HostPool &pool, float *dst, size_t floats)
 {
     if (!dst || floats == 0) return;
-    const int parts = pool.size() * 2;
+    const int parts = pool.size() * 4;
     const size_t bytes = floats * 4;
     const size_t per = ((bytes + parts - 1) / parts + 63) & ~(size_t)63;
     const std::function<void(int)> body = [&](int part) {
@@ -218,141 +218,103 @@ void zero_fill(HostPool &pool, float *dst, size_t floats)
     pool.parallel_for(parts, body);
 }
 
-void scatter_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                     unsigned n, const std::function<void()> *caller_first)
+// ---- the read-back stream ---------------------------------------------------------------------------------------
+// What tile_compact_kernel writes for one sweep: a stream of 32-bit words, per touched cell
+//   { cell index, plane masks [G = ceil(planes / 32)], the values of the planes whose mask bit is set, in plane order }
+// and a table { first word, touched cells } per tile (tile t = tile_cells consecutive cells); a tile's cells are in
+// ASCENDING order. Everything read from the stream is checked before it is used: a cell outside its tile's range or
+// out of order is skipped, an entry that runs past the stream ends its tile -- whatever the stream holds, nothing is
+// written outside the part that owns the tile.
+namespace {
+struct CellEntry {
+    size_t cell;
+    const unsigned *masks;   // G words
+    const unsigned *values;  // the non-zero planes
+    unsigned next;           // first word after this entry
+};
+inline int popcount32(unsigned v) { return __builtin_popcount(v); }
+
+// Decode the entry at word w (false: the stream ends here).
+inline bool read_entry(const unsigned *words, unsigned n_words, unsigned w, int groups, CellEntry &e)
 {
-    if (!dst || cells == 0 || planes <= 0 || n == 0) {
-        if (caller_first) (*caller_first)();
-        return;
-    }
-    const int parts = pool.size() * 2;
-    const unsigned per = (n + parts - 1) / parts;
-    const size_t cell_bytes = (size_t)planes * 4;
-    const std::function<void(int)> body = [&](int part) {  // a cell appears at most once: no two threads share bytes
-        const unsigned i0 = (unsigned)part * per, i1 = (i0 + per < n) ? i0 + per : n;
-        for (unsigned i = i0; i < i1; i++) {
-            const size_t cell = idx[i];
-            if (cell < cells) memcpy(reinterpret_cast<char *>(dst) + cell * cell_bytes, vals + (size_t)i * planes, cell_bytes);
-        }
-    };
-    pool.parallel_for(parts, body, caller_first);
+    if (w >= n_words || n_words - w < 1u + (unsigned)groups) return false;
+    e.cell = words[w];
+    e.masks = words + w + 1;
+    unsigned nnz = 0;
+    for (int g = 0; g < groups; g++) nnz += (unsigned)popcount32(e.masks[g]);
+    if (n_words - w - 1u - (unsigned)groups < nnz) return false;
+    e.values = e.masks + groups;
+    e.next = w + 1u + (unsigned)groups + nnz;
+    return true;
 }
 
-void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                    unsigned n, const std::function<void()> *caller_first)
+// Place the entry's values into a zeroed cell image of `planes` floats (mask bits at or beyond `planes` are ignored).
+inline void place_values(unsigned *cellw, int planes, int groups, const CellEntry &e)
 {
-    if (!dst || cells == 0 || planes <= 0) {
+    const unsigned *v = e.values;
+    for (int g = 0; g < groups; g++) {
+        unsigned m = e.masks[g];
+        while (m) {
+            const int k = g * 32 + __builtin_ctz(m);
+            m &= m - 1u;
+            if (k < planes) cellw[k] = *v;
+            v++;
+        }
+    }
+}
+}  // namespace
+
+// Scatter the stream's values into a destination that is zero already (the second step of the split rebuild).
+void scatter_stream(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *words, unsigned n_words,
+                    const unsigned *table, int tiles, int tile_cells, const std::function<void()> *caller_first)
+{
+    if (!dst || cells == 0 || planes <= 0 || !table || tiles <= 0 || tile_cells <= 0 || n_words == 0) {
         if (caller_first) (*caller_first)();
         return;
     }
-    // Parts are contiguous cell ranges, so no two threads ever write the same bytes. A part is emitted front to
-    // back in blocks that end on kBlock-byte boundaries of the destination ADDRESS, so every store inside a part is a
-    // whole 64-byte line (only the part's first and last line can be partial). The part's entries are grouped
-    // by the block their first byte falls into (counting sort); runs of untouched blocks are streamed as zeros,
-    // a touched block is composed in a cache-resident buffer (zeros + the finished values) and streamed out.
-    // A cell can straddle a block boundary: its tail is carried into the next block (at most one per boundary).
-#ifndef MV3D_EXPAND_BLOCK
-#define MV3D_EXPAND_BLOCK 256
-#endif
-    constexpr uintptr_t kBlock = MV3D_EXPAND_BLOCK;
-    // The list is in no particular order: every part filters the whole list for its own cells.
-    const int parts = pool.size() * 2;
-    const size_t per = (cells + parts - 1) / parts;
-    const size_t cell_bytes = (size_t)planes * 4;
+    const int groups = (planes + 31) / 32;
+    int parts = pool.size() * 4;
+    if (parts > tiles) parts = tiles;
+    const size_t tiles_per_part = ((size_t)tiles + parts - 1) / parts;
     const std::function<void(int)> body = [&](int part) {
-        const size_t c0 = (size_t)part * per;
-        if (c0 >= cells) return;
-        const size_t c1 = (c0 + per < cells) ? c0 + per : cells;
-        const unsigned i0 = 0, i1 = n;
-        char *const base = reinterpret_cast<char *>(dst);
-        if (cell_bytes > kBlock / 2) {  // very deep grids: plain zero-fill, then scatter (a cell may span several blocks)
-            zero_stream(base + c0 * cell_bytes, (c1 - c0) * cell_bytes);
-            store_fence();
-            for (unsigned i = i0; i < i1; i++) {
-                const size_t cell = idx[i];
-                if (cell >= c0 && cell < c1) memcpy(base + cell * cell_bytes, vals + (size_t)i * planes, cell_bytes);
+        const size_t t0 = (size_t)part * tiles_per_part;
+        const size_t t1 = (t0 + tiles_per_part < (size_t)tiles) ? t0 + tiles_per_part : (size_t)tiles;
+        for (size_t t = t0; t < t1; t++) {
+            const size_t lo = t * (size_t)tile_cells;
+            const size_t hi = (lo + (size_t)tile_cells < cells) ? lo + (size_t)tile_cells : cells;
+            size_t floor_cell = lo;
+            unsigned w = table[2 * t];
+            CellEntry e;
+            for (unsigned c = 0; c < table[2 * t + 1] && read_entry(words, n_words, w, groups, e); c++, w = e.next) {
+                if (e.cell < floor_cell || e.cell >= hi) continue;  // a tile's cells are disjoint from every other tile's
+                floor_cell = e.cell + 1;
+                place_values(reinterpret_cast<unsigned *>(dst) + e.cell * (size_t)planes, planes, groups, e);
             }
-            return;
         }
-        const uintptr_t A0 = reinterpret_cast<uintptr_t>(base + c0 * cell_bytes);  // part = addresses [A0, A1)
-        const uintptr_t A1 = reinterpret_cast<uintptr_t>(base + c1 * cell_bytes);
-        const uintptr_t blk0 = A0 / kBlock;
-        const size_t nblocks = (size_t)((A1 - 1) / kBlock - blk0 + 1);
-        auto block_of = [&](size_t cell) { return (size_t)(reinterpret_cast<uintptr_t>(base + cell * cell_bytes) / kBlock - blk0); };
-
-        static thread_local std::vector<unsigned> first, cursor, order;  // first[b] .. first[b + 1]: entries of block b
-        static thread_local std::vector<char> block;
-        first.assign(nblocks + 1, 0u);
-        for (unsigned i = i0; i < i1; i++) {
-            const size_t cell = idx[i];
-            if (cell >= c0 && cell < c1) first[block_of(cell) + 1]++;
-        }
-        for (size_t b = 0; b < nblocks; b++) first[b + 1] += first[b];
-        order.resize(first[nblocks]);
-        cursor.assign(first.begin(), first.end() - 1);
-        if (first[nblocks])
-            for (unsigned i = i0; i < i1; i++) {
-                const size_t cell = idx[i];
-                if (cell >= c0 && cell < c1) order[cursor[block_of(cell)]++] = i;
-            }
-        block.resize(kBlock);
-
-        uintptr_t zero_from = A0;          // start of the pending run of untouched bytes
-        const char *carry = nullptr;       // tail of a cell that began in the previous block
-        size_t carry_bytes = 0;
-        for (size_t b = 0; b < nblocks; b++) {
-            const uintptr_t lo = (b == 0) ? A0 : (blk0 + b) * kBlock;
-            const uintptr_t hi = ((blk0 + b + 1) * kBlock < A1) ? (blk0 + b + 1) * kBlock : A1;
-            const unsigned e0 = first[b], e1 = first[b + 1];
-            if (e0 == e1 && !carry) continue;  // untouched: stays in the zero run
-            if (lo > zero_from) zero_stream(reinterpret_cast<char *>(zero_from), (size_t)(lo - zero_from));
-            const size_t len = (size_t)(hi - lo);
-            memset(block.data(), 0, len);
-            if (carry) {
-                memcpy(block.data(), carry, carry_bytes);  // carry_bytes < cell_bytes <= a block
-                carry = nullptr;
-            }
-            for (unsigned e = e0; e < e1; e++) {
-                const size_t i = order[e];
-                const uintptr_t at = reinterpret_cast<uintptr_t>(base + (size_t)idx[i] * cell_bytes);
-                const char *src = reinterpret_cast<const char *>(vals + i * planes);
-                size_t take = cell_bytes;
-                if (at + cell_bytes > hi) {  // straddles the block end (the part end is a cell boundary, so b + 1 exists)
-                    take = (size_t)(hi - at);
-                    carry = src + take;
-                    carry_bytes = cell_bytes - take;
-                }
-                memcpy(block.data() + (at - lo), src, take);
-            }
-            copy_stream(reinterpret_cast<char *>(lo), block.data(), len);
-            zero_from = hi;
-        }
-        if (A1 > zero_from) zero_stream(reinterpret_cast<char *>(zero_from), (size_t)(A1 - zero_from));
-        store_fence();
     };
     pool.parallel_for(parts, body, caller_first);
 }
 
 // ---- expand_sorted: the rebuild as ONE linear walk ---------------------------------------------------------------
-// The tile kernel reports a tile's touched cells in ascending cell order in a range of the list that the tile table
-// names ({first entry, entries} per tile), so a part (a run of whole tiles = a contiguous byte range of the
-// destination) walks its tiles' entries front to back, streams zeros over the gaps and composes only the few 64-byte
-// lines a cell (or a run of neighbouring cells) touches in a small window. No sorting, no per-block tables, every byte
-// written once.
-void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                   unsigned n, const unsigned *table, int tiles, int tile_cells,
-                   const std::function<void()> *caller_first)
+// A part (a run of whole tiles = a contiguous byte range of the destination) walks its tiles' entries front to back,
+// streams zeros over the gaps and composes only the few 64-byte lines a cell (or a run of neighbouring cells) touches
+// in a small window. No sorting, no per-block tables, every byte of the destination written once.
+void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *words, unsigned n_words,
+                   const unsigned *table, int tiles, int tile_cells, const std::function<void()> *caller_first)
 {
     if (!dst || cells == 0 || planes <= 0) {
         if (caller_first) (*caller_first)();
         return;
     }
-    constexpr size_t kWin = 1024;  // window of composed lines; a cell must fit with a line to spare on either side
-    const size_t cell_bytes = (size_t)planes * 4;
-    if (!table || tiles <= 0 || tile_cells <= 0 || cell_bytes + 192 > kWin) {  // no tile table / very deep grids
-        expand_compact(pool, dst, cells, planes, idx, vals, n, caller_first);
+    if (!table || tiles <= 0 || tile_cells <= 0) {  // nothing to place
+        if (caller_first) (*caller_first)();
+        zero_fill(pool, dst, cells * (size_t)planes);
         return;
     }
+    constexpr size_t kWin = 1024;  // window of composed lines; a cell must fit with a line to spare on either side
+    const size_t cell_bytes = (size_t)planes * 4;
+    const bool windowed = cell_bytes + 192 <= kWin;  // very deep grids: zero the part, then place the values
+    const int groups = (planes + 31) / 32;
     // Parts are claimed dynamically; several per thread, so that the caller's errand and a slow core cost a fraction
     // of a part, not a whole share.
     int parts = pool.size() * 6;
@@ -368,25 +330,31 @@ void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const u
         char *const base = reinterpret_cast<char *>(dst);
         const uintptr_t A0 = reinterpret_cast<uintptr_t>(base + c0 * cell_bytes);  // this part = addresses [A0, A1)
         const uintptr_t A1 = reinterpret_cast<uintptr_t>(base + c1 * cell_bytes);
+        if (!windowed) {
+            zero_stream(reinterpret_cast<char *>(A0), (size_t)(A1 - A0));
+            store_fence();  // the values below land in the same lines with ordinary stores
+        }
         alignas(64) char win[kWin];
         uintptr_t done = A0;        // [A0, done) has been emitted
         uintptr_t wlo = 0, whi = 0; // the open window holds [wlo, whi), wlo == done; whi is line-aligned or A1
         bool open = false;
         size_t floor_cell = c0;     // the next accepted cell must be >= this: ascending order, and memory safety
         for (size_t t = t0; t < t1; t++) {
-            unsigned i = table[2 * t] < n ? table[2 * t] : n;
-            const unsigned i1 = (table[2 * t + 1] < n - i) ? i + table[2 * t + 1] : n;
             if (floor_cell < t * (size_t)tile_cells) floor_cell = t * (size_t)tile_cells;
             const size_t tile_end = ((t + 1) * (size_t)tile_cells < c1) ? (t + 1) * (size_t)tile_cells : c1;
-            for (; i < i1; i++) {
-                const size_t cell = idx[i];
-                if (cell >= cells) break;                            // not a cell: the tile's range ends here
-                if (cell < floor_cell || cell >= tile_end) continue; // out of contract: never written
-                floor_cell = cell + 1;
+            unsigned w = table[2 * t];
+            CellEntry e;
+            for (unsigned c = 0; c < table[2 * t + 1] && read_entry(words, n_words, w, groups, e); c++, w = e.next) {
+                if (e.cell < floor_cell || e.cell >= tile_end) continue;  // out of contract: never written
+                floor_cell = e.cell + 1;
 #ifdef MV3D_HAVE_NT_STORES
-                _mm_prefetch(reinterpret_cast<const char *>(vals + (size_t)(i + 6) * planes), _MM_HINT_T0);
+                _mm_prefetch(reinterpret_cast<const char *>(words + e.next + 64), _MM_HINT_T0);
 #endif
-                const uintptr_t a = reinterpret_cast<uintptr_t>(base + cell * cell_bytes);
+                const uintptr_t a = reinterpret_cast<uintptr_t>(base + e.cell * cell_bytes);
+                if (!windowed) {
+                    place_values(reinterpret_cast<unsigned *>(a), planes, groups, e);
+                    continue;
+                }
                 uintptr_t end = (a + cell_bytes + 63) & ~(uintptr_t)63;
                 if (end > A1) end = A1;
                 if (open && a <= whi) {                              // touches the window's last line: extend it
@@ -413,14 +381,16 @@ void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const u
                     open = true;
                     memset(win, 0, (size_t)(whi - wlo));
                 }
-                memcpy(win + (a - wlo), vals + (size_t)i * planes, cell_bytes);
+                place_values(reinterpret_cast<unsigned *>(win + (a - wlo)), planes, groups, e);
             }
         }
-        if (open) {
-            copy_stream(reinterpret_cast<char *>(wlo), win, (size_t)(whi - wlo));
-            done = whi;
+        if (windowed) {
+            if (open) {
+                copy_stream(reinterpret_cast<char *>(wlo), win, (size_t)(whi - wlo));
+                done = whi;
+            }
+            if (A1 > done) zero_stream(reinterpret_cast<char *>(done), (size_t)(A1 - done));
         }
-        if (A1 > done) zero_stream(reinterpret_cast<char *>(done), (size_t)(A1 - done));
         store_fence();
     };
     pool.parallel_for(parts, body, caller_first);

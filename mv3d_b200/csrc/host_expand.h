@@ -46,24 +46,20 @@ private:
 // number `index`. One process per GPU under torchrun: sharers = LOCAL_WORLD_SIZE, index = LOCAL_RANK.
 std::vector<int> host_cpu_share(int index, int sharers);
 
-// dst[cells][planes] = 0 except dst[idx[i]][:] = vals[i][:] for the n entries (a cell appears at most once, in any
-// order). Entries with a cell index >= cells are ignored. The destination is written once, with streaming stores: every
-// thread filters the list for its own cell range and groups its entries by 256-byte destination block (counting sort).
-void expand_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                    unsigned n, const std::function<void()> *caller_first = nullptr);
-
-// The same, for the list tile_compact_kernel writes: tile t (tile_cells consecutive cells) owns the entries
-// [table[2t], table[2t] + table[2t + 1]), in ASCENDING cell order. One linear walk per part, no sorting. An entry that
-// breaks the order or leaves its tile's cell range is skipped, never written out of range; ranges are clamped to n.
-// Without a table it falls back to expand_compact.
-void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                   unsigned n, const unsigned *table, int tiles, int tile_cells,
-                   const std::function<void()> *caller_first = nullptr);
+// The dense view dst[cells][planes] from what tile_compact_kernel reports for one sweep (see the layout at the top of
+// the stream section in host_expand.cu): `words` is the stream of n_words 32-bit words -- per touched cell its index,
+// ceil(planes / 32) plane masks and the values of the planes whose bit is set -- and `table` holds
+// {first word, touched cells} per tile (tile t = tile_cells consecutive cells, its cells in ascending order).
+// The destination is written exactly once, front to back, with streaming stores: one linear walk per part, no sorting.
+// Whatever the stream and table hold, nothing is written outside dst: out-of-range or out-of-order cells are skipped,
+// entries past the end of the stream end their tile.
+void expand_sorted(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *words, unsigned n_words,
+                   const unsigned *table, int tiles, int tile_cells, const std::function<void()> *caller_first = nullptr);
 
 // The same result in two steps, for a call that has nothing else to overlap with (one sweep per call, the reference
-// symbols): zero_fill runs while the GPU is still encoding, scatter_compact places the finished values afterwards.
+// symbols): zero_fill runs while the GPU is still encoding, scatter_stream places the finished values afterwards.
 void zero_fill(HostPool &pool, float *dst, size_t floats);
-void scatter_compact(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                     unsigned n, const std::function<void()> *caller_first = nullptr);
+void scatter_stream(HostPool &pool, float *dst, size_t cells, int planes, const unsigned *words, unsigned n_words,
+                    const unsigned *table, int tiles, int tile_cells, const std::function<void()> *caller_first = nullptr);
 
 } // namespace mv3d

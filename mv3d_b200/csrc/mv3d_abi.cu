@@ -603,16 +603,26 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
     const size_t front_bytes = front_floats * 4;
     const size_t toff_words = 2 * (size_t)p.tiles_per_frame + 1;  // the tile table {first entry, entries} + the entry counter
 
-    // Layout of the list on both sides: cell indices [cap], then values [cap][planes], cap = points of the sweep. The
-    // touched cells are contiguous from entry 0 (tile by tile in the order the tiles finished; the table says where).
+    // A page-locked front buffer (cudaHostAlloc / cudaHostRegister) takes its copies straight from the device.
+    bool front_direct = false;
+    if (front_host && front_bytes) {
+        cudaPointerAttributes attr;
+        if (cudaPointerGetAttributes(&attr, front_host) == cudaSuccess) front_direct = attr.type == cudaMemoryTypeHost;
+        else cudaGetLastError();
+    }
+
+    // The read-back stream (see tile_body, kCompact): per touched cell { index, plane masks, non-zero values }, contiguous
+    // from word 0 (tile by tile in the order the tiles finished; the table says where). Its capacity covers a sweep
+    // whose every point touches a cell of its own with every plane non-zero; a sweep uses a few percent of it.
     auto enqueue = [&](int i) -> int {
         HostSlot &slot = ctx->slots[i % kSlots];
         if (!slot.stream) CUDA_TRY(cudaStreamCreateWithFlags(&slot.stream, cudaStreamNonBlocking));
         if (!slot.done) CUDA_TRY(cudaEventCreateWithFlags(&slot.done, cudaEventDisableTiming));
         cudaStream_t s = slot.stream;
         const int n = offsets_host[i + 1] - offsets_host[i];
-        const size_t cap = (size_t)n;
-        const size_t list_bytes = cap * ((size_t)p.planes + 1) * 4 + 16;
+        const size_t cap = (size_t)n * ((size_t)p.planes + 1 + (size_t)((p.planes + 31) / 32));  // words
+        if (cap > 0xFFFFFFF0ull) return fail("compact read-back: a sweep of %d points x %d planes does not fit a 32-bit word index", n, p.planes);
+        const size_t list_bytes = cap * 4 + 16;
         if (ensure(slot.points, (size_t)n * 16 + 16, false, s)) return -1;
         if (ensure(slot.compact, list_bytes, false, s)) return -1;
         if (ensure_pinned(slot.stage, list_bytes)) return -1;
@@ -641,19 +651,15 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
             return -1;
         CUDA_TRY(cudaMemcpyAsync(slot.toff_stage.ptr, slot.ctable.ptr, toff_words * 4, cudaMemcpyDeviceToHost, s));
         // Speculative copy sized from the previous sweep (first sweep: every slot); topped up later if short.
-        size_t guess = ctx->compact_est ? (size_t)ctx->compact_est + ctx->compact_est / 4 + 1024 : cap;
+        size_t guess = ctx->compact_est ? (size_t)ctx->compact_est + ctx->compact_est / 4 + 4096 : cap;  // words
         if (guess > cap) guess = cap;
         slot.copied = (unsigned)guess;
         slot.cap = (unsigned)cap;
-        if (guess) {
-            CUDA_TRY(cudaMemcpyAsync(slot.stage.ptr, slot.compact.ptr, guess * 4, cudaMemcpyDeviceToHost, s));
-            CUDA_TRY(cudaMemcpyAsync(static_cast<unsigned *>(slot.stage.ptr) + cap,
-                                     static_cast<unsigned *>(slot.compact.ptr) + cap, guess * p.planes * 4,
-                                     cudaMemcpyDeviceToHost, s));
-        }
-        if (front_host && front_bytes)
-            CUDA_TRY(cudaMemcpyAsync(slot.front_stage.ptr, front_d, front_bytes, cudaMemcpyDeviceToHost, s));
-        ctx->d2h_bytes += toff_words * 4 + guess * ((size_t)p.planes + 1) * 4 + (front_host ? front_bytes : 0);
+        if (guess) CUDA_TRY(cudaMemcpyAsync(slot.stage.ptr, slot.compact.ptr, guess * 4, cudaMemcpyDeviceToHost, s));
+        if (front_host && front_bytes)  // page-locked caller: the DMA delivers the front view itself
+            CUDA_TRY(cudaMemcpyAsync(front_direct ? static_cast<void *>(front_host + (size_t)i * front_floats) : slot.front_stage.ptr,
+                                     front_d, front_bytes, cudaMemcpyDeviceToHost, s));
+        ctx->d2h_bytes += toff_words * 4 + guess * 4 + (front_host ? front_bytes : 0);
         CUDA_TRY(cudaEventRecord(slot.done, s));
         return 0;
     };
@@ -680,16 +686,14 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         t_wait += now() - t0;
         const size_t cap = slot.cap;
         const unsigned *toff = static_cast<const unsigned *>(slot.toff_stage.ptr);
-        const unsigned used = toff[2 * (size_t)p.tiles_per_frame];  // = touched cells of the sweep
-        if (used > cap) return fail("compact read-back: %u entries, capacity %zu", used, cap);
+        const unsigned used = toff[2 * (size_t)p.tiles_per_frame];  // = words of the sweep's stream
+        if (used > cap) return fail("compact read-back: %u words, capacity %zu", used, cap);
         unsigned *stage = static_cast<unsigned *>(slot.stage.ptr), *dev = static_cast<unsigned *>(slot.compact.ptr);
         if (used > slot.copied) {  // the guess was short: fetch the rest
             const size_t more = used - slot.copied;
             CUDA_TRY(cudaMemcpyAsync(stage + slot.copied, dev + slot.copied, more * 4, cudaMemcpyDeviceToHost, slot.stream));
-            CUDA_TRY(cudaMemcpyAsync(stage + cap + (size_t)slot.copied * p.planes, dev + cap + (size_t)slot.copied * p.planes,
-                                     more * p.planes * 4, cudaMemcpyDeviceToHost, slot.stream));
             CUDA_TRY(cudaStreamSynchronize(slot.stream));
-            ctx->d2h_bytes += more * ((size_t)p.planes + 1) * 4;
+            ctx->d2h_bytes += more * 4;
         }
         ctx->compact_est = used;
         // While the workers rebuild sweep i, this thread delivers its front view and queues the GPU work of
@@ -697,7 +701,7 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         int enq_rc = 0;
         const std::function<void()> errand = [&] {
             double t1 = now();
-            if (front_host && front_bytes)
+            if (front_host && front_bytes && !front_direct)
                 memcpy(front_host + (size_t)i * front_floats, slot.front_stage.ptr, front_bytes);
             t_front += now() - t1;
             t1 = now();
@@ -706,10 +710,10 @@ static int encode_host_compact(mv3d_ctx *ctx, const float *points_host, const in
         };
         t0 = now();
         if (split)
-            scatter_compact(*ctx->pool, top_host, cells, p.planes, stage, stage + cap, used, &errand);
+            scatter_stream(*ctx->pool, top_host, cells, p.planes, stage, used, toff, p.tiles_per_frame, p.tile_cells, &errand);
         else
-            expand_sorted(*ctx->pool, top_host + (size_t)i * (size_t)p.top_frame_floats, cells, p.planes, stage,
-                          stage + cap, used, toff, p.tiles_per_frame, p.tile_cells, &errand);
+            expand_sorted(*ctx->pool, top_host + (size_t)i * (size_t)p.top_frame_floats, cells, p.planes, stage, used,
+                          toff, p.tiles_per_frame, p.tile_cells, &errand);
         t_expand += now() - t0;
         if (enq_rc) return -1;
     }
@@ -1162,46 +1166,28 @@ extern "C" int mv3d_frame_checksums_dev(mv3d_ctx *ctx, const float *views_dev, i
     return 0;
 }
 
-// Test hook for the host half of the compact read-back (needs no GPU).
-extern "C" int mv3d_debug_expand_compact(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n,
-                                         int threads)
+// Test hooks for the host half of the compact read-back (need no GPU): `words` / `table` laid out as
+// tile_compact_kernel writes them for one sweep (host_expand.h). _sorted is the single pass the host entry points run for
+// every sweep but the first of a call, _split the two steps the first one takes (zero-fill while the GPU works, then a
+// scatter of the finished values).
+extern "C" int mv3d_debug_expand_sorted(float *dst, size_t cells, int planes, const unsigned *words, unsigned n_words,
+                                        const unsigned *table, int tiles, int tile_cells, int threads)
 {
-    if (!dst || planes <= 0 || (n && !entries)) return fail("mv3d_debug_expand_compact: bad arguments");
-    // the hook takes {cell, values} records; split them into the index / value arrays the library works on
-    std::vector<unsigned> idx(n), vals((size_t)n * planes);
-    for (unsigned i = 0; i < n; i++) {
-        idx[i] = entries[(size_t)i * (planes + 1)];
-        memcpy(vals.data() + (size_t)i * planes, entries + (size_t)i * (planes + 1) + 1, (size_t)planes * 4);
-    }
-    HostPool pool(threads);
-    expand_compact(pool, dst, cells, planes, idx.data(), vals.data(), n, nullptr);
-    return 0;
-}
-
-// The linear-walk rebuild the host entry points use: idx / vals / table laid out as tile_compact_kernel writes them
-// (tile t owns the entries [table[2t], table[2t] + table[2t + 1]), ascending cells).
-extern "C" int mv3d_debug_expand_sorted(float *dst, size_t cells, int planes, const unsigned *idx, const unsigned *vals,
-                                        unsigned n, const unsigned *table, int tiles, int tile_cells, int threads)
-{
-    if (!dst || planes <= 0 || (n && (!idx || !vals)) || !table || tiles <= 0 || tile_cells <= 0)
+    if (!dst || planes <= 0 || (n_words && !words) || !table || tiles <= 0 || tile_cells <= 0)
         return fail("mv3d_debug_expand_sorted: bad arguments");
     HostPool pool(threads);
-    expand_sorted(pool, dst, cells, planes, idx, vals, n, table, tiles, tile_cells, nullptr);
+    expand_sorted(pool, dst, cells, planes, words, n_words, table, tiles, tile_cells, nullptr);
     return 0;
 }
 
-extern "C" int mv3d_debug_expand_split(float *dst, size_t cells, int planes, const unsigned *entries, unsigned n,
-                                       int threads)
+extern "C" int mv3d_debug_expand_split(float *dst, size_t cells, int planes, const unsigned *words, unsigned n_words,
+                                       const unsigned *table, int tiles, int tile_cells, int threads)
 {
-    if (!dst || planes <= 0 || (n && !entries)) return fail("mv3d_debug_expand_split: bad arguments");
-    std::vector<unsigned> idx(n), vals((size_t)n * planes);
-    for (unsigned i = 0; i < n; i++) {
-        idx[i] = entries[(size_t)i * (planes + 1)];
-        memcpy(vals.data() + (size_t)i * planes, entries + (size_t)i * (planes + 1) + 1, (size_t)planes * 4);
-    }
+    if (!dst || planes <= 0 || (n_words && !words) || !table || tiles <= 0 || tile_cells <= 0)
+        return fail("mv3d_debug_expand_split: bad arguments");
     HostPool pool(threads);
     zero_fill(pool, dst, cells * (size_t)planes);
-    scatter_compact(pool, dst, cells, planes, idx.data(), vals.data(), n, nullptr);
+    scatter_stream(pool, dst, cells, planes, words, n_words, table, tiles, tile_cells, nullptr);
     return 0;
 }
 
@@ -1236,9 +1222,14 @@ extern "C" double mv3d_debug_host_fill_buffer_gbs(float *dst, size_t bytes, int 
     std::vector<int> cpus;
     if (pin_sharers > 0) cpus = host_cpu_share(pin_share_index, pin_sharers);
     HostPool pool(threads, cpus);
-    zero_fill(pool, dst, (64u << 20) / 4 < bytes / 4 ? (64u << 20) / 4 : bytes / 4);  // wake the pool up
+    // In pieces of 64 MB -- about one view -- like the rebuild it is compared with: many small parts per thread, so a
+    // slow core delays the end of a piece by a fraction of it.
+    const size_t piece = (size_t)64 << 20;
+    zero_fill(pool, dst, (piece < bytes ? piece : bytes) / 4);  // wake the pool up
     const auto t0 = std::chrono::steady_clock::now();
-    for (int r = 0; r < reps; r++) zero_fill(pool, dst, bytes / 4);
+    for (int r = 0; r < reps; r++)
+        for (size_t b = 0; b < bytes; b += piece)
+            zero_fill(pool, dst + b / 4, ((bytes - b < piece) ? bytes - b : piece) / 4);
     const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     return sec > 0 ? (double)bytes * reps / sec / 1e9 : 0.0;
 }

@@ -1,7 +1,7 @@
-// host_rebuild_bench.cu -- the host half of the compact read-back alone, on a realistic entry list, against the plain
+// host_rebuild_bench.cu -- the host half of the compact read-back alone, on a realistic stream, against the plain
 // streaming zero-fill of the same bytes by the same threads. Needs no GPU (pageable memory).
 //   nvcc -O3 -std=c++17 -o /tmp/host_rebuild_bench tools/host_rebuild_bench.cu mv3d_b200/csrc/host_expand.cu -lpthread
-//   /tmp/host_rebuild_bench list.bin [sweeps=16]     (list.bin from tools/host_rebuild_list.py: u32 n, tiles, tile_cells; table[2*tiles+1]; idx[n])
+//   python tools/host_rebuild_list.py /tmp/list.bin && /tmp/host_rebuild_bench /tmp/list.bin [sweeps=16]
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -19,8 +19,8 @@ int main(int argc, char **argv)
     unsigned hdr[3];
     if (fread(hdr, 4, 3, f) != 3) return 1;
     const unsigned n = hdr[0], tiles = hdr[1], tile_cells = hdr[2];
-    std::vector<unsigned> toff(2 * tiles + 1), idx(n);
-    if (fread(toff.data(), 4, 2 * tiles + 1, f) != 2 * tiles + 1 || fread(idx.data(), 4, n, f) != n) return 1;
+    std::vector<unsigned> table(2 * tiles + 1), words(n);
+    if (fread(table.data(), 4, 2 * tiles + 1, f) != 2 * tiles + 1 || fread(words.data(), 4, n, f) != n) return 1;
     fclose(f);
     const size_t cells = 563200; const int planes = 27;
     const int sweeps = argc > 2 ? atoi(argv[2]) : 16;
@@ -28,36 +28,30 @@ int main(int argc, char **argv)
     float *dst = nullptr;
     if (posix_memalign((void **)&dst, 4096, frame * 4 * sweeps)) return 1;
     memset(dst, 1, frame * 4 * sweeps);
-    // one staging copy per sweep, so the values are as cold as a DMA would leave them
-    std::vector<std::vector<unsigned>> vals(sweeps, std::vector<unsigned>((size_t)n * planes, 0x3f800000u));
+    std::vector<std::vector<unsigned>> copies(sweeps, words);  // one stream per sweep, as cold as a DMA would leave it
     const unsigned hw = std::thread::hardware_concurrency();
     for (int threads : {1, 2, 4, 8, 16, 32}) {
         if ((unsigned)threads > hw) break;
         HostPool pool(threads);
-        double best_z = 1e9, best_e = 1e9, best_s = 1e9, best_l = 1e9;
+        double best_z = 1e9, best_s = 1e9, best_l = 1e9;
         for (int rep = 0; rep < 3; rep++) {
             double t0 = now();
             for (int s = 0; s < sweeps; s++) zero_fill(pool, dst + (size_t)s * frame, frame);
             best_z = std::min(best_z, (now() - t0) / sweeps);
             t0 = now();
-            for (int s = 0; s < sweeps; s++)
-                expand_compact(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, nullptr);
-            best_e = std::min(best_e, (now() - t0) / sweeps);
-            t0 = now();
             for (int s = 0; s < sweeps; s++) {
                 zero_fill(pool, dst + (size_t)s * frame, frame);
-                scatter_compact(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, nullptr);
+                scatter_stream(pool, dst + (size_t)s * frame, cells, planes, copies[s].data(), n, table.data(), (int)tiles, (int)tile_cells, nullptr);
             }
             best_s = std::min(best_s, (now() - t0) / sweeps);
             t0 = now();
             for (int s = 0; s < sweeps; s++)
-                expand_sorted(pool, dst + (size_t)s * frame, cells, planes, idx.data(), vals[s].data(), n, toff.data(), (int)tiles, (int)tile_cells, nullptr);
+                expand_sorted(pool, dst + (size_t)s * frame, cells, planes, copies[s].data(), n, table.data(), (int)tiles, (int)tile_cells, nullptr);
             best_l = std::min(best_l, (now() - t0) / sweeps);
         }
-        printf("threads=%d expand_sorted %.3f ms/sweep %.1f GB/s\n", threads, best_l * 1e3, frame * 4 / best_l / 1e9);
-        printf("threads=%d fill+scatter %.3f ms/sweep %.1f GB/s\n", threads, best_s * 1e3, frame * 4 / best_s / 1e9);
-        printf("threads=%d zero_fill %.3f ms/sweep %.1f GB/s | expand %.3f ms/sweep %.1f GB/s | ratio %.2f\n", threads, best_z * 1e3,
-               frame * 4 / best_z / 1e9, best_e * 1e3, frame * 4 / best_e / 1e9, best_e / best_z);
+        printf("threads=%d zero_fill %.3f ms/sweep %.1f GB/s | fill+scatter %.3f ms %.1f GB/s | expand_sorted %.3f ms %.1f GB/s (%.2f x fill)\n",
+               threads, best_z * 1e3, frame * 4 / best_z / 1e9, best_s * 1e3, frame * 4 / best_s / 1e9, best_l * 1e3,
+               frame * 4 / best_l / 1e9, best_l / best_z);
     }
     return 0;
 }
