@@ -193,6 +193,14 @@ int mv3d_debug_point_keys(mv3d_ctx *ctx, const float *points_dev, int num, const
 int mv3d_frame_checksums_dev(mv3d_ctx *ctx, const float *views_dev, int frames, long long floats_per_frame,
                              unsigned long long *sums_dev, void *stream);
 
+/* The library's own bounds checks, for machines without compute-sanitizer: a build with -DMV3D_SELF_CHECK tests every
+ * index its kernels compute into scratch buffers, shared-memory tiles and outputs, and records violations as bits
+ * (csrc/selfcheck.cuh). *flags receives and clears them. Returns 1 when the checks are compiled in, 0 when not
+ * (*flags = 0), -1 on error. The GPU test suite asserts *flags == 0 after every test when it runs on such a build. */
+int mv3d_debug_selfcheck(mv3d_ctx *ctx, unsigned *flags);
+/* Commits one deliberate violation (bit 15), so that a test can watch the checks report and clear; no-op otherwise. */
+int mv3d_debug_selfcheck_trip(mv3d_ctx *ctx);
+
 /* Test hooks (no GPU needed): the host half of the compact read-back used by the host-buffer entry points. `words` is
  * what the compact tile kernel reports for one sweep -- per touched cell {cell index, ceil(planes / 32) plane masks, the
  * values of the planes whose bit is set} -- and `table` holds {first word, touched cells} per tile (tile t = tile_cells

@@ -85,7 +85,7 @@ EXPORTED_SYMBOLS = (
     "mv3d_encode_batch_dev", "mv3d_encode_batch_host", "mv3d_host_alloc", "mv3d_host_free",
     "mv3d_ctx_launch_count", "mv3d_resolve_strategy", "mv3d_version",
     "mv3d_ctx_set_profiling", "mv3d_kernel_count", "mv3d_kernel_name", "mv3d_ctx_kernel_times",
-    "mv3d_front_view_noalloc", "mv3d_debug_host_fill_gbs", "mv3d_debug_host_fill_buffer_gbs", "mv3d_debug_point_keys", "mv3d_debug_expand_split", "mv3d_debug_expand_sorted", "mv3d_ctx_transfer_bytes",
+    "mv3d_front_view_noalloc", "mv3d_debug_host_fill_gbs", "mv3d_debug_host_fill_buffer_gbs", "mv3d_debug_point_keys", "mv3d_debug_expand_split", "mv3d_debug_expand_sorted", "mv3d_debug_selfcheck", "mv3d_debug_selfcheck_trip", "mv3d_ctx_transfer_bytes",
     "mv3d_pytwin_encode_batch_dev", "mv3d_pytwin_encode_batch_host", "mv3d_debug_atan2f", "mv3d_frame_checksums_dev",
     "mv3d_ctx_set_anchors", "mv3d_remove_empty_anchor_dev", "mv3d_remove_empty_anchor_host",
     "mv3d_encode_filter_batch_dev", "mv3d_pytwin_encode_filter_batch_dev",
@@ -144,6 +144,8 @@ def load_library() -> ctypes.CDLL:
     lib.mv3d_debug_host_fill_gbs.restype = ctypes.c_double
     lib.mv3d_debug_host_fill_buffer_gbs.argtypes = [vp, ctypes.c_size_t, ci, ci, ci, ci]
     lib.mv3d_debug_host_fill_buffer_gbs.restype = ctypes.c_double
+    lib.mv3d_debug_selfcheck.argtypes = [vp, vp]
+    lib.mv3d_debug_selfcheck_trip.argtypes = [vp]
     lib.mv3d_debug_expand_split.argtypes = [vp, ctypes.c_size_t, ci, vp, ctypes.c_uint, vp, ci, ci, ci]
     lib.mv3d_debug_expand_sorted.argtypes = [vp, ctypes.c_size_t, ci, vp, ctypes.c_uint, vp, ci, ci, ci]
     lib.mv3d_ctx_set_anchors.argtypes = [vp, vp, ci]

@@ -24,6 +24,7 @@
 // winner and writes the whole image (zeros included) once.
 #include "encode_kernels.h"
 #include "view_math.cuh"
+#include "selfcheck.cuh"
 
 #include <mutex>
 
@@ -158,11 +159,13 @@ classify_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOff
                     cell[k] = c.cell;
                     if (!kPy && p.want_front) {
                         const int pix = front_pixel(pt[k], p);
+                        MV3D_CHECK(pix < p.front_pixels, MV3D_BAD_PIXEL);
                         if (pix >= 0) atomicMax(winners + pix, (unsigned)idx[k] + 1u);
                     }
                 }
             }
             if (cell[k] != kInvalidKey) tile[k] = tile_of(cell[k], p);
+            MV3D_CHECK(cell[k] == kInvalidKey || tile[k] < (uint32_t)p.tiles_per_frame, MV3D_BAD_TILE);
         }
         if (p.want_top) {
             // Warp-aggregated histogram: lanes that hit the same tile share one atomicAdd. All the atomics of a round
@@ -267,6 +270,7 @@ __device__ __forceinline__ void front_finalize_body(const float4 *__restrict__ p
         float v0 = 0.0f, v1 = 0.0f, v2 = 0.0f;
         if (w) {
             winners[pix] = 0u;
+            MV3D_CHECK((int)(w - 1u) < offs.off[f + 1] - offs.off[f], MV3D_BAD_WINNER);
             const float4 pt = pts[offs.off[f] + (int)(w - 1u)];
             front_values(pt, p, v0, v1, v2);
         }
@@ -348,6 +352,9 @@ bin_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets 
                 zfield = (uint32_t)quantise(pt[j].z, p.z_min, p.z_div, p.z_inv, p.quant_floor);
                 key = __fsub_rn(pt[j].z, p.z_min);
             }
+            MV3D_CHECK(tile < (uint32_t)p.tiles_per_frame, MV3D_BAD_TILE);
+            MV3D_CHECK(start[j] + k[j].y < (unsigned)n, MV3D_BAD_BIN_SLOT);
+            MV3D_CHECK(local < (uint32_t)p.tile_cells && local < 65536u, MV3D_BAD_LOCAL_CELL);
             binned[(size_t)base + start[j] + k[j].y] =
                 make_uint4(local | (zfield << 16), __float_as_uint(key), (uint32_t)i, __float_as_uint(pt[j].w));
         }
@@ -428,6 +435,7 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
             const unsigned *off = tile_off + (size_t)f * (tpf + 1) + tl;
             const unsigned beg = __ldg(off);
             n = (int)(__ldg(off + 1) - beg);
+            MV3D_CHECK(n >= 0 && (long long)beg + n <= (long long)(offs.off[f + 1] - offs.off[f]), MV3D_BAD_BIN_RANGE);
             rec = binned + (size_t)offs.off[f] + beg;
         }
     };
@@ -478,8 +486,15 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
             // a time, so that their L2 latency overlaps
             auto accumulate = [&](const uint4 &q) {
                 const unsigned local = q.x & 0xFFFFu, Z = q.x >> 16;
+                MV3D_CHECK(local < (unsigned)T, MV3D_BAD_LOCAL_CELL);
+                MV3D_CHECK(kPy ? ((Z & (kLowerFlag - 1u)) == kNoSlice || (Z & (kLowerFlag - 1u)) < (unsigned)zn) : Z < (unsigned)zn,
+                           MV3D_BAD_SLICE);
                 unsigned *cellw = img + local * planes;
-                if (atomicAdd(cellw + zn + 1, 1u) == 0u) dirty[atomicAdd(&ndirty, 1u)] = local;
+                if (atomicAdd(cellw + zn + 1, 1u) == 0u) {
+                    const unsigned at = atomicAdd(&ndirty, 1u);
+                    MV3D_CHECK(at < (unsigned)T, MV3D_BAD_DIRTY);
+                    dirty[at] = local;
+                }
                 if ((int)q.y > 0) {  // h > 0: the reference's maps start at 0 and update on strict '>'
                     if (kPy) {  // slice = floor(qz) if it exists, and the one below when qz is integral
                         const unsigned zs = Z & (kLowerFlag - 1u);
@@ -597,6 +612,7 @@ tile_body(const uint4 *__restrict__ binned, const unsigned *__restrict__ tile_of
                     const unsigned local = dirty[d];
                     const unsigned long long kk = key[local];
                     const unsigned pos = compact_base + (unsigned)(kk >> 32);
+                    MV3D_CHECK(pos + (unsigned)kk <= compact_cap, MV3D_BAD_STREAM);
                     if (pos + (unsigned)kk > compact_cap) continue;  // the stream holds every point's worst case: never
                     if (lane == 0) out[pos] = (unsigned)cell0 + local;
                     unsigned at = pos + 1u + (unsigned)G;
@@ -824,6 +840,8 @@ atomic_scatter_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPar
             const CellHit c = classify(pt[k], p);
             if (!c.keep) continue;
             if (p.want_top) {
+                MV3D_CHECK((long long)c.cell < (long long)p.xn * p.yn, MV3D_BAD_CELL);
+                MV3D_CHECK(c.slice >= 0 && c.slice < p.zn, MV3D_BAD_SLICE);
                 unsigned *cellw = out + (size_t)c.cell * p.planes;
                 atomicAdd(cellw + p.zn + 1, 1u);
                 if (c.h > 0.0f) {
@@ -833,6 +851,7 @@ atomic_scatter_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPar
             }
             if (p.want_front) {
                 const int pix = front_pixel(pt[k], p);
+                MV3D_CHECK(pix < p.front_pixels, MV3D_BAD_PIXEL);
                 if (pix >= 0) atomicMax(winners + pix, (unsigned)i + 1u);
             }
         }
@@ -1130,5 +1149,9 @@ int launch_atomic_finalize(const float4 *pts, const FrameOffsets &offs, const Vi
     atomic_finalize_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, lut, top, cellkey);
     return 1;
 }
+
+MV3D_SELF_CHECK_READER(selfcheck_encode)
+__global__ void selfcheck_trip_kernel(int bit) { MV3D_CHECK(bit < 0, MV3D_BAD_ON_PURPOSE); }
+void selfcheck_trip(cudaStream_t s) { selfcheck_trip_kernel<<<1, 1, 0, s>>>(1); }
 
 } // namespace mv3d

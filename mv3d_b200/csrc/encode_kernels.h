@@ -62,4 +62,9 @@ int launch_atomic_scatter(const float4 *pts, const FrameOffsets &offs, const Vie
 int launch_atomic_finalize(const float4 *pts, const FrameOffsets &offs, const ViewParams &p, const float *lut,
                            int batch, int max_points, float *top, unsigned long long *cellkey, cudaStream_t s);
 
+// Violation bits of the -DMV3D_SELF_CHECK build (selfcheck.cuh), read and cleared; 0 in a normal build.
+unsigned selfcheck_encode();
+unsigned selfcheck_sort();
+void selfcheck_trip(cudaStream_t s);  // one deliberate violation (bit MV3D_BAD_ON_PURPOSE)
+
 } // namespace mv3d

@@ -5,6 +5,7 @@
 // There is no CPU implementation in this library: every path ends in the sm_100a kernels of
 // encode_kernels.cu, and every failure is reported through mv3d_last_error().
 #include "ctx.h"
+#include "selfcheck.cuh"
 #include "../../include/mv3d_anchors.h"
 
 #include <cmath>
@@ -1162,6 +1163,33 @@ extern "C" int mv3d_frame_checksums_dev(mv3d_ctx *ctx, const float *views_dev, i
             ctx->launches++;
         }
     }
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
+// The library's own bounds checks (selfcheck.cuh): *flags receives and clears the violation bits the kernels of a
+// -DMV3D_SELF_CHECK build have set since the last call (encode kernels in bits 0-15, sort arm shifted to 16-23).
+// Returns 1 when the checks are compiled in, 0 when not (then *flags = 0), -1 on error.
+extern "C" int mv3d_debug_selfcheck(mv3d_ctx *ctx, unsigned *flags)
+{
+    if (flags) *flags = 0;
+    if (!MV3D_SELF_CHECK_ENABLED) return 0;  // whatever the arguments: a caller may probe with ctx = NULL
+    if (!ctx || !flags) return fail("mv3d_debug_selfcheck: NULL argument");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    CUDA_TRY(cudaDeviceSynchronize());
+    const unsigned a = selfcheck_encode(), b = selfcheck_sort();
+    *flags = (a & 0xFFFFu) | ((b & 0xFFu) << 16) | ((a | b) & 0x80000000u);
+    return 1;
+}
+
+// One deliberate violation, so that a test can see the checks report and clear (no-op in a normal build).
+extern "C" int mv3d_debug_selfcheck_trip(mv3d_ctx *ctx)
+{
+    if (!ctx) return fail("mv3d_debug_selfcheck_trip: ctx is NULL");
+    std::lock_guard<std::mutex> lock(ctx->mu);
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    selfcheck_trip(nullptr);
     CUDA_TRY(cudaGetLastError());
     return 0;
 }

@@ -19,6 +19,7 @@
 
 #include "encode_kernels.h"
 #include "view_math.cuh"
+#include "selfcheck.cuh"
 
 namespace mv3d {
 
@@ -70,6 +71,7 @@ __device__ __forceinline__ SortedEntry fetch_entry(const float4 *__restrict__ pt
         e.slice = key - e.cell * (unsigned)p.zn;
         e.index = svals[i];
         const unsigned f = e.cell / cells;
+        MV3D_CHECK(f < (unsigned)kMaxBatchPerLaunch && (int)e.index < offs.off[f + 1] - offs.off[f], MV3D_BAD_WINNER);
         const float4 pt = __ldg(pts + offs.off[f] + e.index);
         e.hbits = __float_as_uint(__fsub_rn(pt.z, p.z_min));
         e.wbits = __float_as_uint(pt.w);
@@ -104,6 +106,7 @@ sort_reduce_kernel(const float4 *__restrict__ pts, const __grid_constant__ Frame
     }
     if (prev == e.cell) return;  // not the head of its cell's run
 
+    MV3D_CHECK(e.slice < (unsigned)p.zn, MV3D_BAD_SLICE);
     float *out = top + (size_t)e.cell * p.planes;  // frames are contiguous: (frame * cells + cell) * planes
     unsigned count = 0, cur_slice = e.slice, cur_max = 0u, best_w = 0u;
     unsigned long long best = 0ull;
@@ -186,5 +189,7 @@ int launch_sort_reduce(const float4 *pts, const FrameOffsets &offs, const ViewPa
     sort_reduce_kernel<<<(unsigned)blocks, kSortThreads, 0, s>>>(pts, offs, p, lut, skeys, svals, n, invalid_key, top);
     return 1;
 }
+
+MV3D_SELF_CHECK_READER(selfcheck_sort)
 
 } // namespace mv3d

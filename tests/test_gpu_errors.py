@@ -159,3 +159,20 @@ def test_wrapper_refuses_mismatched_buffers():
     with pytest.raises(ValueError, match="float32 numpy"):
         enc.encode_host(h, np.array([0, 100], np.int32), SMALL, SMALL_FRONT, top_out=np.zeros((1, *SMALL.shape), np.float64))
     enc.close()
+
+
+def test_selfcheck_reports_and_clears(torch_cuda, encoder_lib):
+    """The library's own bounds checks (csrc/selfcheck.cuh, -DMV3D_SELF_CHECK: the stand-in for compute-sanitizer on this
+    pool): on such a build a deliberate violation is reported once and cleared; on a normal build the hook says so."""
+    import ctypes
+    lib = encoder_lib
+    ctx = ctypes.c_void_p()
+    assert lib.mv3d_ctx_create(0, ctypes.byref(ctx)) == 0
+    flags = ctypes.c_uint(123)
+    enabled = lib.mv3d_debug_selfcheck(ctx, ctypes.byref(flags))
+    assert enabled in (0, 1) and flags.value == 0
+    assert lib.mv3d_debug_selfcheck_trip(ctx) == 0
+    assert lib.mv3d_debug_selfcheck(ctx, ctypes.byref(flags)) == enabled
+    assert flags.value == ((1 << 15) if enabled else 0)
+    assert lib.mv3d_debug_selfcheck(ctx, ctypes.byref(flags)) == enabled and flags.value == 0
+    lib.mv3d_ctx_destroy(ctx)
