@@ -717,6 +717,8 @@ __global__ void __launch_bounds__(kPointThreads)
 front_finalize_kernel(const float4 *__restrict__ pts, const __grid_constant__ FrameOffsets offs,
                       const __grid_constant__ ViewParams p, unsigned *__restrict__ fv_winner, float *__restrict__ front)
 {
+    pdl_trigger();
+    pdl_wait();  // the winners are the output of the pass in front of this launch
     front_finalize_body(pts, offs, p, fv_winner, front, blockIdx.y, blockIdx.x, gridDim.x);
 }
 
@@ -800,6 +802,7 @@ pyfront_reduce_kernel(const float4 *__restrict__ pts, FrameOffsets offs, PyFront
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) fill_zero_kernel(float *__restrict__ dst, size_t count)
 {
+    pdl_trigger();  // the atomic pass behind it may load and classify its first points while this fill drains
     // head (to 16-byte alignment), vector body, tail
     const uintptr_t addr = reinterpret_cast<uintptr_t>(dst);
     size_t head = ((16 - (addr & 15)) & 15) / 4;
@@ -814,6 +817,11 @@ __global__ void __launch_bounds__(256) fill_zero_kernel(float *__restrict__ dst,
     if (tid < count - tail0) dst[tail0 + tid] = 0.0f;
 }
 
+#ifndef MV3D_ATOMIC_ITEMS
+#define MV3D_ATOMIC_ITEMS 2
+#endif
+constexpr int kAtomicItems = MV3D_ATOMIC_ITEMS;  // points per thread and round of the two atomic passes
+
 // Pass 1: reduce straight into the (zeroed) output. Height slots hold kRawTag | h bits until finalised,
 // the density slot holds the raw count, cellkey holds the (h, ~index) winner key.
 __global__ void __launch_bounds__(kPointThreads)
@@ -821,32 +829,43 @@ atomic_scatter_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPar
                       float *__restrict__ top, unsigned long long *__restrict__ cellkey,
                       unsigned *__restrict__ fv_winner)
 {
+    pdl_trigger();
     const int f = blockIdx.y;
     const int base = offs.off[f];
     const int n = offs.off[f + 1] - base;
     unsigned *out = reinterpret_cast<unsigned *>(top + (size_t)f * p.top_frame_floats);
     unsigned long long *keys = cellkey + (size_t)f * ((size_t)p.xn * p.yn);
     unsigned *winners = fv_winner + (size_t)f * p.front_pixels;
-    // two points per thread and round: both loads are issued before the first atomic
+    // kAtomicItems points per thread and round: all loads are issued before the first atomic
     const int stride = gridDim.x * blockDim.x;
-    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 2 * stride) {
-        float4 pt[2];
-        pt[0] = load_point(pts + base + i0);
-        if (i0 + stride < n) pt[1] = load_point(pts + base + i0 + stride);
+    bool waited = false;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += kAtomicItems * stride) {
+        float4 pt[kAtomicItems];
+        CellHit c[kAtomicItems];
 #pragma unroll
-        for (int k = 0; k < 2; k++) {
+        for (int k = 0; k < kAtomicItems; k++)
+            if (i0 + k * stride < n) pt[k] = load_point(pts + base + i0 + k * stride);
+#pragma unroll
+        for (int k = 0; k < kAtomicItems; k++) {
+            c[k].keep = false;
+            if (i0 + k * stride < n) c[k] = classify(pt[k], p);
+        }
+        if (!waited) {  // the points are the caller's; the zero-fill in front of this launch must be complete from here on
+            pdl_wait();
+            waited = true;
+        }
+#pragma unroll
+        for (int k = 0; k < kAtomicItems; k++) {
             const int i = i0 + k * stride;
-            if (i >= n) continue;
-            const CellHit c = classify(pt[k], p);
-            if (!c.keep) continue;
+            if (!c[k].keep) continue;
             if (p.want_top) {
-                MV3D_CHECK((long long)c.cell < (long long)p.xn * p.yn, MV3D_BAD_CELL);
-                MV3D_CHECK(c.slice >= 0 && c.slice < p.zn, MV3D_BAD_SLICE);
-                unsigned *cellw = out + (size_t)c.cell * p.planes;
+                MV3D_CHECK((long long)c[k].cell < (long long)p.xn * p.yn, MV3D_BAD_CELL);
+                MV3D_CHECK(c[k].slice >= 0 && c[k].slice < p.zn, MV3D_BAD_SLICE);
+                unsigned *cellw = out + (size_t)c[k].cell * p.planes;
                 atomicAdd(cellw + p.zn + 1, 1u);
-                if (c.h > 0.0f) {
-                    atomicMax(cellw + c.slice, __float_as_uint(c.h) | kRawTag);
-                    atomicMax(keys + c.cell, cell_key(c.h, (uint32_t)i));
+                if (c[k].h > 0.0f) {
+                    atomicMax(cellw + c[k].slice, __float_as_uint(c[k].h) | kRawTag);
+                    atomicMax(keys + c[k].cell, cell_key(c[k].h, (uint32_t)i));
                 }
             }
             if (p.want_front) {
@@ -856,6 +875,7 @@ atomic_scatter_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPar
             }
         }
     }
+    if (!waited) pdl_wait();
 }
 
 // Pass 2: every kept point revisits its cell. The slot winner (tagged value == its own) converts the height;
@@ -866,25 +886,36 @@ __global__ void __launch_bounds__(kPointThreads)
 atomic_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewParams p, const float *__restrict__ lut,
                        float *__restrict__ top, unsigned long long *__restrict__ cellkey)
 {
+    pdl_trigger();
     const int f = blockIdx.y;
     const int base = offs.off[f];
     const int n = offs.off[f + 1] - base;
     unsigned *out = reinterpret_cast<unsigned *>(top + (size_t)f * p.top_frame_floats);
     unsigned long long *keys = cellkey + (size_t)f * ((size_t)p.xn * p.yn);
     const int stride = gridDim.x * blockDim.x;
-    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += 2 * stride) {
-        float4 pt[2];
-        pt[0] = load_point(pts + base + i0);
-        if (i0 + stride < n) pt[1] = load_point(pts + base + i0 + stride);
-        // both points' cell words are requested before either is examined
-        CellHit c[2];
-        unsigned cnt[2] = {0u, 0u}, slot[2] = {0u, 0u};
-        unsigned long long key[2] = {0ull, 0ull};
+    bool waited = false;
+    for (int i0 = blockIdx.x * blockDim.x + threadIdx.x; i0 < n; i0 += kAtomicItems * stride) {
+        float4 pt[kAtomicItems];
 #pragma unroll
-        for (int k = 0; k < 2; k++) {
+        for (int k = 0; k < kAtomicItems; k++)
+            if (i0 + k * stride < n) pt[k] = load_point(pts + base + i0 + k * stride);
+        // every point's cell words are requested before any is examined
+        CellHit c[kAtomicItems];
+        unsigned cnt[kAtomicItems], slot[kAtomicItems];
+        unsigned long long key[kAtomicItems];
+#pragma unroll
+        for (int k = 0; k < kAtomicItems; k++) {
             c[k].keep = false;
-            if (i0 + k * stride >= n) continue;
-            c[k] = classify(pt[k], p);
+            if (i0 + k * stride < n) c[k] = classify(pt[k], p);
+        }
+        if (!waited) {  // the scatter pass in front of this launch must be complete before its results are read
+            pdl_wait();
+            waited = true;
+        }
+#pragma unroll
+        for (int k = 0; k < kAtomicItems; k++) {
+            cnt[k] = slot[k] = 0u;
+            key[k] = 0ull;
             if (!c[k].keep) continue;
             unsigned *cellw = out + (size_t)c[k].cell * p.planes;
             cnt[k] = *reinterpret_cast<volatile unsigned *>(cellw + p.zn + 1);
@@ -894,7 +925,7 @@ atomic_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPa
             }
         }
 #pragma unroll
-        for (int k = 0; k < 2; k++) {
+        for (int k = 0; k < kAtomicItems; k++) {
             if (!c[k].keep) continue;
             const int i = i0 + k * stride;
             unsigned *cellw = out + (size_t)c[k].cell * p.planes;
@@ -906,6 +937,7 @@ atomic_finalize_kernel(const float4 *__restrict__ pts, FrameOffsets offs, ViewPa
             }
         }
     }
+    if (!waited) pdl_wait();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1097,7 +1129,7 @@ int launch_front_finalize(const float4 *pts, const FrameOffsets &offs, const Vie
                           unsigned *fv_winner, float *front, cudaStream_t s)
 {
     dim3 grid(point_blocks(p.front_pixels), batch);
-    front_finalize_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, fv_winner, front);
+    launch_after(front_finalize_kernel, grid, dim3(kPointThreads), 0, s, pts, offs, p, fv_winner, front);
     return 1;
 }
 
@@ -1138,7 +1170,7 @@ int launch_atomic_scatter(const float4 *pts, const FrameOffsets &offs, const Vie
                           float *top, unsigned long long *cellkey, unsigned *fv_winner, cudaStream_t s)
 {
     dim3 grid(point_blocks(max_points), batch);
-    atomic_scatter_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, top, cellkey, fv_winner);
+    launch_after(atomic_scatter_kernel, grid, dim3(kPointThreads), 0, s, pts, offs, p, top, cellkey, fv_winner);
     return 1;
 }
 
@@ -1146,7 +1178,7 @@ int launch_atomic_finalize(const float4 *pts, const FrameOffsets &offs, const Vi
                            int batch, int max_points, float *top, unsigned long long *cellkey, cudaStream_t s)
 {
     dim3 grid(point_blocks(max_points), batch);
-    atomic_finalize_kernel<<<grid, kPointThreads, 0, s>>>(pts, offs, p, lut, top, cellkey);
+    launch_after(atomic_finalize_kernel, grid, dim3(kPointThreads), 0, s, pts, offs, p, lut, top, cellkey);
     return 1;
 }
 
