@@ -81,7 +81,10 @@ def full(path, out, traffic_json=None):
             cur = json.load(open(traffic_json))
         except Exception:
             cur = {}
-        cur.update({k: sum(v) / len(v) for k, v in traffic.items()})
+        commit = subprocess.run(["git", "rev-parse", "--short", "HEAD"], capture_output=True, text=True).stdout.strip()
+        for k, v in traffic.items():  # same record as the strategies mode writes: bench.py prints commit and capture
+            cur[k] = {"bytes": sum(v) / len(v), "commit": commit, "ncu_file": os.path.basename(path),
+                      "workload": "config 2, one launch of 64 sweeps (bench.py's step)", "strategy": "tile"}
         json.dump(cur, open(traffic_json, "w"), indent=1)
 
 
