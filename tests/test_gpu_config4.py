@@ -69,3 +69,34 @@ def test_config4_resident_stream_checksums(torch_cuda, oracle_mod, strategy):
         assert np.array_equal(top[j].cpu().numpy(), et) and np.array_equal(front[j].cpu().numpy(), ef)
     stream.close()
     chk.close()
+
+
+@pytest.mark.parametrize("strategy,batch,reps", [("tile", 64, 300), ("atomic", 4, 300)])
+def test_back_to_back_launches_are_deterministic(torch_cuda, oracle_mod, strategy, batch, reps):
+    """Soak: the same batch encoded hundreds of times back to back with no host synchronisation in between, alternating
+    two output slots -- the launches are chained by programmatic dependent launch (each kernel starts while its
+    predecessor drains), so a missing dependency would show as a rare wrong frame. Every frame's checksum of every
+    repetition must equal the oracle's."""
+    torch = torch_cuda
+    from mv3d_b200.encoder import ViewEncoder
+    top_p, front_p = KITTI_PAPER_TOP, KITTI_FRONT_64x512
+    distinct = min(batch, 16)
+    clouds = [hdl64_sweep(700 + k)[: 120000 - 7000 * (k % 4)] for k in range(distinct)]
+    want = np.array([[checksum(t), checksum(f)] for t, f in (oracle_mod.top_and_front_maps(c, top_p, front_p) for c in clouds)],
+                    dtype=np.uint64)
+    pts, offs = pack_sweeps([clouds[i % distinct] for i in range(batch)])
+    d = torch.from_numpy(pts).cuda()
+    enc = ViewEncoder(0, strategy=strategy)
+    slots = [(torch.empty((batch, *top_p.shape), device="cuda"), torch.empty((batch, *front_p.shape), device="cuda")) for _ in range(2)]
+    sums = torch.zeros((reps, 2, batch), dtype=torch.int64, device="cuda")
+    for r in range(reps):
+        top, front = slots[r % 2]
+        enc.encode_device(d, offs, top_p, front_p, top_out=top, front_out=front)
+        enc.frame_checksums(top, out=sums[r, 0])
+        enc.frame_checksums(front, out=sums[r, 1])
+    torch.cuda.synchronize()
+    got = sums.cpu().numpy().astype(np.uint64)
+    expect = np.stack([want[np.arange(batch) % distinct, 0], want[np.arange(batch) % distinct, 1]])
+    bad = np.argwhere(got != expect[None])
+    assert bad.size == 0, f"{strategy}: {len(bad)} (repetition, view, frame) checksums differ, first {bad[:5].tolist()}"
+    enc.close()
