@@ -119,10 +119,13 @@ int mv3d_encode_batch_dev(mv3d_ctx *ctx, const float *points_dev, const int *off
 
 /* Same, with host buffers, pipelined sweep by sweep over internal streams; returns after the outputs are
  * complete in host memory. The bird's-eye view is ~95 % zeros, so by default it is read back COMPACT: the
- * device reports the finished values of the touched cells only and host threads (MV3D_HOST_THREADS, default
- * min(16, cores)) rebuild the dense tensor in the caller's buffer -- a zero-fill plus a scatter, no encoding
- * arithmetic on the host. MV3D_HOST_READBACK=dense copies the dense tensor over PCIe instead (pinned buffers
- * from mv3d_host_alloc are then DMA'd directly, pageable ones go through the driver's staging path). */
+ * device reports, per touched cell, its index and the finished values of its non-zero planes (about 1 MB per KITTI
+ * sweep instead of 60.8 MB) and host threads (MV3D_HOST_THREADS, default min(16, CPUs / LOCAL_WORLD_SIZE); pinned to
+ * the rank's share of the CPUs when several ranks share a host, MV3D_HOST_PIN) rebuild the dense tensor in the
+ * caller's buffer in one pass of streaming stores -- placement only, no encoding arithmetic on the host. The rate is
+ * bound by the host's memory (every sweep's 60.8 MB has to be written there by somebody), not by the GPU.
+ * MV3D_HOST_READBACK=dense copies the dense tensor over PCIe instead (pinned buffers from mv3d_host_alloc are then
+ * DMA'd directly, pageable ones go through the driver's staging path). */
 int mv3d_encode_batch_host(mv3d_ctx *ctx, const float *points_host, const int *offsets_host, int batch,
                            float *top_host, float *front_host,
                            const mv3d_top_params *tp, const mv3d_front_params *fp,
