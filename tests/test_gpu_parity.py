@@ -4,7 +4,7 @@ import numpy as np
 import pytest
 
 import cases
-from mv3d_b200.params import DENSE_TOP, KITTI_FRONT_64x512, KITTI_PAPER_TOP
+from mv3d_b200.params import DENSE_TOP, KITTI_FRONT_64x512, KITTI_PAPER_TOP, TopParams
 from mv3d_b200.sweeps import dense_cloud, hdl64_sweep, pack_sweeps
 
 pytestmark = pytest.mark.gpu
@@ -446,3 +446,25 @@ def test_five_million_points_in_one_sweep(torch_cuda, oracle_mod, strategy):
         createTopAndFrontMaps(pts, len(pts), out, fout, KITTI_PAPER_TOP.as_top_paras(), KITTI_FRONT_64x512.as_front_paras())
         assert_same(out, et, "5M host symbol top")
         assert_same(fout, ef, "5M host symbol front")
+
+
+@pytest.mark.parametrize("zn,z_div", [(40, 0.2), (33, 0.25), (300, 0.025), (1, 8.0)])
+def test_host_read_back_stream_with_many_planes(torch_cuda, oracle_mod, zn, z_div):
+    """The read-back stream of the host entry points carries a plane mask per 32 planes: grids with 42 and 35 planes
+    (two mask words), 302 planes (ten; the cell is wider than the host's compose window, so the zero-then-place path
+    runs) and 3 planes, through the batched host call and the reference symbol, against the oracle."""
+    from mv3d_b200.encoder import ViewEncoder
+    from mv3d_b200.ver3 import createTopMaps
+    top_p = TopParams(0.0, 35.2, -20.0, 20.0, -4.2, -4.2 + zn * z_div, 0.2, 0.2, z_div, 176, 200, zn)
+    sweeps = [hdl64_sweep(40), hdl64_sweep(41)[:50000], np.zeros((0, 4), np.float32), hdl64_sweep(42)[:7]]
+    pts, offs = pack_sweeps(sweeps)
+    enc = ViewEncoder(0)
+    for rep in range(2):
+        top, front = enc.encode_host(pts, offs, top_p, None)
+        assert front is None
+        for i, s in enumerate(sweeps):
+            assert_same(top[i], oracle_mod.top_maps(s, top_p), f"zn={zn} rep {rep} sweep {i}")
+    enc.close()
+    out = np.full(top_p.shape, 5.0, np.float32)
+    createTopMaps(sweeps[0], sweeps[0].shape[0], out, top_p.as_top_paras())
+    assert_same(out, oracle_mod.top_maps(sweeps[0], top_p), f"zn={zn} reference symbol")

@@ -2,6 +2,7 @@
 // streaming zero-fill of the same bytes by the same threads. Needs no GPU (pageable memory).
 //   nvcc -O3 -std=c++17 -o /tmp/host_rebuild_bench tools/host_rebuild_bench.cu mv3d_b200/csrc/host_expand.cu -lpthread
 //   python tools/host_rebuild_list.py /tmp/list.bin && /tmp/host_rebuild_bench /tmp/list.bin [sweeps=16]
+#include <sys/mman.h>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -26,7 +27,14 @@ int main(int argc, char **argv)
     const int sweeps = argc > 2 ? atoi(argv[2]) : 16;
     const size_t frame = cells * planes;
     float *dst = nullptr;
-    if (posix_memalign((void **)&dst, 4096, frame * 4 * sweeps)) return 1;
+    const bool huge = getenv("HUGE") && atoi(getenv("HUGE")) != 0;  // HUGE=1: 2 MB pages (madvise) for the destination
+    {
+        const size_t bytes = frame * 4 * sweeps, two_mb = (size_t)2 << 20;
+        char *raw = (char *)mmap(nullptr, bytes + two_mb, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+        if (raw == MAP_FAILED) return 1;
+        dst = (float *)(((uintptr_t)raw + two_mb - 1) & ~(uintptr_t)(two_mb - 1));
+        printf("destination: %s pages (madvise rc %d)\n", huge ? "2 MB" : "4 KB", madvise(dst, bytes, huge ? MADV_HUGEPAGE : MADV_NOHUGEPAGE));
+    }
     memset(dst, 1, frame * 4 * sweeps);
     std::vector<std::vector<unsigned>> copies(sweeps, words);  // one stream per sweep, as cold as a DMA would leave it
     const unsigned hw = std::thread::hardware_concurrency();
