@@ -31,6 +31,7 @@ def main():
     ap.add_argument("--distinct", type=int, default=128)
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--gather", action="store_true")
+    ap.add_argument("--depth", type=int, default=2, help="batches in flight of the host-staged stream")
     ap.add_argument("--check", type=int, default=8, help="frames re-checked on rank 0")
     ap.add_argument("--prestaged", action="store_true",
                     help="SURVEY.md 8(d) config 4 as specified: inputs pre-staged in each GPU's HBM (packed per batch "
@@ -108,7 +109,7 @@ def main():
         launches = enc.launch_count - launches0
         enc.close()
     else:
-        stream = SweepStream(local, top_p, front_p, batch=args.batch, depth=2)
+        stream = SweepStream(local, top_p, front_p, batch=args.batch, depth=args.depth)
         for _ in stream.run(mine[: 2 * args.batch], load):  # warm-up: page-locked staging, output slots, workspaces
             pass
         torch.cuda.synchronize()
