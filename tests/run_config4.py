@@ -110,7 +110,7 @@ def main():
         enc.close()
     else:
         stream = SweepStream(local, top_p, front_p, batch=args.batch, depth=args.depth)
-        for _ in stream.run(mine[: 2 * args.batch], load):  # warm-up: page-locked staging, output slots, workspaces
+        for _ in stream.run(mine[: 2 * args.depth * args.batch], load):  # warm-up: every slot's page-locked staging, outputs, workspace
             pass
         torch.cuda.synchronize()
         if world > 1:
