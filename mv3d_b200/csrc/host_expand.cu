@@ -203,6 +203,29 @@ static void store_fence()
 #endif
 }
 
+void copy_fill(HostPool &pool, void *dst, const void *const *srcs, const size_t *dst_offsets, const size_t *bytes, int n)
+{
+    if (!dst || !srcs || n <= 0) return;
+    // pieces of at most 256 KB, so that a few long sources still spread over every thread
+    constexpr size_t kPiece = (size_t)256 << 10;
+    std::vector<size_t> first(n + 1, 0);
+    for (int i = 0; i < n; i++) first[i + 1] = first[i] + (bytes[i] + kPiece - 1) / kPiece;
+    const size_t pieces = first[n];
+    if (pieces == 0) return;
+    const int parts = (int)std::min<size_t>(pieces, (size_t)pool.size() * 8);
+    const std::function<void(int)> body = [&](int part) {
+        const size_t p0 = pieces * (size_t)part / parts, p1 = pieces * ((size_t)part + 1) / parts;
+        int i = (int)(std::upper_bound(first.begin(), first.end(), p0) - first.begin()) - 1;
+        for (size_t p = p0; p < p1; p++) {
+            while (p >= first[i + 1]) i++;
+            const size_t off = (p - first[i]) * kPiece, len = std::min(kPiece, bytes[i] - off);
+            copy_stream(static_cast<char *>(dst) + dst_offsets[i] + off, static_cast<const char *>(srcs[i]) + off, len);
+        }
+        store_fence();
+    };
+    pool.parallel_for(parts, body);
+}
+
 void zero_fill(HostPool &pool, float *dst, size_t floats)
 {
     if (!dst || floats == 0) return;

@@ -46,6 +46,10 @@ private:
 // number `index`. One process per GPU under torchrun: sharers = LOCAL_WORLD_SIZE, index = LOCAL_RANK.
 std::vector<int> host_cpu_share(int index, int sharers);
 
+// Gather n source ranges into one destination buffer with streaming stores (no read-for-ownership of the destination,
+// which a DMA reads next): source i goes to dst + dst_offsets[i], bytes[i] long. Cut into 256 KB pieces over the pool.
+void copy_fill(HostPool &pool, void *dst, const void *const *srcs, const size_t *dst_offsets, const size_t *bytes, int n);
+
 // The dense view dst[cells][planes] from what tile_compact_kernel reports for one sweep (see the layout at the top of
 // the stream section in host_expand.cu): `words` is the stream of n_words 32-bit words -- per touched cell its index,
 // ceil(planes / 32) plane masks and the values of the planes whose bit is set -- and `table` holds

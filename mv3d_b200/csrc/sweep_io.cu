@@ -9,6 +9,7 @@
 // first axis can grow to 21 digits in place, blank padding to a multiple of 64 bytes, a newline.
 #include "../../include/mv3d_io.h"
 #include "ctx.h"
+#include "host_expand.h"
 
 #include <fcntl.h>
 #include <sys/stat.h>
@@ -19,6 +20,8 @@
 #include <cerrno>
 #include <cstdint>
 #include <cstring>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -322,12 +325,35 @@ extern "C" int mv3d_io_pack_sweeps(const float *const *sweeps, int n, float *dst
         if (offsets[i + 1] < offsets[i]) return fail("mv3d_io_pack_sweeps: offsets must not decrease");
         if (offsets[i + 1] > offsets[i] && !sweeps[i]) return fail("mv3d_io_pack_sweeps: sweep %d is NULL", i);
     }
-    // a sweep is ~2 MB: one memcpy each, spread over the threads (a single thread copies at ~10 GB/s, the batch of a
-    // 64-sweep launch is 123 MB)
-    run_parallel(n, threads, [&](int i) -> std::string {
-        memcpy(dst + 4 * offsets[i], sweeps[i], (size_t)(offsets[i + 1] - offsets[i]) * 16);
-        return "";
-    });
+    // The batch of a 64-sweep launch is 123 MB and the copy engine reads it next: streaming stores (no read-for-ownership
+    // of the staging buffer) from a pool of threads that outlives the call -- starting sixteen threads per batch cost as
+    // much as the copy. One pool per process and thread count, calls serialised on it.
+    static std::mutex mu;
+    static std::unique_ptr<mv3d::HostPool> pool;
+    static int pool_threads = 0;
+    static pid_t pool_pid = 0;
+    if (threads <= 0) {
+        const char *env = getenv("MV3D_IO_THREADS");
+        threads = env && atoi(env) > 0 ? atoi(env) : 16;
+        const unsigned hw = std::thread::hardware_concurrency();
+        if (hw > 0 && (unsigned)threads > hw) threads = (int)hw;
+    }
+    std::vector<const void *> srcs(n);
+    std::vector<size_t> offs(n), bytes(n);
+    for (int i = 0; i < n; i++) {
+        srcs[i] = sweeps[i];
+        offs[i] = (size_t)offsets[i] * 16;
+        bytes[i] = (size_t)(offsets[i + 1] - offsets[i]) * 16;
+    }
+    std::lock_guard<std::mutex> lock(mu);
+    if (pool && pool_pid != getpid()) pool.release();  // forked: the parent's worker threads do not exist here (leaked on purpose)
+    if (!pool || pool_threads != threads) {
+        pool.reset(new (std::nothrow) mv3d::HostPool(threads));
+        pool_pid = getpid();
+        if (!pool) return fail("mv3d_io_pack_sweeps: cannot create the copy pool");
+        pool_threads = threads;
+    }
+    mv3d::copy_fill(*pool, dst, srcs.data(), offs.data(), bytes.data(), n);
     return 0;
 }
 

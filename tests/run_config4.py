@@ -31,7 +31,7 @@ def main():
     ap.add_argument("--distinct", type=int, default=128)
     ap.add_argument("--batch", type=int, default=64)
     ap.add_argument("--gather", action="store_true")
-    ap.add_argument("--depth", type=int, default=2, help="batches in flight of the host-staged stream")
+    ap.add_argument("--depth", type=int, default=3, help="batches in flight of the host-staged stream")
     ap.add_argument("--check", type=int, default=8, help="frames re-checked on rank 0")
     ap.add_argument("--prestaged", action="store_true",
                     help="SURVEY.md 8(d) config 4 as specified: inputs pre-staged in each GPU's HBM (packed per batch "
@@ -125,6 +125,8 @@ def main():
             done += nb
         torch.cuda.synchronize()
         elapsed = shard.max_over_ranks(time.perf_counter() - t0, device=dev)
+        if rank == 0:
+            print("host thread, seconds (warm-up included):", {k: round(v, 4) for k, v in stream.trace.items()}, file=sys.stderr)
         launches = stream.launch_count + chk.launch_count
         stream.close()
     chk.close()
