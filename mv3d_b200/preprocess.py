@@ -63,10 +63,14 @@ def preprocess_files(files: Sequence[str], top_dir: Optional[str], front_dir: Op
     stats = {"frames": 0, "points": 0, "read_s": 0.0, "encode_s": 0.0, "write_s": 0.0, "skipped": skipped}
     nxt = {}
 
-    def read(group, slot):
+    # Three page-locked staging buffers in rotation: one being read into, one being encoded from, one spare -- a fresh
+    # page-locked allocation per batch costs more than reading the batch.
+    stagings = [sweep_io.SweepStaging() for _ in range(3)]
+
+    def read(group, slot, staging):
         t0 = time.perf_counter()
         try:
-            slot["data"] = sweep_io.read_sweeps(group, threads=io_threads)
+            slot["data"] = sweep_io.read_sweeps(group, threads=io_threads, staging=staging)
         except Exception as e:
             slot["error"] = e
         slot["s"] = time.perf_counter() - t0
@@ -74,7 +78,7 @@ def preprocess_files(files: Sequence[str], top_dir: Optional[str], front_dir: Op
     def start(i):
         if i < len(groups):
             slot = {}
-            th = threading.Thread(target=read, args=(groups[i], slot), daemon=True)
+            th = threading.Thread(target=read, args=(groups[i], slot, stagings[i % 3]), daemon=True)
             th.start()
             nxt[i] = (th, slot)
 

@@ -58,20 +58,37 @@ def sweep_sizes(paths: Sequence[str]) -> np.ndarray:
     return out
 
 
-def read_sweeps(paths: Sequence[str], threads: int = 0, pinned: bool = True):
+def read_sweeps(paths: Sequence[str], threads: int = 0, pinned: bool = True, staging: "SweepStaging | None" = None):
     """Read a batch of KITTI `.bin` sweeps into ONE packed `(total, 4)` float32 array (page-locked by default) and
     return `(points, offsets)` -- what `pack_sweeps` makes of a list of arrays, and what `ViewEncoder.encode_host` /
-    a single `cudaMemcpyAsync` want."""
+    a single `cudaMemcpyAsync` want. A caller that reads batch after batch passes a `SweepStaging`: the page-locked
+    buffer is then reused (allocating one per batch costs more than reading the files), and `points` is a view of it that
+    stays valid until the same staging object is used again."""
     lib = _lib.load_library()
     sizes = sweep_sizes(paths)
     offsets = np.zeros(len(paths) + 1, dtype=np.int64)
     np.cumsum(sizes, out=offsets[1:])
     total = int(offsets[-1])
-    points = pinned_empty((total, 4), np.float32) if pinned else np.empty((total, 4), np.float32)
+    if staging is not None:
+        points = staging.take(total)
+    else:
+        points = pinned_empty((total, 4), np.float32) if pinned else np.empty((total, 4), np.float32)
     arr, _keep = _paths(paths)
     if lib.mv3d_io_read_sweeps(arr, len(paths), points.ctypes.data, offsets.ctypes.data, int(threads)) != 0:
         raise OSError(_lib.last_error())
     return points, offsets.astype(np.int32)
+
+
+class SweepStaging:
+    """A grow-only page-locked staging buffer for `read_sweeps`: `take(n)` returns a `(n, 4)` float32 view of it."""
+
+    def __init__(self):
+        self._buf = None  # allocated on first use: a run that finds nothing to read needs no GPU driver
+
+    def take(self, points: int) -> np.ndarray:
+        if self._buf is None or points > self._buf.shape[0]:
+            self._buf = pinned_empty((points + points // 4 + 1024, 4), np.float32)
+        return self._buf[:points]
 
 
 def pack_sweeps_into(sweeps: Sequence[np.ndarray], dst: np.ndarray, threads: int = 0) -> np.ndarray:
