@@ -329,7 +329,7 @@ extern "C" int mv3d_io_pack_sweeps(const float *const *sweeps, int n, float *dst
     // of the staging buffer) from a pool of threads that outlives the call -- starting sixteen threads per batch cost as
     // much as the copy. One pool per process and thread count, calls serialised on it.
     static std::mutex mu;
-    static std::unique_ptr<mv3d::HostPool> pool;
+    static mv3d::HostPool *pool = nullptr;  // never destroyed: joining its threads at exit would hang a forked child
     static int pool_threads = 0;
     static pid_t pool_pid = 0;
     if (threads <= 0) {
@@ -346,9 +346,13 @@ extern "C" int mv3d_io_pack_sweeps(const float *const *sweeps, int n, float *dst
         bytes[i] = (size_t)(offsets[i + 1] - offsets[i]) * 16;
     }
     std::lock_guard<std::mutex> lock(mu);
-    if (pool && pool_pid != getpid()) pool.release();  // forked: the parent's worker threads do not exist here (leaked on purpose)
-    if (!pool || pool_threads != threads) {
-        pool.reset(new (std::nothrow) mv3d::HostPool(threads));
+    if (pool && pool_pid != getpid()) pool = nullptr;  // forked: the parent's worker threads do not exist here
+    if (pool && pool_threads != threads) {
+        delete pool;
+        pool = nullptr;
+    }
+    if (!pool) {
+        pool = new (std::nothrow) mv3d::HostPool(threads);
         pool_pid = getpid();
         if (!pool) return fail("mv3d_io_pack_sweeps: cannot create the copy pool");
         pool_threads = threads;
